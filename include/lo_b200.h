@@ -1,0 +1,181 @@
+/*
+ * lo_b200.h — C ABI of the B200-native scan-to-keyframe registration library (liblo_b200.so).
+ *
+ * This is the drop-in boundary for the reference's registration hot path. The reference
+ * (vovo-4K/lidar_odometry_demo) has no FFI layer: its seam is three plain C++ classes. Each entry point
+ * below names the reference interface it replaces (paths relative to the reference tree); the C++ facade
+ * in lidar_odometry_demo_b200/host/ re-creates those classes on top of this ABI, and INTEGRATION.md shows
+ * the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns LO_OK (0) or a negative LO_E_* code; lo_last_error() gives the text.
+ *   - no C++ exceptions cross the ABI; all device memory is owned by the opaque handles.
+ *   - point layouts are the reference's wire structs, so `cloud.points.data()` can be passed as is:
+ *       xyz16    pcl::PointXYZ      16 B  {x,y,z,pad}
+ *       pn48     pcl::PointNormal   48 B  {x,y,z,pad, nx,ny,nz,pad, curvature,pad[3]}
+ *       xyzirt32 lidar_point::PointXYZIRT 32 B {x,y,z,pad, intensity, ring(u16)@20, time@24}
+ *                (src/lidar_point_type.h:13-31)
+ *   - pose7 = {tx,ty,tz, qw,qx,qy,qz} float  (Pose3D, src/pose_3d.h:10-21)
+ *   - handles are not thread-safe; distinct lo_ctx are independent (one per GPU / per sequence).
+ *   - calls taking host pointers are synchronous: results are on the host when they return.
+ *     `_dev` variants take device pointers (cudaMalloc'ed or a torch tensor's data_ptr) on the context's
+ *     device and only enqueue work on the context's stream.
+ *   - there is no CPU fallback: if no CUDA device is present lo_ctx_create fails with LO_E_CUDA.
+ */
+#ifndef LO_B200_H
+#define LO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    LO_OK = 0,
+    LO_E_CUDA = -1,      /* CUDA runtime error (text in lo_last_error) */
+    LO_E_ARG = -2,       /* bad argument */
+    LO_E_CAPACITY = -3,  /* caller buffer too small; the needed count is returned through the size out-param */
+    LO_E_RANGE = -4,     /* a voxel index fell outside the supported +-2^20 range */
+    LO_E_IO = -5         /* file could not be read / parsed */
+};
+
+typedef struct lo_ctx lo_ctx;
+typedef struct lo_grid lo_grid;
+typedef struct lo_odometry lo_odometry;
+
+/* ---- context: one CUDA device + one stream + scratch ---------------------------------------- */
+int lo_ctx_create(int device, lo_ctx** out);
+void lo_ctx_destroy(lo_ctx* ctx);
+const char* lo_last_error(void);
+/* cudaStream_t of the context (for CUDA-event timing by the caller) */
+void* lo_ctx_stream(lo_ctx* ctx);
+int lo_ctx_synchronize(lo_ctx* ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t lo_ctx_kernel_launches(const lo_ctx* ctx);
+
+/* ---- voxel keys: VoxelGrid::getIndices + IndicesHash (src/voxel_grid.h:31-38,68-75) ---------- */
+/* keys3: n x 3 int64 (ix,iy,iz); hash22: n uint32, the reference's 22-bit hash; either may be NULL */
+int lo_voxel_keys(lo_ctx* ctx, float voxel_size, const float* xyz16, size_t n, int64_t* keys3, uint32_t* hash22);
+
+/* ---- VoxelGrid (src/voxel_grid.h:17-257) ------------------------------------------------------ */
+/* VoxelGrid(voxel_size, max_points). capacity_hint = expected number of voxels (0: default); the table
+ * grows on demand. The grid keeps, per voxel, the first max_points points in arrival order (:77-93). */
+int lo_grid_create(lo_ctx* ctx, float voxel_size, size_t max_points, size_t capacity_hint, lo_grid** out);
+void lo_grid_destroy(lo_grid* g);
+/* setVoxelSize (:61-66): clears the grid */
+int lo_grid_set_voxel_size(lo_grid* g, float voxel_size);
+/* size() (:248-251): number of voxels */
+int lo_grid_size(lo_grid* g, size_t* n_voxels, size_t* n_points);
+/* addCloud (:77-93) for pn48 (has_normals=1) / addCloudWithoutNormals (:95-110) for xyz16 (has_normals=0) */
+int lo_grid_add_cloud(lo_grid* g, const void* points, size_t n, int has_normals);
+int lo_grid_add_cloud_dev(lo_grid* g, const void* d_points, size_t n, int has_normals);
+/* getCloud (:112-129) mode 0 -> pn48; getCloudWithoutNormals (:132-146) mode 1 -> xyz16;
+ * getSparseCloudWithoutNormals (:149-162) mode 2 -> xyz16 (first point of every voxel).
+ * order 0: unspecified (fast); order 1: the reference's tsl::robin_map iteration order, valid for grids
+ * that were filled by add_cloud calls only (no radius_cleanup) — the down-sampler use of lidar_odometry.cpp:37-50.
+ * *n receives the number of points; LO_E_CAPACITY if cap is too small. out may be NULL to query *n. */
+int lo_grid_get_cloud(lo_grid* g, int mode, int order, void* out, size_t cap, size_t* n);
+/* radiusCleanup (:236-246): erase voxels whose FIRST stored point is farther than radius from center */
+int lo_grid_radius_cleanup(lo_grid* g, const float center[3], float radius);
+
+typedef struct lo_pair {   /* VoxelGrid::Correspondence (:40-46) */
+    double source_point_local[3];
+    double plane_origin[3];
+    double plane_normal[3];
+} lo_pair;
+/* findMatchingPairs (:206-234) with the query index kept: pairs[i] / valid[i] for every query i
+ * (entries of invalid queries are zero); *n_valid = number of valid correspondences. */
+int lo_grid_find_matching_pairs(lo_grid* g, const float* xyz16, size_t m, const float pose7[7], float max_dist,
+                                lo_pair* pairs, uint8_t* valid, size_t* n_valid);
+
+/* ---- residual + normal equations (src/cloud_matcher.cpp:38-103,134-154) ----------------------- */
+typedef struct lo_normal_eq {
+    double cost;        /* sum of 0.5*rho(r^2) + prior */
+    double g[6];        /* J'r, tangent order: rotation(3), translation(3) */
+    double jtj[36];     /* J'J row-major */
+    uint64_t n_valid;   /* correspondences found */
+} lo_normal_eq;
+/* One fused pass: correspondence search at pose7 (float, as findMatchingPairs sees it) then
+ * PointToPlaneErrorAnalytic + HuberLoss(0.15) corrector evaluated at x7d = {qw,qx,qy,qz,tx,ty,tz} (double),
+ * reduced to the 6x6 normal equations; prior_b = NormalPrior mean (the guess translation). */
+int lo_nn_residual(lo_grid* g, const float* xyz16, size_t m, const float pose7[7], const double x7d[7],
+                   const double prior_b[3], float max_dist, lo_normal_eq* out);
+int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], const double x7d[7],
+                       const double prior_b[3], float max_dist, lo_normal_eq* out_host_or_null);
+
+/* ---- CloudMatcher::align (src/cloud_matcher.h:13-17, src/cloud_matcher.cpp:105-178) ----------- */
+typedef struct lo_align_stats {
+    int32_t outer_iterations;        /* 1..35 */
+    int32_t lm_iterations;           /* recorded LM iterations summed over all outer iterations */
+    int32_t valid_pairs;             /* correspondences in the last outer iteration */
+    int32_t termination;             /* of the last solve: 0 no_convergence, 1 function tol, 2 parameter tol, 3 gradient tol, 4 failure */
+    double final_cost;
+    double last_step_norm;
+    float pose_log[35][7];           /* pose after each outer iteration's float round-trip */
+    int32_t pairs_log[35];
+} lo_align_stats;
+int lo_align(lo_grid* keyframe, const float* xyz16, size_t m, const float guess7[7], float out7[7],
+             lo_align_stats* stats /* nullable */);
+int lo_align_dev(lo_grid* keyframe, const void* d_xyz16, size_t m, const float guess7[7], float out7[7],
+                 lo_align_stats* stats /* nullable */);
+
+/* ---- CloudTransformer / utils (src/utils) ------------------------------------------------------ */
+/* pointTimeNormalize (point_time_normalize.h:14-39) followed by transformNonRigid
+ * (cloud_transform.h:15-40) with (start7, end7); out may alias in. */
+int lo_deskew(lo_ctx* ctx, const void* xyzirt32_in, size_t n, const float start7[7], const float end7[7],
+              void* xyzirt32_out);
+/* transform<PointXYZ> (cloud_transform.h:42-66) */
+int lo_transform_xyz(lo_ctx* ctx, const float* xyz16_in, size_t n, const float pose7[7], float* xyz16_out);
+/* transformWithNormals (cloud_transform.h:68-97) */
+int lo_transform_with_normals(lo_ctx* ctx, const float* pn48_in, size_t n, const float pose7[7], float* pn48_out);
+/* rangeFilter (range_filter.h:12-28), order preserving; *n_out = points kept */
+int lo_range_filter(lo_ctx* ctx, const float* pn48_in, size_t n, float min_range, float max_range, float* pn48_out,
+                    size_t* n_out);
+/* CloudClassifier::classify (cloud_classifier.h:19-168): planar points with normals, reference order */
+int lo_classify(lo_ctx* ctx, const void* xyzirt32_in, size_t n, float* pn48_planar_out, size_t cap, size_t* n_planar);
+
+/* ---- per-point PCA normals: the test's pcl::NormalEstimation (test/test.cpp:196-205) ---------- */
+int lo_pca_normals(lo_ctx* ctx, const float* xyz16, size_t n, float radius, float* normals3_out);
+
+/* ---- LidarOdometry (src/lidar_odometry.h:18-86, src/lidar_odometry.cpp:14-89) ----------------- */
+typedef struct lo_params {               /* LidarOdometry::Params (lidar_odometry.h:25-32), config/params.yaml:4-11 */
+    float lidar_min_range;
+    float lidar_max_range;
+    float keyframe_voxel_size;
+    uint64_t keyframe_max_points_cnt;
+    float keyframe_matching_voxel_size;
+    float keyframe_update_voxel_size;
+    float keyframe_cleanup_range;
+    float angular_divergence_threshold;
+} lo_params;
+void lo_params_default(lo_params* p);                      /* GetROSDeclaration defaults (lidar_odometry.h:36-48) */
+int lo_params_from_yaml(const char* path, lo_params* p);  /* reads config/params.yaml's lidar_odometry block */
+
+typedef struct lo_scan_stats {
+    uint32_t n_points, n_planar, n_update, n_query;  /* N, P, U, M of SURVEY.md section 3.1 */
+    int32_t outer_iterations;
+    int32_t unstable;            /* 1 if the divergence gate fell back to the prediction */
+    uint32_t keyframe_voxels;
+    uint32_t reserved;
+} lo_scan_stats;
+
+int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odometry** out);
+void lo_odometry_destroy(lo_odometry* h);
+/* processCloud (lidar_odometry.cpp:22-76) */
+int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t n);
+int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);
+/* same pipeline entered after CloudClassifier::classify (lidar_odometry.cpp:35 onwards) with a planar cloud */
+int lo_odometry_process_planar(lo_odometry* h, const float* pn48_planar, size_t n);
+int lo_odometry_pose(lo_odometry* h, float out7[7]);                       /* getCurrentPose */
+int lo_odometry_stats(lo_odometry* h, lo_scan_stats* out);
+/* getKeyFrameCloud (full=0, sparse) / getFullKeyFrameCloud (full=1): xyz16 */
+int lo_odometry_keyframe(lo_odometry* h, int full, float* xyz16_out, size_t cap, size_t* n);
+int lo_odometry_keyframe_pn(lo_odometry* h, float* pn48_out, size_t cap, size_t* n);
+int lo_odometry_deskewed(lo_odometry* h, void* xyzirt32_out, size_t cap, size_t* n);  /* getTempCloud */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LO_B200_H */

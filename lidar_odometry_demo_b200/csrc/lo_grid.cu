@@ -1,0 +1,449 @@
+// K2/K3: the GPU voxel grid that replaces VoxelGrid's tsl::robin_map (src/voxel_grid.h:17-257).
+//
+// Layout in HBM (DESIGN.md "data layout"):
+//   slots   [capacity]              16 B {key64, vid, count}; open addressing, linear probing, load <= 0.5
+//   points  [payload_cap * width]   float4 xyz + w (w = arrival ticket of the stored point)
+//   normals [payload_cap * width]   float4
+// A voxel keeps its first `max_points` points in arrival order (voxel_grid.h:82-91). Parallel insertion
+// reproduces that order without sorting: every point carries a ticket (its position in the arrival
+// sequence) and is pushed through the free entries of its voxel's slab with a chain of atomicMin on the
+// w lane; entry k ends up holding the k-th smallest ticket, whatever the thread interleaving.
+#include <algorithm>
+
+#include "lo_host.h"
+
+namespace lo {
+
+constexpr uint32_t kInvalid = 0xFFFFFFFFu;
+
+struct PointSource {       // AoS input: pcl::PointNormal (48 B) or pcl::PointXYZ (16 B)
+    const float* base;
+    uint32_t stride_f;     // floats per record: 12 or 4
+    int has_normals;
+};
+
+__device__ inline void load_point(const PointSource& src, uint32_t i, const Pose* pose, float p[3], float nrm[3]) {
+    const float4 a = *reinterpret_cast<const float4*>(src.base + static_cast<size_t>(i) * src.stride_f);
+    p[0] = a.x; p[1] = a.y; p[2] = a.z;
+    if (src.has_normals) {
+        const float4 b = *reinterpret_cast<const float4*>(src.base + static_cast<size_t>(i) * src.stride_f + 4);
+        nrm[0] = b.x; nrm[1] = b.y; nrm[2] = b.z;
+    } else {
+        nrm[0] = nrm[1] = nrm[2] = 0.f;
+    }
+    if (pose) {  // transformWithNormals fused into the load (src/utils/cloud_transform.h:68-97)
+        float r[9], o[3];
+        rotation_matrix_f(pose->w, pose->x, pose->y, pose->z, r);
+        mat_vec_f(r, p[0], p[1], p[2], o);
+        p[0] = o[0] + pose->t[0]; p[1] = o[1] + pose->t[1]; p[2] = o[2] + pose->t[2];
+        mat_vec_f(r, nrm[0], nrm[1], nrm[2], o);
+        nrm[0] = o[0]; nrm[1] = o[1]; nrm[2] = o[2];
+    }
+}
+
+__device__ inline uint32_t alloc_vid(uint32_t* counters, const uint32_t* free_list) {
+    const int t = atomicSub(reinterpret_cast<int*>(&counters[GC_FREE_TOP]), 1);
+    if (t > 0) return free_list[t - 1];
+    return atomicAdd(&counters[GC_BUMP], 1u);
+}
+
+// pass 1: find or create the voxel of every point
+__global__ void grid_locate_kernel(PointSource src, uint32_t n_bound, const uint32_t* __restrict__ d_n, const Pose* __restrict__ pose, GridView g,
+                                   uint32_t* __restrict__ counters, const uint32_t* __restrict__ free_list,
+                                   uint32_t* __restrict__ slot_of) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = d_n ? min(n_bound, *d_n) : n_bound;
+    if (i >= n) return;
+    float p[3], nrm[3];
+    load_point(src, i, pose, p, nrm);
+    const long long ix = axis_index(p[0], g.voxel_size), iy = axis_index(p[1], g.voxel_size), iz = axis_index(p[2], g.voxel_size);
+    const bool finite = isfinite(p[0]) && isfinite(p[1]) && isfinite(p[2]);
+    if (!finite || !axis_in_range(ix) || !axis_in_range(iy) || !axis_in_range(iz)) {
+        counters[GC_RANGE_ERR] = 1;
+        slot_of[i] = kInvalid;
+        return;
+    }
+    const unsigned long long key = pack_key(ix, iy, iz);
+    uint32_t h = probe_hash(key) & g.mask;
+    while (true) {
+        unsigned long long k = g.slots[h].key;
+        if (k == kKeyEmpty) {
+            k = atomicCAS(&g.slots[h].key, kKeyEmpty, key);
+            if (k == kKeyEmpty) {  // this thread created the voxel
+                g.slots[h].vid = alloc_vid(counters, free_list);
+                g.slots[h].count = 0;
+                atomicAdd(&counters[GC_VOXELS], 1u);
+                break;
+            }
+        }
+        if (k == key) break;
+        h = (h + 1) & g.mask;
+    }
+    slot_of[i] = h;
+}
+
+// pass 2: ticket chain. Entry e >= base of the voxel's slab ends up with the (e-base)-th smallest ticket.
+__global__ void grid_chain_kernel(uint32_t n_bound, const uint32_t* __restrict__ d_n, uint32_t ticket_base, GridView g, const uint32_t* __restrict__ slot_of,
+                                  uint32_t* __restrict__ base_of) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = d_n ? min(n_bound, *d_n) : n_bound;
+    if (i >= n) return;
+    const uint32_t s = slot_of[i];
+    if (s == kInvalid) return;
+    const uint32_t vid = g.slots[s].vid;
+    const uint32_t base = g.slots[s].count;
+    base_of[i] = base;
+    uint32_t carry = ticket_base + i;
+    uint32_t* lane_w = reinterpret_cast<uint32_t*>(g.points + static_cast<size_t>(vid) * g.width) + 3;
+    for (uint32_t e = base; e < g.width; e++) {
+        const uint32_t old = atomicMin(lane_w + 4 * e, carry);
+        if (old == kInvalid) break;     // entry was free: carry placed, nothing displaced
+        if (old > carry) carry = old;   // carry placed, the displaced ticket moves on
+    }
+}
+
+// pass 3: every point whose ticket survived writes its coordinates and normal
+__global__ void grid_write_kernel(PointSource src, uint32_t n_bound, const uint32_t* __restrict__ d_n, uint32_t ticket_base, const Pose* __restrict__ pose,
+                                  GridView g, uint32_t* __restrict__ counters, const uint32_t* __restrict__ slot_of,
+                                  const uint32_t* __restrict__ base_of) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = d_n ? min(n_bound, *d_n) : n_bound;
+    if (i >= n) return;
+    const uint32_t s = slot_of[i];
+    if (s == kInvalid) return;
+    const uint32_t vid = g.slots[s].vid;
+    const uint32_t ticket = ticket_base + i;
+    float4* slab = g.points + static_cast<size_t>(vid) * g.width;
+    for (uint32_t e = base_of[i]; e < g.width; e++) {
+        const uint32_t w = __float_as_uint(slab[e].w);
+        if (w == ticket) {
+            float p[3], nrm[3];
+            load_point(src, i, pose, p, nrm);
+            slab[e] = make_float4(p[0], p[1], p[2], __uint_as_float(ticket));
+            g.normals[static_cast<size_t>(vid) * g.width + e] = make_float4(nrm[0], nrm[1], nrm[2], 0.f);
+            atomicMax(&g.slots[s].count, e + 1);
+            atomicAdd(&counters[GC_POINTS], 1u);
+            break;
+        }
+        if (w > ticket) break;  // entries are sorted: the ticket was dropped (voxel full)
+    }
+}
+
+__global__ void grid_fix_counters_kernel(uint32_t* counters) {
+    if (reinterpret_cast<int*>(counters)[GC_FREE_TOP] < 0) counters[GC_FREE_TOP] = 0;
+}
+
+// radiusCleanup (voxel_grid.h:236-246): the voxel's position is its FIRST stored point
+__global__ void grid_cleanup_kernel(GridView g, uint32_t capacity, const float* __restrict__ center, float radius,
+                                    uint32_t* __restrict__ counters, uint32_t* __restrict__ free_list) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= capacity) return;
+    const Slot slot = g.slots[s];
+    if (slot.key == kKeyEmpty || slot.key == kKeyTomb) return;
+    const float4 o = g.points[static_cast<size_t>(slot.vid) * g.width];
+    const float r2 = radius * radius;
+    const float dx = o.x - center[0], dy = o.y - center[1], dz = o.z - center[2];
+    const float d2 = dx * dx + (dy * dy + dz * dz);
+    if (d2 > r2) {
+        g.slots[s].key = kKeyTomb;
+        g.slots[s].count = 0;
+        uint32_t* lane_w = reinterpret_cast<uint32_t*>(g.points + static_cast<size_t>(slot.vid) * g.width) + 3;
+        for (uint32_t e = 0; e < slot.count; e++) lane_w[4 * e] = kInvalid;
+        const uint32_t top = atomicAdd(&counters[GC_FREE_TOP], 1u);
+        free_list[top] = slot.vid;
+        atomicSub(&counters[GC_VOXELS], 1u);
+        atomicSub(&counters[GC_POINTS], slot.count);
+        atomicAdd(&counters[GC_TOMBS], 1u);
+    }
+}
+
+// move live slots into a fresh table (growth, or purge of tombstones)
+__global__ void grid_rebuild_kernel(const Slot* __restrict__ old_slots, uint32_t old_capacity, Slot* __restrict__ new_slots,
+                                    uint32_t new_mask) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= old_capacity) return;
+    const Slot slot = old_slots[s];
+    if (slot.key == kKeyEmpty || slot.key == kKeyTomb) return;
+    uint32_t h = probe_hash(slot.key) & new_mask;
+    while (atomicCAS(&new_slots[h].key, kKeyEmpty, slot.key) != kKeyEmpty) h = (h + 1) & new_mask;
+    new_slots[h].vid = slot.vid;
+    new_slots[h].count = slot.count;
+}
+
+// getCloud / getCloudWithoutNormals / getSparseCloudWithoutNormals, unspecified voxel order
+__global__ void grid_export_kernel(GridView g, uint32_t capacity, int mode, void* __restrict__ out, uint32_t* __restrict__ cursor) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= capacity) return;
+    const Slot slot = g.slots[s];
+    if (slot.key == kKeyEmpty || slot.key == kKeyTomb || slot.count == 0) return;
+    const uint32_t cnt = (mode == 2) ? 1u : slot.count;
+    const uint32_t off = atomicAdd(cursor, cnt);
+    if (!out) return;
+    for (uint32_t e = 0; e < cnt; e++) {
+        const float4 p = g.points[static_cast<size_t>(slot.vid) * g.width + e];
+        if (mode == 0) {
+            const float4 nv = g.normals[static_cast<size_t>(slot.vid) * g.width + e];
+            float4* o = reinterpret_cast<float4*>(static_cast<PointNormal*>(out) + off + e);
+            o[0] = make_float4(p.x, p.y, p.z, 1.f);
+            o[1] = make_float4(nv.x, nv.y, nv.z, 0.f);
+            o[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+            reinterpret_cast<float4*>(out)[off + e] = make_float4(p.x, p.y, p.z, 1.f);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+static uint32_t next_pow2(uint64_t v) {
+    uint64_t p = 1;
+    while (p < v) p <<= 1;
+    return static_cast<uint32_t>(p);
+}
+
+static int alloc_table(lo_grid* g, uint32_t capacity, Slot** out) {
+    LO_CUDA(cudaMalloc(out, static_cast<size_t>(capacity) * sizeof(Slot)));
+    LO_CUDA(cudaMemsetAsync(*out, 0xFF, static_cast<size_t>(capacity) * sizeof(Slot), g->ctx->stream));
+    return LO_OK;
+}
+
+static int grow_payload(lo_grid* g, uint32_t new_cap) {
+    lo_ctx* ctx = g->ctx;
+    float4 *np = nullptr, *nn = nullptr;
+    uint32_t* nf = nullptr;
+    const size_t new_elems = static_cast<size_t>(new_cap) * g->width, old_elems = static_cast<size_t>(g->payload_cap) * g->width;
+    LO_CUDA(cudaMalloc(&np, new_elems * sizeof(float4)));
+    LO_CUDA(cudaMalloc(&nn, new_elems * sizeof(float4)));
+    LO_CUDA(cudaMalloc(&nf, static_cast<size_t>(new_cap) * sizeof(uint32_t)));
+    if (old_elems) {
+        LO_CUDA(cudaMemcpyAsync(np, g->points, old_elems * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
+        LO_CUDA(cudaMemcpyAsync(nn, g->normals, old_elems * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
+        LO_CUDA(cudaMemcpyAsync(nf, g->free_list, static_cast<size_t>(g->payload_cap) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    LO_CUDA(cudaMemsetAsync(np + old_elems, 0xFF, (new_elems - old_elems) * sizeof(float4), ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (g->points) cudaFree(g->points);
+    if (g->normals) cudaFree(g->normals);
+    if (g->free_list) cudaFree(g->free_list);
+    g->points = np; g->normals = nn; g->free_list = nf;
+    g->payload_cap = new_cap;
+    return LO_OK;
+}
+
+static int rebuild_table(lo_grid* g, uint32_t new_capacity) {
+    lo_ctx* ctx = g->ctx;
+    Slot* fresh = nullptr;
+    LO_TRY(alloc_table(g, new_capacity, &fresh));
+    if (g->slots && g->capacity) {
+        grid_rebuild_kernel<<<blocks_for(g->capacity, 256), 256, 0, ctx->stream>>>(g->slots, g->capacity, fresh, new_capacity - 1);
+        LO_LAUNCHED(ctx);
+        LO_CUDA(cudaMemsetAsync(g->counters + GC_TOMBS, 0, sizeof(uint32_t), ctx->stream));
+        LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(g->slots);
+    }
+    g->slots = fresh;
+    g->capacity = new_capacity;
+    g->h_counters[GC_TOMBS] = 0;
+    return LO_OK;
+}
+
+int grid_refresh_counters(lo_grid* g) {
+    LO_CUDA(cudaMemcpyAsync(g->h_counters, g->counters, sizeof(g->h_counters), cudaMemcpyDeviceToHost, g->ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(g->ctx->stream));
+    return LO_OK;
+}
+
+// Make room for `incoming` more points (each may open a new voxel). Uses the host mirror of the counters,
+// which every mutating entry point refreshes, so no device synchronisation happens here unless we grow.
+int grid_reserve(lo_grid* g, size_t incoming) {
+    const uint64_t live = g->h_counters[GC_VOXELS], tombs = g->h_counters[GC_TOMBS];
+    const uint64_t need_slots = (live + tombs + incoming) * 2;
+    if (need_slots > g->capacity) {
+        const uint32_t cap = next_pow2(std::max<uint64_t>((live + incoming) * 4, 1024));
+        LO_TRY(rebuild_table(g, cap));
+    } else if (tombs > g->capacity / 8) {
+        LO_TRY(rebuild_table(g, g->capacity));
+    }
+    const int64_t free_top = static_cast<int32_t>(g->h_counters[GC_FREE_TOP]);
+    const uint64_t need_payload = g->h_counters[GC_BUMP] + incoming - static_cast<uint64_t>(std::max<int64_t>(free_top, 0) > static_cast<int64_t>(incoming) ? incoming : std::max<int64_t>(free_top, 0));
+    if (need_payload > g->payload_cap) {
+        const uint32_t cap = next_pow2(std::max<uint64_t>(need_payload * 2, 1024));
+        LO_TRY(grow_payload(g, cap));
+    }
+    return LO_OK;
+}
+
+int grid_add_dev(lo_grid* g, const void* d_points, size_t n, int has_normals, const Pose* d_pose, const uint32_t* d_n) {
+    if (n == 0) return LO_OK;
+    lo_ctx* ctx = g->ctx;
+    LO_TRY(grid_reserve(g, n));
+    LO_TRY(ctx->tmp_a.ensure(n * sizeof(uint32_t)));
+    LO_TRY(ctx->tmp_b.ensure(n * sizeof(uint32_t)));
+    PointSource src{static_cast<const float*>(d_points), has_normals ? 12u : 4u, has_normals};
+    const uint32_t nn = static_cast<uint32_t>(n);
+    const uint32_t ticket_base = g->h_counters[GC_TICKET];
+    const GridView v = g->view();
+    const unsigned blocks = blocks_for(n, 256);
+    grid_locate_kernel<<<blocks, 256, 0, ctx->stream>>>(src, nn, d_n, d_pose, v, g->counters, g->free_list, ctx->tmp_a.as<uint32_t>());
+    LO_LAUNCHED(ctx);
+    grid_chain_kernel<<<blocks, 256, 0, ctx->stream>>>(nn, d_n, ticket_base, v, ctx->tmp_a.as<uint32_t>(), ctx->tmp_b.as<uint32_t>());
+    LO_LAUNCHED(ctx);
+    grid_write_kernel<<<blocks, 256, 0, ctx->stream>>>(src, nn, d_n, ticket_base, d_pose, v, g->counters, ctx->tmp_a.as<uint32_t>(),
+                                                       ctx->tmp_b.as<uint32_t>());
+    LO_LAUNCHED(ctx);
+    grid_fix_counters_kernel<<<1, 1, 0, ctx->stream>>>(g->counters);
+    LO_LAUNCHED(ctx);
+    g->h_counters[GC_TICKET] = ticket_base + nn;
+    // conservative host-side bounds until the next refresh
+    g->h_counters[GC_VOXELS] += nn;
+    g->h_counters[GC_BUMP] += nn;
+    return LO_OK;
+}
+
+int grid_clear(lo_grid* g) {
+    lo_ctx* ctx = g->ctx;
+    if (g->capacity) LO_CUDA(cudaMemsetAsync(g->slots, 0xFF, static_cast<size_t>(g->capacity) * sizeof(Slot), ctx->stream));
+    // only the slabs that were ever handed out can hold tickets
+    const size_t used = static_cast<size_t>(std::min<uint64_t>(g->h_counters[GC_BUMP], g->payload_cap)) * g->width;
+    if (used) LO_CUDA(cudaMemsetAsync(g->points, 0xFF, used * sizeof(float4), ctx->stream));
+    LO_CUDA(cudaMemsetAsync(g->counters, 0, GC_COUNT * sizeof(uint32_t), ctx->stream));
+    for (auto& c : g->h_counters) c = 0;
+    g->cleaned = false;
+    return LO_OK;
+}
+
+int grid_cleanup_dev(lo_grid* g, const float* d_center3, float radius) {
+    if (!g->capacity) return LO_OK;
+    lo_ctx* ctx = g->ctx;
+    grid_cleanup_kernel<<<blocks_for(g->capacity, 256), 256, 0, ctx->stream>>>(g->view(), g->capacity, d_center3, radius, g->counters,
+                                                                               g->free_list);
+    LO_LAUNCHED(ctx);
+    g->cleaned = true;
+    return LO_OK;
+}
+
+int grid_export_dev(lo_grid* g, int mode, void* d_out, uint32_t* d_count) {
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaMemsetAsync(d_count, 0, sizeof(uint32_t), ctx->stream));
+    if (!g->capacity) return LO_OK;
+    grid_export_kernel<<<blocks_for(g->capacity, 256), 256, 0, ctx->stream>>>(g->view(), g->capacity, mode, d_out, d_count);
+    LO_LAUNCHED(ctx);
+    return LO_OK;
+}
+
+}  // namespace lo
+
+using namespace lo;
+
+extern "C" int lo_grid_create(lo_ctx* ctx, float voxel_size, size_t max_points, size_t capacity_hint, lo_grid** out) {
+    if (!ctx || !out || !(voxel_size > 0.f)) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    lo_grid* g = new lo_grid();
+    g->ctx = ctx;
+    g->voxel_size = voxel_size;
+    g->max_points = max_points;
+    g->width = static_cast<uint32_t>(max_points ? max_points : 1);
+    LO_CUDA(cudaMalloc(&g->counters, GC_COUNT * sizeof(uint32_t)));
+    LO_CUDA(cudaMemsetAsync(g->counters, 0, GC_COUNT * sizeof(uint32_t), ctx->stream));
+    const uint64_t hint = capacity_hint ? capacity_hint : 4096;
+    int st = rebuild_table(g, next_pow2(std::max<uint64_t>(hint * 2, 1024)));
+    if (st == LO_OK) st = grow_payload(g, next_pow2(std::max<uint64_t>(hint, 1024)));
+    if (st != LO_OK) {
+        lo_grid_destroy(g);
+        return st;
+    }
+    *out = g;
+    return LO_OK;
+}
+
+extern "C" void lo_grid_destroy(lo_grid* g) {
+    if (!g) return;
+    cudaSetDevice(g->ctx->device);
+    cudaStreamSynchronize(g->ctx->stream);
+    if (g->slots) cudaFree(g->slots);
+    if (g->points) cudaFree(g->points);
+    if (g->normals) cudaFree(g->normals);
+    if (g->free_list) cudaFree(g->free_list);
+    if (g->counters) cudaFree(g->counters);
+    delete g;
+}
+
+extern "C" int lo_grid_set_voxel_size(lo_grid* g, float voxel_size) {
+    if (!g || !(voxel_size > 0.f)) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(g->ctx->device));
+    LO_TRY(grid_clear(g));
+    g->voxel_size = voxel_size;
+    LO_CUDA(cudaStreamSynchronize(g->ctx->stream));
+    return LO_OK;
+}
+
+extern "C" int lo_grid_size(lo_grid* g, size_t* n_voxels, size_t* n_points) {
+    if (!g) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(g->ctx->device));
+    LO_TRY(grid_refresh_counters(g));
+    if (n_voxels) *n_voxels = g->h_counters[GC_VOXELS];
+    if (n_points) *n_points = g->h_counters[GC_POINTS];
+    return LO_OK;
+}
+
+static int finish_mutation(lo_grid* g) {
+    LO_TRY(grid_refresh_counters(g));
+    if (g->h_counters[GC_RANGE_ERR]) {
+        set_error("a point was not finite or its voxel index fell outside +-2^20; it was skipped");
+        LO_CUDA(cudaMemsetAsync(g->counters + GC_RANGE_ERR, 0, sizeof(uint32_t), g->ctx->stream));
+        return LO_E_RANGE;
+    }
+    return LO_OK;
+}
+
+extern "C" int lo_grid_add_cloud_dev(lo_grid* g, const void* d_points, size_t n, int has_normals) {
+    if (!g || (!d_points && n)) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(g->ctx->device));
+    LO_TRY(grid_add_dev(g, d_points, n, has_normals, nullptr, nullptr));
+    return finish_mutation(g);
+}
+
+extern "C" int lo_grid_add_cloud(lo_grid* g, const void* points, size_t n, int has_normals) {
+    if (!g || (!points && n)) return LO_E_ARG;
+    if (n == 0) return LO_OK;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const size_t bytes = n * (has_normals ? sizeof(PointNormal) : sizeof(PointXYZ));
+    LO_TRY(ctx->in_a.ensure(bytes));
+    LO_CUDA(cudaMemcpyAsync(ctx->in_a.p, points, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    LO_TRY(grid_add_dev(g, ctx->in_a.p, n, has_normals, nullptr, nullptr));
+    return finish_mutation(g);
+}
+
+extern "C" int lo_grid_radius_cleanup(lo_grid* g, const float center[3], float radius) {
+    if (!g || !center) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    float* d_c = ctx->small.as<float>();
+    LO_CUDA(cudaMemcpyAsync(d_c, center, 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    LO_TRY(grid_cleanup_dev(g, d_c, radius));
+    return finish_mutation(g);
+}
+
+extern "C" int lo_grid_get_cloud(lo_grid* g, int mode, int order, void* out, size_t cap, size_t* n) {
+    if (!g || mode < 0 || mode > 2 || !n) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    LO_TRY(grid_refresh_counters(g));
+    const size_t total = (mode == 2) ? g->h_counters[GC_VOXELS] : g->h_counters[GC_POINTS];
+    *n = total;
+    if (!out) return LO_OK;
+    if (cap < total) return LO_E_CAPACITY;
+    if (total == 0) return LO_OK;
+    if (order == 1 && g->cleaned) {
+        set_error("reference iteration order is only emulated for grids without radius_cleanup");
+        return LO_E_ARG;
+    }
+    const size_t rec = (mode == 0) ? sizeof(PointNormal) : sizeof(PointXYZ);
+    LO_TRY(ctx->out_a.ensure(total * rec));
+    uint32_t* d_count = ctx->small.as<uint32_t>() + 64;
+    if (order == 1) LO_TRY(robin_export_dev(g, mode, ctx->out_a.p, d_count));
+    else LO_TRY(grid_export_dev(g, mode, ctx->out_a.p, d_count));
+    LO_CUDA(cudaMemcpyAsync(out, ctx->out_a.p, total * rec, cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return LO_OK;
+}

@@ -1,0 +1,516 @@
+// K4/K5/K6 kernels and their C-ABI entry points:
+//   find_pairs_kernel      VoxelGrid::findMatchingPairs with the query index kept (parity dumps)
+//   nn_residual_kernel     the fused metric kernel: 27-neighbour search + residual/Jacobian/Huber weight +
+//                          warp-shuffle / shared-memory reduction of the 6x6 normal equations
+//   align_kernel           CloudMatcher::align as ONE persistent cooperative kernel: up to 35 outer
+//                          iterations x (search + evaluate, <= 4 LM iterations) with grid-wide barriers and
+//                          no host round trip until the final pose
+#include <cooperative_groups.h>
+
+#include <algorithm>
+#include <cstring>
+
+#include "lo_host.h"
+#include "lo_lm.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace lo {
+
+// ---------------------------------------------------------------------------------------------------
+// shared accumulation helpers. `row` points at this warp's kAcc doubles in shared memory.
+struct Terms {
+    double j[6];
+    double rc;     // corrected residual
+    double cost;   // 0.5 * rho(s)
+};
+
+__device__ inline Terms pair_terms(const EvalPoint& ep, const float pf[3], const float of[3], const float nf[3]) {
+    Terms t;
+    const double p[3] = {pf[0], pf[1], pf[2]}, o[3] = {of[0], of[1], of[2]}, n[3] = {nf[0], nf[1], nf[2]};
+    const double w = ep.q[0], x = ep.q[1], y = ep.q[2], z = ep.q[3];
+    double uv[3] = {y * p[2] - z * p[1], z * p[0] - x * p[2], x * p[1] - y * p[0]};
+    uv[0] += uv[0]; uv[1] += uv[1]; uv[2] += uv[2];
+    const double c[3] = {y * uv[2] - z * uv[1], z * uv[0] - x * uv[2], x * uv[1] - y * uv[0]};
+    double d[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) d[i] = (((p[i] + w * uv[i]) + c[i]) + ep.t[i]) - o[i];
+    const double r = dot3d(d, n);
+    const double s = r * r;
+    const double a = 0.15, b = a * a;
+    double rho0, rho1;
+    if (s > b) {
+        const double rr = sqrt(s);
+        rho0 = 2.0 * a * rr - b;
+        rho1 = fmax(2.2250738585072014e-308, a / rr);
+    } else {
+        rho0 = s;
+        rho1 = 1.0;
+    }
+    t.cost = 0.5 * rho0;
+    const double sc = sqrt(rho1);
+    const double q0 = w, q1 = x, q2 = y, q3 = z;
+    const double mk[4][9] = {{q0, -q3, q2, q3, q0, -q1, -q2, q1, q0},
+                             {q1, q2, q3, q2, -q1, -q0, q3, q0, -q1},
+                             {-q2, q1, q0, q1, q2, q3, -q0, q3, -q2},
+                             {-q3, -q0, q1, q0, -q3, q2, q1, q2, q3}};
+    double jq[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        double v[3];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+            v[i] = ((2.0 * mk[k][3 * i]) * p[0] + (2.0 * mk[k][3 * i + 1]) * p[1]) + (2.0 * mk[k][3 * i + 2]) * p[2];
+        jq[k] = dot3d(v, n);
+    }
+#pragma unroll
+    for (int col = 0; col < 3; col++) {
+        double v = 0.0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) v += jq[k] * ep.pj[k][col];
+        t.j[col] = sc * v;
+    }
+#pragma unroll
+    for (int col = 0; col < 3; col++) t.j[3 + col] = sc * n[col];
+    t.rc = sc * r;
+    return t;
+}
+
+// one lane adds one pair (no shuffles)
+__device__ inline void accumulate_lane(double* row, const Terms& t) {
+    int at = 0;
+#pragma unroll
+    for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int b = a; b < 6; b++) row[at++] += t.j[a] * t.j[b];
+#pragma unroll
+    for (int a = 0; a < 6; a++) row[21 + a] += t.j[a] * t.rc;
+    row[27] += t.cost;
+    row[28] += 1.0;
+}
+
+__device__ inline double warp_sum(double v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(kFullMask, v, off);
+    return v;
+}
+
+// all 32 lanes hold (at most) one pair each; products are reduced by shuffles one value at a time so that
+// only j[6], rc and one temporary are live (keeps the kernel under 64 registers)
+__device__ inline void accumulate_warp(double* row, const Terms& t, bool valid, int lane) {
+    const double m = valid ? 1.0 : 0.0;
+    int at = 0;
+#pragma unroll
+    for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int b = a; b < 6; b++) {
+            const double v = warp_sum(m * (t.j[a] * t.j[b]));
+            if (lane == 0) row[at] += v;
+            at++;
+        }
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+        const double v = warp_sum(m * (t.j[a] * t.rc));
+        if (lane == 0) row[21 + a] += v;
+    }
+    const double c = warp_sum(m * t.cost);
+    const double k = warp_sum(m);
+    if (lane == 0) {
+        row[27] += c;
+        row[28] += k;
+    }
+}
+
+// sum the per-warp rows of a block into out[kAcc] (global); rows are zeroed for the next pass
+__device__ inline void block_rows_to_global(double* rows, double* out) {
+    __syncthreads();
+    const int nwarps = blockDim.x >> 5;
+    if (threadIdx.x < kAcc) {
+        double v = 0.0;
+        for (int w = 0; w < nwarps; w++) {
+            v += rows[w * kAcc + threadIdx.x];
+            rows[w * kAcc + threadIdx.x] = 0.0;
+        }
+        out[threadIdx.x] = v;
+    }
+    __syncthreads();
+}
+
+// every block sums the per-block partials [nblocks][32] into total[kAcc] (shared), in a fixed order
+__device__ inline void reduce_partials(const double* partials, int nblocks, double* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (int c = warp; c < kAcc; c += nwarps) {
+        double v = 0.0;
+        for (int b = lane; b < nblocks; b += 32) v += __ldcg(partials + b * 32 + c);
+        v = warp_sum(v);
+        if (lane == 0) total[c] = v;
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------------
+__global__ void find_pairs_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m, QueryTransform tf, float max_d2,
+                                  lo_pair* __restrict__ pairs, uint8_t* __restrict__ valid, uint32_t* __restrict__ n_valid) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= m) return;
+    const PointXYZ q = queries[warp];
+    float wq[3];
+    transform_query(tf, q.x, q.y, q.z, wq);
+    const Found f = nn_search_warp(g, wq, max_d2, lane);
+    if (lane == 0) {
+        lo_pair out;
+        memset(&out, 0, sizeof(out));
+        if (f.valid) {
+            out.source_point_local[0] = q.x; out.source_point_local[1] = q.y; out.source_point_local[2] = q.z;
+            for (int k = 0; k < 3; k++) {
+                out.plane_origin[k] = f.o[k];
+                out.plane_normal[k] = f.n[k];
+            }
+            atomicAdd(n_valid, 1u);
+        }
+        pairs[warp] = out;
+        valid[warp] = f.valid ? 1 : 0;
+    }
+}
+
+// Fused NN + residual. Each warp walks tiles of 32 consecutive queries: the 27-lane search runs once per
+// query, lane j keeps the correspondence of query j, then all 32 lanes evaluate their residual/Jacobian in
+// parallel and the warp reduces the 28 sums by shuffles into its shared-memory row.
+constexpr int kNnThreads = 256;
+__global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+                                                                  QueryTransform tf, EvalPoint ep, float max_d2,
+                                                                  double* __restrict__ partials) {
+    __shared__ double rows[(kNnThreads / 32) * kAcc];
+    const int lane = threadIdx.x & 31, warp_in_block = threadIdx.x >> 5;
+    for (int k = threadIdx.x; k < (kNnThreads / 32) * kAcc; k += blockDim.x) rows[k] = 0.0;
+    __syncthreads();
+    double* row = rows + warp_in_block * kAcc;
+    const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t tiles = (m + 31) / 32;
+    for (uint32_t tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; tile < tiles; tile += total_warps) {
+        const uint32_t base = tile * 32;
+        const uint32_t mine = base + lane;
+        PointXYZ q{0.f, 0.f, 0.f, 0.f};
+        if (mine < m) q = queries[mine];  // coalesced 16 B loads
+        bool my_valid = false;
+        float my_o[3] = {0.f, 0.f, 0.f}, my_n[3] = {0.f, 0.f, 0.f};
+        const uint32_t in_tile = min(32u, m - base);
+        for (uint32_t j = 0; j < in_tile; j++) {
+            const float qx = __shfl_sync(kFullMask, q.x, j), qy = __shfl_sync(kFullMask, q.y, j), qz = __shfl_sync(kFullMask, q.z, j);
+            float wq[3];
+            transform_query(tf, qx, qy, qz, wq);
+            const Found f = nn_search_warp(g, wq, max_d2, lane);
+            if (lane == static_cast<int>(j)) {
+                my_valid = f.valid;
+                for (int k = 0; k < 3; k++) {
+                    my_o[k] = f.o[k];
+                    my_n[k] = f.n[k];
+                }
+            }
+        }
+        const float pf[3] = {q.x, q.y, q.z};
+        const Terms t = pair_terms(ep, pf, my_o, my_n);
+        accumulate_warp(row, t, my_valid, lane);
+    }
+    block_rows_to_global(rows, partials + blockIdx.x * 32);
+}
+
+// final reduction of nn_residual_kernel's partials + the prior, by one block
+__global__ void normal_eq_finalize_kernel(const double* __restrict__ partials, int nblocks, EvalPoint ep, double b0, double b1, double b2,
+                                          lo_normal_eq* __restrict__ out) {
+    __shared__ double total[32];
+    reduce_partials(partials, nblocks, total);
+    if (threadIdx.x == 0) {
+        double acc[kAcc];
+        for (int k = 0; k < kAcc; k++) acc[k] = total[k];
+        const double b[3] = {b0, b1, b2};
+        add_prior(acc, ep.t, b);
+        out->cost = acc[27];
+        for (int a = 0; a < 6; a++) {
+            out->g[a] = acc[21 + a];
+            for (int c = 0; c < 6; c++) out->jtj[a * 6 + c] = sym(acc, a, c);
+        }
+        out->n_valid = static_cast<uint64_t>(acc[28] + 0.5);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// CloudMatcher::align (src/cloud_matcher.cpp:105-178) as one persistent cooperative kernel.
+constexpr int kAlignThreads = 512;
+
+struct AlignArgs {
+    GridView g;
+    const PointXYZ* queries;
+    uint32_t m;
+    const uint32_t* m_dev; // nullable: actual query count on the device (m is then an upper bound)
+    float4* pair_o;        // [m] plane_origin, w = 1 if the query has a correspondence
+    float4* pair_n;        // [m] plane_normal
+    double* partials;      // [2][gridDim.x][32]
+    const float* guess;    // device pose7
+    float* out_pose;       // device pose7
+    lo_align_stats* stats; // device, nullable
+    float max_dist;
+};
+
+__global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    if (a.m_dev) a.m = min(a.m, *a.m_dev);
+    __shared__ double rows[(kAlignThreads / 32) * kAcc];
+    __shared__ double total[32];
+    __shared__ LmState lm;
+    __shared__ EvalPoint ep_s;
+    __shared__ float pose_s[7];
+    __shared__ int flag_s;
+
+    const int lane = threadIdx.x & 31;
+    const uint32_t gthread = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t gwarp = gthread >> 5;
+    const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+    const int nblocks = gridDim.x;
+    double* row = rows + (threadIdx.x >> 5) * kAcc;
+    for (int k = threadIdx.x; k < (kAlignThreads / 32) * kAcc; k += blockDim.x) rows[k] = 0.0;
+    if (threadIdx.x < 7) pose_s[threadIdx.x] = a.guess[threadIdx.x];
+    __syncthreads();
+    const double prior_b[3] = {static_cast<double>(a.guess[0]), static_cast<double>(a.guess[1]), static_cast<double>(a.guess[2])};
+    const float max_d2 = a.max_dist * a.max_dist;  // voxel_grid.h:215
+    int buf = 0;
+    int lm_total = 0;
+    bool cont = false;  // meaningful in thread 0 only
+
+    for (int outer = 0; outer < 35; outer++) {  // cloud_matcher.cpp:117
+        // ---- correspondences at the current (float) pose + evaluation at x0 = double(pose) ----
+        Pose pf;
+        pf.t[0] = pose_s[0]; pf.t[1] = pose_s[1]; pf.t[2] = pose_s[2];
+        pf.w = pose_s[3]; pf.x = pose_s[4]; pf.y = pose_s[5]; pf.z = pose_s[6];
+        const QueryTransform tf = make_query_transform(pf);
+        double x0[7] = {pf.w, pf.x, pf.y, pf.z, pf.t[0], pf.t[1], pf.t[2]};  // cloud_matcher.cpp:122-131
+        const EvalPoint ep0 = make_eval_point(x0);
+        for (uint32_t qi = gwarp; qi < a.m; qi += total_warps) {
+            const PointXYZ q = a.queries[qi];
+            float wq[3];
+            transform_query(tf, q.x, q.y, q.z, wq);
+            const Found f = nn_search_warp(a.g, wq, max_d2, lane);
+            if (lane == 0) {
+                a.pair_o[qi] = make_float4(f.o[0], f.o[1], f.o[2], f.valid ? 1.f : 0.f);
+                a.pair_n[qi] = make_float4(f.n[0], f.n[1], f.n[2], 0.f);
+                if (f.valid) {
+                    const float pq[3] = {q.x, q.y, q.z};
+                    accumulate_lane(row, pair_terms(ep0, pq, f.o, f.n));
+                }
+            }
+        }
+        block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
+        grid.sync();
+        reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, total);
+        buf ^= 1;
+        if (threadIdx.x == 0) {
+            double acc[kAcc];
+            for (int k = 0; k < kAcc; k++) acc[k] = total[k];
+            add_prior(acc, ep0.t, prior_b);
+            cont = lm_begin(lm, x0, acc);
+            if (a.stats && blockIdx.x == 0) {
+                a.stats->pairs_log[outer] = static_cast<int32_t>(total[28] + 0.5);
+                a.stats->valid_pairs = static_cast<int32_t>(total[28] + 0.5);
+            }
+        }
+        // ---- ceres::Solve: at most 4 LM iterations on the fixed correspondences ----
+        while (true) {
+            if (threadIdx.x == 0) {
+                const bool need_eval = cont && lm_propose(lm);
+                flag_s = need_eval ? 1 : 0;
+                if (need_eval) ep_s = make_eval_point(lm.cand);
+            }
+            __syncthreads();
+            if (!flag_s) break;
+            for (uint32_t base = gwarp * 32; base < a.m; base += total_warps * 32) {
+                const uint32_t i = base + lane;
+                bool valid = false;
+                Terms t;
+                if (i < a.m) {
+                    const float4 o = __ldcg(a.pair_o + i);
+                    valid = o.w != 0.f;
+                    if (valid) {
+                        const float4 nv = __ldcg(a.pair_n + i);
+                        const PointXYZ q = a.queries[i];
+                        const float pq[3] = {q.x, q.y, q.z}, of[3] = {o.x, o.y, o.z}, nf[3] = {nv.x, nv.y, nv.z};
+                        t = pair_terms(ep_s, pq, of, nf);
+                    }
+                }
+                if (!valid) {
+                    for (int k = 0; k < 6; k++) t.j[k] = 0.0;
+                    t.rc = 0.0;
+                    t.cost = 0.0;
+                }
+                accumulate_warp(row, t, valid, lane);
+            }
+            block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
+            grid.sync();
+            reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, total);
+            buf ^= 1;
+            if (threadIdx.x == 0) {
+                double acc[kAcc];
+                for (int k = 0; k < kAcc; k++) acc[k] = total[k];
+                add_prior(acc, ep_s.t, prior_b);
+                cont = lm_update(lm, acc);
+            }
+        }
+        // ---- float round trip of the pose (cloud_matcher.cpp:161-167) and the outer stop rule (:169) ----
+        if (threadIdx.x == 0) {
+            pose_s[3] = static_cast<float>(lm.x[0]); pose_s[4] = static_cast<float>(lm.x[1]);
+            pose_s[5] = static_cast<float>(lm.x[2]); pose_s[6] = static_cast<float>(lm.x[3]);
+            pose_s[0] = static_cast<float>(lm.x[4]); pose_s[1] = static_cast<float>(lm.x[5]); pose_s[2] = static_cast<float>(lm.x[6]);
+            lm_total += lm.recorded;
+            flag_s = (lm.last_step_norm < 1e-4 && outer > 3) ? 1 : 0;
+            if (a.stats && blockIdx.x == 0) {
+                for (int k = 0; k < 7; k++) a.stats->pose_log[outer][k] = pose_s[k];
+                a.stats->outer_iterations = outer + 1;
+                a.stats->lm_iterations = lm_total;
+                a.stats->termination = lm.termination;
+                a.stats->final_cost = lm.x_cost;
+                a.stats->last_step_norm = lm.last_step_norm;
+            }
+        }
+        __syncthreads();
+        if (flag_s) break;
+        __syncthreads();  // flag_s is rewritten by thread 0 at the top of the next solve
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {  // cloud_matcher.cpp:175 Quaternionf::normalize()
+        const float w = pose_s[3], x = pose_s[4], y = pose_s[5], z = pose_s[6];
+        const float nrm = sqrtf((x * x + z * z) + (y * y + w * w));
+        a.out_pose[0] = pose_s[0]; a.out_pose[1] = pose_s[1]; a.out_pose[2] = pose_s[2];
+        a.out_pose[3] = w / nrm; a.out_pose[4] = x / nrm; a.out_pose[5] = y / nrm; a.out_pose[6] = z / nrm;
+    }
+}
+
+// enqueue align on the context's stream; every pointer is a device pointer
+int align_enqueue(lo_grid* kf, const PointXYZ* d_queries, uint32_t m, const uint32_t* d_m, const float* d_guess7, float* d_out7,
+                  lo_align_stats* d_stats) {
+    lo_ctx* ctx = kf->ctx;
+    if (ctx->align_blocks == 0) {
+        int per_sm = 0;
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, align_kernel, kAlignThreads, 0));
+        if (per_sm < 1) {
+            set_error("align kernel does not fit on an SM");
+            return LO_E_CUDA;
+        }
+        ctx->align_blocks = per_sm * ctx->sm_count;
+    }
+    // do not spin up more blocks than there is work for: one warp per query in the search phase
+    int blocks = ctx->align_blocks;
+    const int wanted = static_cast<int>((static_cast<uint64_t>(m) * 32 + kAlignThreads - 1) / kAlignThreads);
+    blocks = std::max(1, std::min(blocks, wanted));
+    LO_TRY(ctx->tmp_a.ensure(std::max<size_t>(m, 1) * sizeof(float4)));
+    LO_TRY(ctx->tmp_b.ensure(std::max<size_t>(m, 1) * sizeof(float4)));
+    LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(2) * ctx->align_blocks * 32 * sizeof(double)));
+    AlignArgs args;
+    args.g = kf->view();
+    args.queries = d_queries;
+    args.m = m;
+    args.m_dev = d_m;
+    args.pair_o = ctx->tmp_a.as<float4>();
+    args.pair_n = ctx->tmp_b.as<float4>();
+    args.partials = ctx->tmp_c.as<double>();
+    args.guess = d_guess7;
+    args.out_pose = d_out7;
+    args.stats = d_stats;
+    args.max_dist = 0.3f;  // cloud_matcher.cpp:139
+    void* kargs[] = {&args};
+    LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(align_kernel), dim3(blocks), dim3(kAlignThreads), kargs, 0, ctx->stream));
+    ctx->launches++;
+    return LO_OK;
+}
+
+}  // namespace lo
+
+using namespace lo;
+
+static int stage_queries(lo_ctx* ctx, const float* xyz16, size_t m) {
+    LO_TRY(ctx->in_a.ensure(std::max<size_t>(m, 1) * sizeof(PointXYZ)));
+    if (m) LO_CUDA(cudaMemcpyAsync(ctx->in_a.p, xyz16, m * sizeof(PointXYZ), cudaMemcpyHostToDevice, ctx->stream));
+    return LO_OK;
+}
+
+extern "C" int lo_grid_find_matching_pairs(lo_grid* g, const float* xyz16, size_t m, const float pose7[7], float max_dist,
+                                           lo_pair* pairs, uint8_t* valid, size_t* n_valid) {
+    if (!g || (!xyz16 && m) || !pose7 || !pairs || !valid) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    if (n_valid) *n_valid = 0;
+    if (m == 0) return LO_OK;
+    LO_TRY(stage_queries(ctx, xyz16, m));
+    LO_TRY(ctx->out_a.ensure(m * sizeof(lo_pair)));
+    LO_TRY(ctx->out_b.ensure(m));
+    uint32_t* d_n = ctx->small.as<uint32_t>();
+    LO_CUDA(cudaMemsetAsync(d_n, 0, sizeof(uint32_t), ctx->stream));
+    const QueryTransform tf = make_query_transform(pose_from7(pose7));
+    const float max_d2 = max_dist * max_dist;
+    find_pairs_kernel<<<blocks_for(m * 32, 256), 256, 0, ctx->stream>>>(g->view(), ctx->in_a.as<PointXYZ>(), static_cast<uint32_t>(m), tf,
+                                                                        max_d2, ctx->out_a.as<lo_pair>(), ctx->out_b.as<uint8_t>(), d_n);
+    LO_LAUNCHED(ctx);
+    uint32_t h_n = 0;
+    LO_CUDA(cudaMemcpyAsync(pairs, ctx->out_a.p, m * sizeof(lo_pair), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(valid, ctx->out_b.p, m, cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(&h_n, d_n, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (n_valid) *n_valid = h_n;
+    return LO_OK;
+}
+
+extern "C" int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], const double x7d[7],
+                                  const double prior_b[3], float max_dist, lo_normal_eq* out) {
+    if (!g || (!d_xyz16 && m) || !pose7 || !x7d || !prior_b) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const QueryTransform tf = make_query_transform(pose_from7(pose7));
+    const EvalPoint ep = make_eval_point(x7d);
+    const uint32_t tiles = static_cast<uint32_t>((m + 31) / 32);
+    // one tile per warp, capped at a few waves of the machine; the kernel grid-strides beyond that
+    const int max_blocks = ctx->sm_count * 8 * 4;
+    const int blocks = std::max(1, std::min<int>(max_blocks, static_cast<int>((tiles + kNnThreads / 32 - 1) / (kNnThreads / 32))));
+    LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(blocks) * 32 * sizeof(double)));
+    lo_normal_eq* d_out = reinterpret_cast<lo_normal_eq*>(ctx->small.as<char>() + 1024);
+    nn_residual_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m), tf,
+                                                               ep, max_dist * max_dist, ctx->tmp_c.as<double>());
+    LO_LAUNCHED(ctx);
+    normal_eq_finalize_kernel<<<1, 256, 0, ctx->stream>>>(ctx->tmp_c.as<double>(), blocks, ep, prior_b[0], prior_b[1], prior_b[2], d_out);
+    LO_LAUNCHED(ctx);
+    if (out) {
+        LO_CUDA(cudaMemcpyAsync(out, d_out, sizeof(lo_normal_eq), cudaMemcpyDeviceToHost, ctx->stream));
+        LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return LO_OK;
+}
+
+extern "C" int lo_nn_residual(lo_grid* g, const float* xyz16, size_t m, const float pose7[7], const double x7d[7],
+                              const double prior_b[3], float max_dist, lo_normal_eq* out) {
+    if (!g || (!xyz16 && m) || !out) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    LO_TRY(stage_queries(ctx, xyz16, m));
+    return lo_nn_residual_dev(g, ctx->in_a.p, m, pose7, x7d, prior_b, max_dist, out);
+}
+
+extern "C" int lo_align_dev(lo_grid* kf, const void* d_xyz16, size_t m, const float guess7[7], float out7[7], lo_align_stats* stats) {
+    if (!kf || (!d_xyz16 && m) || !guess7 || !out7) return LO_E_ARG;
+    lo_ctx* ctx = kf->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    float* d_guess = ctx->small.as<float>() + 16;
+    float* d_out = ctx->small.as<float>() + 32;
+    lo_align_stats* d_stats = reinterpret_cast<lo_align_stats*>(ctx->small.as<char>() + 4096);
+    LO_CUDA(cudaMemcpyAsync(d_guess, guess7, 7 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    if (stats) LO_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(lo_align_stats), ctx->stream));
+    LO_TRY(align_enqueue(kf, static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m), nullptr, d_guess, d_out, stats ? d_stats : nullptr));
+    LO_CUDA(cudaMemcpyAsync(out7, d_out, 7 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (stats) LO_CUDA(cudaMemcpyAsync(stats, d_stats, sizeof(lo_align_stats), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return LO_OK;
+}
+
+extern "C" int lo_align(lo_grid* kf, const float* xyz16, size_t m, const float guess7[7], float out7[7], lo_align_stats* stats) {
+    if (!kf || (!xyz16 && m)) return LO_E_ARG;
+    lo_ctx* ctx = kf->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    LO_TRY(stage_queries(ctx, xyz16, m));
+    return lo_align_dev(kf, ctx->in_a.p, m, guess7, out7, stats);
+}

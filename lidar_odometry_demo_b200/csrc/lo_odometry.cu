@@ -1,0 +1,308 @@
+// LidarOdometry::processCloud (src/lidar_odometry.cpp:22-76) as a device-resident pipeline: every stage is
+// enqueued on the context's stream, poses and counts stay in device memory, and the host synchronises once
+// per scan to read back the pose and the per-scan counters (28 + 64 bytes).
+#include <algorithm>
+#include <cstring>
+
+#include "lo_points.cuh"
+
+namespace lo {
+
+struct OdomDev {          // device-resident state of one LidarOdometry
+    Pose previous;        // previous_transform_  (lidar_odometry.h:84)
+    Pose current;         // current_transform_   (lidar_odometry.h:85)
+    Pose relative, relative_inv, guess, next, identity;
+    float center[4];      // current translation for radiusCleanup
+    uint32_t n_planar, n_update, n_query, unstable;
+    uint32_t pad[4];
+    lo_align_stats align;
+};
+
+__device__ inline Pose identity_pose() {
+    Pose p;
+    p.t[0] = p.t[1] = p.t[2] = 0.f;
+    p.w = 1.f; p.x = p.y = p.z = 0.f;
+    return p;
+}
+
+__global__ void odom_init_kernel(OdomDev* s) {
+    s->previous = identity_pose();
+    s->current = identity_pose();
+    s->identity = identity_pose();
+    s->n_planar = s->n_update = s->n_query = s->unstable = 0;
+}
+
+// lidar_odometry.cpp:27-30,51: relative = previous.relativeTo(current); previous = current;
+// deskew start pose = relative.inverse(); guess = current.compose(relative)
+__global__ void odom_predict_kernel(OdomDev* s) {
+    const Pose rel = pose_relative_to(s->previous, s->current);
+    s->previous = s->current;
+    s->relative = rel;
+    s->relative_inv = pose_inverse(rel);
+    s->guess = pose_compose(s->current, rel);
+    s->unstable = 0;
+    s->n_query = 0;
+    s->align.outer_iterations = 0;
+}
+
+__device__ inline float as_float(double v) { return static_cast<float>(v); }
+
+// lidar_odometry.cpp:53-65: Euler-angle divergence gate, then current = new
+__global__ void odom_gate_kernel(OdomDev* s, float threshold) {
+    const Pose nw = s->next, cur = s->current;
+    // new.rotation * current.rotation.inverse()
+    Pose a = identity_pose(), b = identity_pose();
+    a.w = nw.w; a.x = nw.x; a.y = nw.y; a.z = nw.z;
+    b.w = cur.w; b.x = cur.x; b.y = cur.y; b.z = cur.z;
+    const Pose d = pose_compose(a, pose_inverse(b));
+    float r[9];
+    rotation_matrix_f(d.w, d.x, d.y, d.z, r);
+    // Matrix3f::eulerAngles(0,1,2) (Eigen 3.4); libm float functions evaluated in double and rounded once
+    const float pi_f = 3.14159265358979323846f;
+    float e0 = as_float(atan2(static_cast<double>(r[5]), static_cast<double>(r[8])));
+    const float c2 = sqrtf(r[0] * r[0] + r[1] * r[1]);
+    float e1;
+    if (e0 > 0.f) {
+        e0 -= pi_f;
+        e1 = as_float(atan2(static_cast<double>(-r[2]), static_cast<double>(-c2)));
+    } else {
+        e1 = as_float(atan2(static_cast<double>(-r[2]), static_cast<double>(c2)));
+    }
+    const float s1 = as_float(sin(static_cast<double>(e0))), c1 = as_float(cos(static_cast<double>(e0)));
+    const float e2 = as_float(atan2(static_cast<double>(s1 * r[6] - c1 * r[3]), static_cast<double>(c1 * r[4] - s1 * r[7])));
+    const float ang[3] = {-e0, -e1, -e2};
+    bool ok = true;
+    for (int k = 0; k < 3; k++) {
+        const float deg = (ang[k] * 180.0f) / pi_f;
+        const float m = fabsf(deg);
+        ok = ok && (m < threshold || m > 180 - threshold);
+    }
+    Pose out = nw;
+    if (!ok) {
+        out = s->guess;
+        s->unstable = 1;
+    }
+    s->current = out;
+    s->center[0] = out.t[0]; s->center[1] = out.t[1]; s->center[2] = out.t[2];
+}
+
+struct ScanReadback {   // one D2H per scan
+    float pose[7];
+    uint32_t n_planar, n_update, n_query, unstable;
+    int32_t outer_iterations;
+    uint32_t kf_counters[GC_COUNT];
+};
+
+__global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counters, ScanReadback* out) {
+    pose_to7(s->current, out->pose);
+    out->n_planar = s->n_planar;
+    out->n_update = s->n_update;
+    out->n_query = s->n_query;
+    out->unstable = s->unstable;
+    out->outer_iterations = s->align.outer_iterations;
+    for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = kf_counters[k];
+}
+
+}  // namespace lo
+
+using namespace lo;
+
+struct lo_odometry {
+    lo_ctx* ctx = nullptr;
+    lo_params params;
+    lo_grid* keyframe = nullptr;
+    lo_grid* update_ds = nullptr;    // VoxelGrid(keyframe_update_voxel_size, 1)   lidar_odometry.cpp:37
+    lo_grid* match_ds = nullptr;     // VoxelGrid(keyframe_matching_voxel_size, 1) lidar_odometry.cpp:46
+    OdomDev* d_state = nullptr;
+    ScanReadback* d_readback = nullptr;
+    ScanReadback* h_readback = nullptr;  // pinned
+    DevBuf scan, deskewed, filtered, update, query;
+    uint32_t n_last = 0;             // points in the deskewed cloud
+    lo_scan_stats stats;
+    float pose[7] = {0, 0, 0, 1, 0, 0, 0};
+};
+
+static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P) {
+    lo_ctx* ctx = h->ctx;
+    OdomDev* s = h->d_state;
+    LO_TRY(h->update.ensure(std::max<size_t>(bound, 1) * sizeof(PointNormal)));
+    LO_TRY(h->query.ensure(std::max<size_t>(bound, 1) * sizeof(PointXYZ)));
+    // keyframe_downsampler (cpp:37-38) and its getCloud() in the reference's iteration order
+    LO_TRY(grid_clear(h->update_ds));
+    LO_TRY(grid_add_dev(h->update_ds, h->filtered.p, bound, 1, nullptr, d_P));
+    LO_TRY(robin_export_bounded(h->update_ds, 0, h->update.p, &s->n_update, bound));
+    const bool first = h->keyframe->h_counters[GC_VOXELS] == 0;  // cpp:40 (host mirror from the last scan's readback)
+    if (first) {
+        LO_TRY(grid_add_dev(h->keyframe, h->update.p, bound, 1, nullptr, &s->n_update));  // cpp:42
+        return LO_OK;
+    }
+    // matching_downsampler (cpp:46-47) and getCloudWithoutNormals()
+    LO_TRY(grid_clear(h->match_ds));
+    LO_TRY(grid_add_dev(h->match_ds, h->filtered.p, bound, 1, nullptr, d_P));
+    LO_TRY(robin_export_bounded(h->match_ds, 1, h->query.p, &s->n_query, bound));
+    // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
+    LO_TRY(align_enqueue(h->keyframe, h->query.as<PointXYZ>(), bound, &s->n_query, reinterpret_cast<const float*>(&s->guess),
+                         reinterpret_cast<float*>(&s->next), &s->align));
+    odom_gate_kernel<<<1, 1, 0, ctx->stream>>>(s, h->params.angular_divergence_threshold);  // cpp:53-65
+    LO_LAUNCHED(ctx);
+    LO_TRY(grid_cleanup_dev(h->keyframe, s->center, h->params.keyframe_cleanup_range));  // cpp:67
+    // transformWithNormals fused into the insert (cpp:69-70)
+    LO_TRY(grid_add_dev(h->keyframe, h->update.p, bound, 1, &s->current, &s->n_update));
+    return LO_OK;
+}
+
+static int finish_scan(lo_odometry* h, uint32_t n_points) {
+    lo_ctx* ctx = h->ctx;
+    odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback);
+    LO_LAUNCHED(ctx);
+    LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    const ScanReadback& r = *h->h_readback;
+    std::memcpy(h->pose, r.pose, sizeof(h->pose));
+    std::memcpy(h->keyframe->h_counters, r.kf_counters, sizeof(r.kf_counters));
+    // arrival tickets are tracked on the host
+    h->stats.n_points = n_points;
+    h->stats.n_planar = r.n_planar;
+    h->stats.n_update = r.n_update;
+    h->stats.n_query = r.n_query;
+    h->stats.outer_iterations = r.outer_iterations;
+    h->stats.unstable = static_cast<int32_t>(r.unstable);
+    h->stats.keyframe_voxels = r.kf_counters[GC_VOXELS];
+    if (r.kf_counters[GC_RANGE_ERR]) {
+        set_error("a key-frame point was not finite or outside the +-2^20 voxel index range");
+        return LO_E_RANGE;
+    }
+    return LO_OK;
+}
+
+// keep the host-tracked ticket counter across the device counter readback
+static void preserve_ticket(lo_grid* g, uint32_t ticket) { g->h_counters[GC_TICKET] = ticket; }
+
+extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odometry** out) {
+    if (!ctx || !params || !out) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    lo_odometry* h = new lo_odometry();
+    h->ctx = ctx;
+    h->params = *params;
+    std::memset(&h->stats, 0, sizeof(h->stats));
+    int st = lo_grid_create(ctx, params->keyframe_voxel_size, static_cast<size_t>(params->keyframe_max_points_cnt), 1 << 17, &h->keyframe);
+    if (st == LO_OK) st = lo_grid_create(ctx, params->keyframe_update_voxel_size, 1, 1 << 15, &h->update_ds);
+    if (st == LO_OK) st = lo_grid_create(ctx, params->keyframe_matching_voxel_size, 1, 1 << 15, &h->match_ds);
+    if (st != LO_OK) {
+        lo_odometry_destroy(h);
+        return st;
+    }
+    LO_CUDA(cudaMalloc(&h->d_state, sizeof(OdomDev)));
+    LO_CUDA(cudaMemsetAsync(h->d_state, 0, sizeof(OdomDev), ctx->stream));
+    LO_CUDA(cudaMalloc(&h->d_readback, sizeof(ScanReadback)));
+    LO_CUDA(cudaMallocHost(&h->h_readback, sizeof(ScanReadback)));
+    odom_init_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state);
+    LO_LAUNCHED(ctx);
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    *out = h;
+    return LO_OK;
+}
+
+extern "C" void lo_odometry_destroy(lo_odometry* h) {
+    if (!h) return;
+    cudaSetDevice(h->ctx->device);
+    cudaStreamSynchronize(h->ctx->stream);
+    lo_grid_destroy(h->keyframe);
+    lo_grid_destroy(h->update_ds);
+    lo_grid_destroy(h->match_ds);
+    if (h->d_state) cudaFree(h->d_state);
+    if (h->d_readback) cudaFree(h->d_readback);
+    if (h->h_readback) cudaFreeHost(h->h_readback);
+    for (DevBuf* b : {&h->scan, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    delete h;
+}
+
+extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, size_t n) {
+    if (!h || (!d_xyzirt32 && n)) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    OdomDev* s = h->d_state;
+    const uint32_t nn = static_cast<uint32_t>(n);
+    const uint32_t kf_ticket = h->keyframe->h_counters[GC_TICKET];
+    LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
+    LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
+    odom_predict_kernel<<<1, 1, 0, ctx->stream>>>(s);  // cpp:27-28
+    LO_LAUNCHED(ctx);
+    LO_TRY(deskew_dev(ctx, static_cast<const PointXYZIRT*>(d_xyzirt32), nn, &s->relative_inv, &s->identity,
+                      h->deskewed.as<PointXYZIRT>()));  // cpp:25,30
+    h->n_last = nn;
+    // classify (cpp:33) fused with rangeFilter (cpp:35)
+    LO_TRY(classify_dev(ctx, h->deskewed.as<PointXYZIRT>(), nn, 1, h->params.lidar_min_range, h->params.lidar_max_range,
+                        h->filtered.as<PointNormal>(), &s->n_planar));
+    LO_TRY(run_from_filtered(h, nn, &s->n_planar));
+    const uint32_t ticket_after = h->keyframe->h_counters[GC_TICKET];
+    (void)kf_ticket;
+    const int st = finish_scan(h, nn);
+    preserve_ticket(h->keyframe, ticket_after);
+    return st;
+}
+
+extern "C" int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t n) {
+    if (!h || (!xyzirt32 && n)) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
+    if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, ctx->stream));
+    return lo_odometry_process_dev(h, h->scan.p, n);
+}
+
+extern "C" int lo_odometry_process_planar(lo_odometry* h, const float* pn48_planar, size_t n) {
+    if (!h || (!pn48_planar && n)) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    OdomDev* s = h->d_state;
+    const uint32_t nn = static_cast<uint32_t>(n);
+    LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
+    LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
+    if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, pn48_planar, n * sizeof(PointNormal), cudaMemcpyHostToDevice, ctx->stream));
+    odom_predict_kernel<<<1, 1, 0, ctx->stream>>>(s);
+    LO_LAUNCHED(ctx);
+    LO_TRY(range_filter_dev(ctx, h->scan.as<PointNormal>(), nn, h->params.lidar_min_range, h->params.lidar_max_range,
+                            h->filtered.as<PointNormal>(), &s->n_planar));
+    h->n_last = 0;
+    LO_TRY(run_from_filtered(h, nn, &s->n_planar));
+    const uint32_t ticket_after = h->keyframe->h_counters[GC_TICKET];
+    const int st = finish_scan(h, nn);
+    preserve_ticket(h->keyframe, ticket_after);
+    return st;
+}
+
+extern "C" int lo_odometry_pose(lo_odometry* h, float out7[7]) {
+    if (!h || !out7) return LO_E_ARG;
+    std::memcpy(out7, h->pose, sizeof(h->pose));
+    return LO_OK;
+}
+
+extern "C" int lo_odometry_stats(lo_odometry* h, lo_scan_stats* out) {
+    if (!h || !out) return LO_E_ARG;
+    *out = h->stats;
+    return LO_OK;
+}
+
+extern "C" int lo_odometry_keyframe(lo_odometry* h, int full, float* xyz16_out, size_t cap, size_t* n) {
+    if (!h || !n) return LO_E_ARG;
+    return lo_grid_get_cloud(h->keyframe, full ? 1 : 2, 0, xyz16_out, cap, n);
+}
+
+extern "C" int lo_odometry_keyframe_pn(lo_odometry* h, float* pn48_out, size_t cap, size_t* n) {
+    if (!h || !n) return LO_E_ARG;
+    return lo_grid_get_cloud(h->keyframe, 0, 0, pn48_out, cap, n);
+}
+
+extern "C" int lo_odometry_deskewed(lo_odometry* h, void* xyzirt32_out, size_t cap, size_t* n) {
+    if (!h || !n) return LO_E_ARG;
+    *n = h->n_last;
+    if (!xyzirt32_out) return LO_OK;
+    if (cap < h->n_last) return LO_E_CAPACITY;
+    if (h->n_last == 0) return LO_OK;
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    LO_CUDA(cudaMemcpyAsync(xyzirt32_out, h->deskewed.p, static_cast<size_t>(h->n_last) * sizeof(PointXYZIRT), cudaMemcpyDeviceToHost,
+                            h->ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(h->ctx->stream));
+    return LO_OK;
+}

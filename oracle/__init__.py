@@ -79,7 +79,7 @@ class Oracle:
             "orc_align": (C.c_int, [vp, vp, sz, vp, vp, vp]),
             "orc_pca_normals": (None, [vp, sz, fl, vp]),
             "orc_params_default": (None, [vp]), "orc_odom_create": (vp, [vp]), "orc_odom_destroy": (None, [vp]),
-            "orc_odom_process": (None, [vp, vp, sz, vp, vp]), "orc_odom_pose": (None, [vp, vp]),
+            "orc_odom_process": (None, [vp, vp, sz, vp, vp]), "orc_odom_process_planar": (None, [vp, vp, sz, vp, vp]), "orc_odom_pose": (None, [vp, vp]),
             "orc_odom_keyframe": (sz, [vp, C.c_int, vp, sz]), "orc_odom_keyframe_pn": (sz, [vp, vp, sz]),
             "orc_odom_deskewed": (sz, [vp, vp, sz]),
         }
@@ -276,6 +276,13 @@ class OracleOdometry:
         counts = np.zeros(4, np.uint64)
         stats = np.zeros(4)
         self.o.L.orc_odom_process(self.h, _p(cloud), len(cloud), _p(counts), _p(stats))
+        return counts, stats
+
+    def process_planar(self, planar):
+        planar = np.ascontiguousarray(planar, dtype=PN)
+        counts = np.zeros(4, np.uint64)
+        stats = np.zeros(4)
+        self.o.L.orc_odom_process_planar(self.h, _p(planar), len(planar), _p(counts), _p(stats))
         return counts, stats
 
     def pose(self):

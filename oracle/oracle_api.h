@@ -96,6 +96,7 @@ void orc_odom_destroy(void* h);
  * {outer_iterations, unstable(0/1), ms_total, ms_align}. use_classifier=1 runs CloudClassifier; 0 expects the
  * caller to use orc_odom_process_planar instead. */
 void orc_odom_process(void* h, const void* xyzirt32, size_t n, uint64_t counts4[4], double stats4[4]);
+void orc_odom_process_planar(void* h, const float* pn48_planar, size_t n, uint64_t counts4[4], double stats4[4]);
 void orc_odom_pose(const void* h, float out7[7]);
 size_t orc_odom_keyframe(const void* h, int full, float* xyz16_out, size_t cap);
 size_t orc_odom_keyframe_pn(const void* h, float* pn48_out, size_t cap);
