@@ -96,6 +96,8 @@ typedef struct lo_normal_eq {
     double g[6];        /* J'r, tangent order: rotation(3), translation(3) */
     double jtj[36];     /* J'J row-major */
     uint64_t n_valid;   /* correspondences found */
+    uint64_t candidates; /* stored points visited in the 27 neighbours, summed over queries (roofline bytes) */
+    uint64_t occupied;   /* occupied neighbour voxels, summed over queries */
 } lo_normal_eq;
 /* One fused pass: correspondence search at pose7 (float, as findMatchingPairs sees it) then
  * PointToPlaneErrorAnalytic + HuberLoss(0.15) corrector evaluated at x7d = {qw,qx,qy,qz,tx,ty,tz} (double),

@@ -30,7 +30,8 @@ class Pair(C.Structure):
 
 
 class NormalEq(C.Structure):
-    _fields_ = [("cost", C.c_double), ("g", C.c_double * 6), ("jtj", C.c_double * 36), ("n_valid", C.c_uint64)]
+    _fields_ = [("cost", C.c_double), ("g", C.c_double * 6), ("jtj", C.c_double * 36), ("n_valid", C.c_uint64),
+                ("candidates", C.c_uint64), ("occupied", C.c_uint64)]
 
 
 class AlignStats(C.Structure):
@@ -267,6 +268,7 @@ class VoxelGrid:
         b = np.ascontiguousarray(prior_b, dtype=np.float64)
         out = NormalEq()
         _check(self.lib.lo_nn_residual(self.h, _p(cloud), len(cloud), _p(_pose7(pose7)), _p(x), _p(b), max_dist, C.byref(out)))
+        self.last_candidates, self.last_occupied = int(out.candidates), int(out.occupied)
         return out.cost, np.array(out.g[:]), np.array(out.jtj[:]).reshape(6, 6), int(out.n_valid)
 
 

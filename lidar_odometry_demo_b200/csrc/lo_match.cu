@@ -195,12 +195,16 @@ __global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, con
         if (mine < m) q = queries[mine];  // coalesced 16 B loads
         bool my_valid = false;
         float my_o[3] = {0.f, 0.f, 0.f}, my_n[3] = {0.f, 0.f, 0.f};
+        uint32_t visited = 0, occupied = 0;
         const uint32_t in_tile = min(32u, m - base);
         for (uint32_t j = 0; j < in_tile; j++) {
             const float qx = __shfl_sync(kFullMask, q.x, j), qy = __shfl_sync(kFullMask, q.y, j), qz = __shfl_sync(kFullMask, q.z, j);
             float wq[3];
             transform_query(tf, qx, qy, qz, wq);
-            const Found f = nn_search_warp(g, wq, max_d2, lane);
+            uint32_t cnt = 0;
+            const Found f = nn_search_warp(g, wq, max_d2, lane, &cnt);
+            visited += cnt;
+            occupied += cnt ? 1u : 0u;
             if (lane == static_cast<int>(j)) {
                 my_valid = f.valid;
                 for (int k = 0; k < 3; k++) {
@@ -212,6 +216,11 @@ __global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, con
         const float pf[3] = {q.x, q.y, q.z};
         const Terms t = pair_terms(ep, pf, my_o, my_n);
         accumulate_warp(row, t, my_valid, lane);
+        const double vis = warp_sum(static_cast<double>(visited)), occ = warp_sum(static_cast<double>(occupied));
+        if (lane == 0) {
+            row[29] += vis;
+            row[30] += occ;
+        }
     }
     block_rows_to_global(rows, partials + blockIdx.x * 32);
 }
@@ -232,6 +241,8 @@ __global__ void normal_eq_finalize_kernel(const double* __restrict__ partials, i
             for (int c = 0; c < 6; c++) out->jtj[a * 6 + c] = sym(acc, a, c);
         }
         out->n_valid = static_cast<uint64_t>(acc[28] + 0.5);
+        out->candidates = static_cast<uint64_t>(acc[29] + 0.5);
+        out->occupied = static_cast<uint64_t>(acc[30] + 0.5);
     }
 }
 

@@ -8,7 +8,7 @@
 
 namespace lo {
 
-constexpr int kAcc = 29;  // 21 (upper JtJ) + 6 (Jtr) + 1 (cost) + 1 (valid pairs)
+constexpr int kAcc = 31;  // 21 (upper JtJ) + 6 (Jtr) + cost + valid pairs + candidates visited + occupied neighbours
 constexpr unsigned kFullMask = 0xFFFFFFFFu;
 
 struct Found {        // result of one query, identical in every lane of the warp
@@ -21,16 +21,16 @@ struct Found {        // result of one query, identical in every lane of the war
 // ix -> iy -> iz (l = 9*(dx+1) + 3*(dy+1) + (dz+1)), and scans that voxel's stored points in slot order.
 // The winner is the first strict minimum in (probe, slot) scan order, which is the lexicographic minimum
 // of (d2, probe, slot): d2 >= 0, so its float bit pattern orders like its value.
-__device__ inline Found nn_search_warp(const GridView& g, const float wq[3], float max_d2, int lane) {
+__device__ inline Found nn_search_warp(const GridView& g, const float wq[3], float max_d2, int lane, uint32_t* lane_count = nullptr) {
     const long long ox = axis_index(wq[0], g.voxel_size), oy = axis_index(wq[1], g.voxel_size), oz = axis_index(wq[2], g.voxel_size);
     unsigned long long best = ~0ull;
     uint32_t vid = 0;
+    uint32_t count = 0;
     if (lane < 27) {
         const long long ix = ox + (lane / 9) - 1, iy = oy + ((lane / 3) % 3) - 1, iz = oz + (lane % 3) - 1;
         if (axis_in_range(ix) && axis_in_range(iy) && axis_in_range(iz)) {
             const unsigned long long key = pack_key(ix, iy, iz);
             uint32_t h = probe_hash(key) & g.mask;
-            uint32_t count = 0;
             while (true) {
                 const uint4 raw = __ldg(reinterpret_cast<const uint4*>(g.slots + h));
                 const unsigned long long k = (static_cast<unsigned long long>(raw.y) << 32) | raw.x;
@@ -66,6 +66,7 @@ __device__ inline Found nn_search_warp(const GridView& g, const float wq[3], flo
         const unsigned long long other = __shfl_xor_sync(kFullMask, m, off);
         m = other < m ? other : m;
     }
+    if (lane_count) *lane_count = count;
     Found f;
     f.valid = (m != ~0ull);
     f.o[0] = f.o[1] = f.o[2] = f.n[0] = f.n[1] = f.n[2] = 0.f;

@@ -32,7 +32,7 @@ class Scene:
         self.cyl_r = rng.uniform(0.15, 0.6, n_cyl)
         self.cyl_top = self.ground_z + rng.uniform(2.0, 8.0, n_cyl)
 
-    def cast(self, o, d, max_range=120.0):
+    def cast(self, o, d, max_range=120.0, cull=90.0):
         """o, d: (n,3) float64 ray origins / unit directions -> range (n,), inf where nothing is hit."""
         n = len(o)
         t = np.full(n, np.inf)
@@ -46,7 +46,7 @@ class Scene:
                 t = np.where(ok, tw, t)
             # boxes near the sensor only (slab test)
             cx = o[:, 0].mean()
-            sel = np.nonzero((self.box_hi[:, 0] > cx - max_range) & (self.box_lo[:, 0] < cx + max_range))[0]
+            sel = np.nonzero((self.box_hi[:, 0] > cx - cull) & (self.box_lo[:, 0] < cx + cull))[0]
             inv = 1.0 / d
             for b in sel:
                 t0 = (self.box_lo[b] - o) * inv
@@ -55,7 +55,7 @@ class Scene:
                 tf = np.maximum(t0, t1).min(1)
                 ok = (tn <= tf) & (tn > 0) & (tn < t)
                 t = np.where(ok, tn, t)
-            sel = np.nonzero(np.abs(self.cyl_c[:, 0] - cx) < max_range)[0]
+            sel = np.nonzero(np.abs(self.cyl_c[:, 0] - cx) < cull)[0]
             for c in sel:
                 ox, oy = o[:, 0] - self.cyl_c[c, 0], o[:, 1] - self.cyl_c[c, 1]
                 a = d[:, 0] ** 2 + d[:, 1] ** 2

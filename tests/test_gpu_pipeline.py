@@ -1,0 +1,101 @@
+"""GPU parity for the per-point stages, the reference-order down-sampler export and the odometry pipeline."""
+import numpy as np
+import pytest
+
+import lidar_odometry_demo_b200 as lo
+from util import PN, XYZ, bits_equal, planar_scene, pn_to_xyz, pose_error, random_pn, sort_rows
+
+pytestmark = pytest.mark.gpu
+F = ("x", "y", "z", "nx", "ny", "nz")
+POSES = [np.array(p, np.float32) for p in ([0, 0, 0, 1, 0, 0, 0], [0.4, -0.02, 0.01, 0.99995, 0.001, -0.002, 0.009],
+                                           [-2, 2, 0, 0.9238795, 0.2705981, 0.2705981, 0.0])]
+
+
+def test_rigid_transforms_bit_exact(ctx, port):
+    pn = random_pn(5000, 3)
+    for pose in POSES:
+        assert bits_equal(ctx.transform_with_normals(pn, pose), port.transform_with_normals(pn, pose), F)
+        assert bits_equal(ctx.transform_xyz(pn_to_xyz(pn), pose), port.transform_xyz(pn_to_xyz(pn), pose), ("x", "y", "z"))
+
+
+def test_range_filter_bit_exact(ctx, port):
+    pn = random_pn(20000, 4, spread=30.0)
+    a, b = ctx.range_filter(pn, 4.0, 80.0), port.range_filter(pn, 4.0, 80.0)
+    assert len(a) == len(b) and bits_equal(a, b, F)
+
+
+def test_deskew(ctx, port, stream12):
+    scan = stream12[0][3]
+    for start in POSES[1:]:
+        end = POSES[0]
+        got = ctx.deskew(scan, start, end)
+        want = port.transform_nonrigid(port.time_normalize(scan), start, end)
+        assert np.array_equal(got["time"].view(np.uint32), want["time"].view(np.uint32))
+        assert np.array_equal(got["ring"], want["ring"]) and np.array_equal(got["intensity"], want["intensity"])
+        for k in ("x", "y", "z"):   # glibc sinf/acosf vs device: tolerance 1e-6 abs, most points identical
+            assert np.abs(got[k].astype(np.float64) - want[k]).max() < 2e-5
+        same = np.mean([(got[k].view(np.uint32) == want[k].view(np.uint32)).mean() for k in ("x", "y", "z")])
+        assert same > 0.97, same   # measured 0.989 on B200 vs glibc 2.39
+
+
+def test_classifier(ctx, port, stream12):
+    scan = stream12[0][2]
+    ident = POSES[0]
+    deskewed = port.transform_nonrigid(port.time_normalize(scan), ident, ident)
+    got = ctx.classify(deskewed)
+    want, _ = port.classify(deskewed)
+    # azimuth binning uses atan2f (glibc) vs a correctly rounded device atan2: identical except for rare bin flips
+    assert abs(len(got) - len(want)) <= 0.002 * len(want)
+    a, b = sort_rows(got), sort_rows(want)
+    sa = set(map(bytes, a)); sb = set(map(bytes, b))
+    assert len(sa ^ sb) <= 0.004 * len(sb)
+    if len(got) == len(want) and len(sa ^ sb) == 0:
+        assert bits_equal(got, want, F)   # and then the order is the reference's too
+
+
+def test_downsampler_reference_order(ctx, port, stream12):
+    """VoxelGrid(vs,1).addCloud + getCloud(): the tsl::robin_map iteration order."""
+    planar = planar_scene(port, stream12[0], 1)
+    for vs in (0.1, 0.3):
+        g = lo.VoxelGrid(ctx, vs, 1); o = port.grid(vs, 1)
+        g.addCloud(planar); o.add_cloud(planar)
+        got, want = g.getCloud(reference_order=True), o.get_cloud()
+        assert len(got) == len(want)
+        assert np.array_equal(sort_rows(got), sort_rows(want))
+        same = (got["x"].view(np.uint32) == want["x"].view(np.uint32)) & (got["y"].view(np.uint32) == want["y"].view(np.uint32))
+        # round 1: ties inside one ideal bucket are emitted in arrival order (DESIGN.md "robin order")
+        assert same.mean() > 0.90, same.mean()
+
+
+def test_odometry_planar_entry(ctx, port, stream12):
+    """processCloud from the planar cloud on: poses within 1e-4 m / 1e-4 rad of the oracle on every scan."""
+    scans = stream12[0]
+    od = lo.LidarOdometry(ctx)
+    oo = port.odometry()
+    for k in range(8):
+        planar = planar_scene(port, scans, k)
+        # un-filtered planar cloud is what the entry takes; planar_scene already filtered, which is idempotent
+        od.processPlanar(planar)
+        counts, _ = oo.process_planar(planar)
+        st = od.stats()
+        assert st.n_planar == counts[1] and st.n_update == counts[2] and st.n_query == counts[3]
+        dt, dr = pose_error(od.getCurrentPose(), oo.pose())
+        assert dt < 1e-4 and dr < 1e-4, (k, dt, dr)
+    assert od.stats().keyframe_voxels == len(oo.keyframe(False))
+
+
+def test_odometry_full_pipeline(ctx, port, stream12):
+    scans, pos, _ = stream12
+    od = lo.LidarOdometry(ctx)
+    oo = port.odometry()
+    worst = (0.0, 0.0)
+    for k in range(len(scans)):
+        od.processCloud(scans[k])
+        counts, stats = oo.process(scans[k])
+        st = od.stats()
+        assert abs(int(st.n_planar) - int(counts[1])) <= 0.01 * max(1, counts[1])
+        dt, dr = pose_error(od.getCurrentPose(), oo.pose())
+        worst = (max(worst[0], dt), max(worst[1], dr))
+    assert worst[0] < 1e-4 and worst[1] < 1e-4, worst
+    # the deskewed cloud of the last scan is exported like getTempCloud()
+    assert len(od.getTempCloud()) == len(scans[-1])
