@@ -3,6 +3,7 @@
 
 #include <algorithm>
 
+#include "lo_libm.cuh"
 #include "lo_points.cuh"
 
 namespace lo {
@@ -39,10 +40,9 @@ __global__ void time_minmax_kernel(const PointXYZIRT* __restrict__ in, uint32_t 
     }
 }
 
-// sinf / acosf of the reference run in glibc; evaluating in double and rounding once gives the correctly
-// rounded float, which is what glibc's float routines return in all but rare boundary cases.
-__device__ inline float sin_as_float(float a) { return static_cast<float>(sin(static_cast<double>(a))); }
-__device__ inline float acos_as_float(float a) { return static_cast<float>(acos(static_cast<double>(a))); }
+// sinf / acosf of the reference run in glibc: restated bit for bit in lo_libm.cuh
+__device__ inline float sin_as_float(float a) { return libm::sinf_glibc(a); }
+__device__ inline float acos_as_float(float a) { return libm::acosf_fdlibm(a); }
 
 __global__ void deskew_kernel(const PointXYZIRT* __restrict__ in, uint32_t n, const uint32_t* __restrict__ minmax,
                               const Pose* __restrict__ start_p, const Pose* __restrict__ end_p, PointXYZIRT* __restrict__ out) {
@@ -231,7 +231,7 @@ __global__ void cell_fill_kernel(const PointXYZIRT* __restrict__ in, uint32_t n,
     const float4 a = reinterpret_cast<const float4*>(in)[2 * i];
     const uint32_t ring = in[i].ring & 0xFF;
     // :49-50  float azimuth = atan2(-y, x) + pi;  index = abs(azimuth * W / (2.0 * pi))
-    const float at = static_cast<float>(atan2(static_cast<double>(-a.y), static_cast<double>(a.x)));
+    const float at = libm::atan2f_fdlibm(-a.y, a.x);  // glibc atan2f, bit for bit (lo_libm.cuh)
     const float azimuth = static_cast<float>(static_cast<double>(at) + 3.141592653589793);
     const double scaled = static_cast<double>(azimuth * static_cast<float>(W)) / (2.0 * 3.141592653589793);
     if (!(scaled == scaled)) return;
