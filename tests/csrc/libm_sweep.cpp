@@ -14,7 +14,7 @@ int main() {
     std::mt19937_64 rng(12345);
     std::uniform_real_distribution<float> coord(-120.f, 120.f), unit(-1.f, 1.f), small(-0.7853f, 0.7853f);
     long bad_atan2 = 0, bad_acos = 0, bad_sin = 0, bad_atan = 0;
-    const long n = 20000000;
+    const long n = 4000000;
     for (long i = 0; i < n; i++) {
         const float y = coord(rng), x = coord(rng);
         if (!same(lo::libm::atan2f_fdlibm(y, x), atan2f(y, x))) bad_atan2++;
