@@ -37,6 +37,7 @@ __host__ __device__ inline double sym(const double* H, int a, int b) { return a 
 
 // NormalPrior(diag(10), b) with TrivialLoss (cloud_matcher.cpp:153-154): three rows 10*(t-b), Jacobian 10*I
 __host__ __device__ inline void add_prior(double acc[kAcc], const double t[3], const double b[3]) {
+#pragma unroll
     for (int k = 0; k < 3; k++) {
         const double r = 10.0 * (t[k] - b[k]);
         acc[27] += 0.5 * (r * r);
@@ -48,6 +49,7 @@ __host__ __device__ inline void add_prior(double acc[kAcc], const double t[3], c
 __host__ __device__ inline void quaternion_plus(const double x[4], const double d[3], double out[4]) {
     const double nd = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
     if (nd == 0.0) {
+#pragma unroll
         for (int i = 0; i < 4; i++) out[i] = x[i];
         return;
     }
@@ -61,6 +63,7 @@ __host__ __device__ inline void quaternion_plus(const double x[4], const double 
 
 __host__ __device__ inline double norm7(const double v[7]) {
     double s = 0.0;
+#pragma unroll
     for (int i = 0; i < 7; i++) s += v[i] * v[i];
     return sqrt(s);
 }
@@ -76,19 +79,24 @@ __host__ __device__ inline bool lm_record(LmState& s, double step_norm) {
 }
 
 __host__ __device__ inline void lm_take_point(LmState& s, const double acc[kAcc]) {
+#pragma unroll
     for (int k = 0; k < 21; k++) s.H[k] = acc[k];
+#pragma unroll
     for (int k = 0; k < 6; k++) s.g[k] = acc[21 + k];
     s.x_cost = acc[27];
     double gm = 0.0;
+#pragma unroll
     for (int k = 0; k < 6; k++) gm = fmax(gm, fabs(s.g[k]));
     s.grad_max = gm;
 }
 
 // IterationZero. acc = normal equations at x0 (prior included). Returns true if the solve continues.
 __host__ __device__ inline bool lm_begin(LmState& s, const double x0[7], const double acc[kAcc]) {
+#pragma unroll
     for (int i = 0; i < 7; i++) s.x[i] = x0[i];
     s.x_norm = norm7(s.x);
     lm_take_point(s, acc);
+#pragma unroll
     for (int k = 0; k < 6; k++) s.scale[k] = 1.0 / (1.0 + sqrt(s.H[tri(k, k)]));
     s.radius = 1e4;
     s.decrease_factor = 2.0;
@@ -104,9 +112,12 @@ __host__ __device__ inline bool lm_begin(LmState& s, const double x0[7], const d
 // Solve (Hs + diag(d2)) y = gs by Cholesky; false if not positive definite / not finite.
 __host__ __device__ inline bool solve6(const double Hs[21], const double d2[6], const double gs[6], double y[6]) {
     double L[6][6];
+#pragma unroll
     for (int a = 0; a < 6; a++)
+#pragma unroll
         for (int b = 0; b <= a; b++) {
             double v = Hs[tri(b, a)] + (a == b ? d2[a] : 0.0);
+#pragma unroll
             for (int k = 0; k < b; k++) v -= L[a][k] * L[b][k];
             if (a == b) {
                 if (!(v > 0.0)) return false;
@@ -116,16 +127,21 @@ __host__ __device__ inline bool solve6(const double Hs[21], const double d2[6], 
             }
         }
     double z[6];
+#pragma unroll
     for (int a = 0; a < 6; a++) {
         double v = gs[a];
+#pragma unroll
         for (int k = 0; k < a; k++) v -= L[a][k] * z[k];
         z[a] = v / L[a][a];
     }
+#pragma unroll
     for (int a = 5; a >= 0; a--) {
         double v = z[a];
+#pragma unroll
         for (int k = a + 1; k < 6; k++) v -= L[k][a] * y[k];
         y[a] = v / L[a][a];
     }
+#pragma unroll
     for (int a = 0; a < 6; a++)
         if (!isfinite(y[a])) return false;
     return true;
@@ -136,24 +152,31 @@ __host__ __device__ inline bool solve6(const double Hs[21], const double d2[6], 
 __host__ __device__ inline bool lm_propose(LmState& s) {
     while (true) {
         double Hs[21], gs[6];
+#pragma unroll
         for (int a = 0; a < 6; a++) {
             gs[a] = s.g[a] * s.scale[a];
+#pragma unroll
             for (int b = a; b < 6; b++) Hs[tri(a, b)] = s.H[tri(a, b)] * s.scale[a] * s.scale[b];
         }
         if (!s.reuse_diagonal)
+#pragma unroll
             for (int a = 0; a < 6; a++) s.diagonal[a] = fmin(fmax(Hs[tri(a, a)], 1e-6), 1e32);
         double d2[6], y[6], step[6];
+#pragma unroll
         for (int a = 0; a < 6; a++) d2[a] = s.diagonal[a] / s.radius;
         const bool ok = solve6(Hs, d2, gs, y);
         s.reuse_diagonal = 1;
         bool valid = false;
         if (ok) {
+#pragma unroll
             for (int a = 0; a < 6; a++) step[a] = -y[a];
             // model_cost_change = -(J s)'(r + J s / 2) = -(s'gs + s'Hs s / 2)
             double lin = 0.0, quad = 0.0;
+#pragma unroll
             for (int a = 0; a < 6; a++) {
                 lin += step[a] * gs[a];
                 double row = 0.0;
+#pragma unroll
                 for (int b = 0; b < 6; b++) row += sym(Hs, a, b) * step[b];
                 quad += step[a] * row;
             }
@@ -164,8 +187,10 @@ __host__ __device__ inline bool lm_propose(LmState& s) {
         if (valid) {
             s.num_invalid = 0;
             double delta[6];
+#pragma unroll
             for (int a = 0; a < 6; a++) delta[a] = step[a] * s.scale[a];
             quaternion_plus(s.x, delta, s.cand);
+#pragma unroll
             for (int k = 0; k < 3; k++) s.cand[4 + k] = s.x[4 + k] + delta[3 + k];
             return true;
         }
@@ -187,6 +212,7 @@ __host__ __device__ inline bool lm_update(LmState& s, const double acc[kAcc]) {
     double step_norm = 0.0;
     if (s.any_success) {  // Ceres 2.2: parameter tolerance only after one successful step
         double d = 0.0;
+#pragma unroll
         for (int i = 0; i < 7; i++) d += (s.x[i] - s.cand[i]) * (s.x[i] - s.cand[i]);
         step_norm = sqrt(d);
         if (step_norm <= 1e-8 * (s.x_norm + 1e-8)) { s.termination = LM_CONV_PARAMETER; return false; }
@@ -195,6 +221,7 @@ __host__ __device__ inline bool lm_update(LmState& s, const double acc[kAcc]) {
     if (fabs(cost_change) <= 1e-5 * s.x_cost) { s.termination = LM_CONV_FUNCTION; return false; }
     const double rho = cand_cost >= 1.7976931348623157e308 ? -1.7976931348623157e308 : cost_change / s.model_cost_change;
     if (rho > 1e-3) {
+#pragma unroll
         for (int i = 0; i < 7; i++) s.x[i] = s.cand[i];
         s.x_norm = norm7(s.x);
         lm_take_point(s, acc);

@@ -8,6 +8,7 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "lo_host.h"
@@ -18,7 +19,8 @@ namespace cg = cooperative_groups;
 namespace lo {
 
 // ---------------------------------------------------------------------------------------------------
-// shared accumulation helpers. `row` points at this warp's kAcc doubles in shared memory.
+// shared accumulation helpers. `row` points at this warp's kRow (= 32 >= kAcc) doubles in shared memory.
+constexpr int kRow = 32;
 struct Terms {
     double j[6];
     double rc;     // corrected residual
@@ -128,23 +130,41 @@ __device__ inline void block_rows_to_global(double* rows, double* out) {
     if (threadIdx.x < kAcc) {
         double v = 0.0;
         for (int w = 0; w < nwarps; w++) {
-            v += rows[w * kAcc + threadIdx.x];
-            rows[w * kAcc + threadIdx.x] = 0.0;
+            v += rows[w * kRow + threadIdx.x];
+            rows[w * kRow + threadIdx.x] = 0.0;
         }
         out[threadIdx.x] = v;
     }
     __syncthreads();
 }
 
-// every block sums the per-block partials [nblocks][32] into total[kAcc] (shared), in a fixed order
-__device__ inline void reduce_partials(const double* partials, int nblocks, double* total) {
+// every block sums the per-block partials [nblocks][32] into total[kAcc] (shared), in a fixed order.
+// Thread t reads elements t, t + blockDim, ... of the flat array (coalesced); because blockDim is a multiple
+// of 32 a thread always sees column (t & 31), so it keeps one running sum; the per-warp sums are then added
+// in warp order. `scratch` holds (blockDim.x / 32) * 32 doubles (the caller's per-warp rows are reused).
+__device__ inline void reduce_partials(const double* partials, int nblocks, double* scratch, double* total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    for (int c = warp; c < kAcc; c += nwarps) {
-        double v = 0.0;
-        for (int b = lane; b < nblocks; b += 32) v += __ldcg(partials + b * 32 + c);
-        v = warp_sum(v);
-        if (lane == 0) total[c] = v;
+    double v = 0.0;
+    const int n = nblocks * 32;
+    for (int e0 = threadIdx.x; e0 < n; e0 += 8 * blockDim.x) {  // 8 independent loads in flight, fixed order of addition
+        double t[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int e = e0 + u * blockDim.x;
+            t[u] = e < n ? __ldcg(partials + e) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) v += t[u];
     }
+    scratch[warp * 32 + lane] = v;
+    __syncthreads();
+    if (threadIdx.x < kAcc) {
+        double t = 0.0;
+        for (int w = 0; w < nwarps; w++) t += scratch[w * 32 + threadIdx.x];
+        total[threadIdx.x] = t;
+    }
+    __syncthreads();
+    scratch[warp * 32 + lane] = 0.0;  // the rows double as accumulators of the next pass
     __syncthreads();
 }
 
@@ -181,11 +201,11 @@ constexpr int kNnThreads = 256;
 __global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
                                                                   QueryTransform tf, EvalPoint ep, float max_d2,
                                                                   double* __restrict__ partials) {
-    __shared__ double rows[(kNnThreads / 32) * kAcc];
+    __shared__ double rows[(kNnThreads / 32) * kRow];
     const int lane = threadIdx.x & 31, warp_in_block = threadIdx.x >> 5;
-    for (int k = threadIdx.x; k < (kNnThreads / 32) * kAcc; k += blockDim.x) rows[k] = 0.0;
+    for (int k = threadIdx.x; k < (kNnThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
     __syncthreads();
-    double* row = rows + warp_in_block * kAcc;
+    double* row = rows + warp_in_block * kRow;
     const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t tiles = (m + 31) / 32;
     for (uint32_t tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; tile < tiles; tile += total_warps) {
@@ -229,7 +249,8 @@ __global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, con
 __global__ void normal_eq_finalize_kernel(const double* __restrict__ partials, int nblocks, EvalPoint ep, double b0, double b1, double b2,
                                           lo_normal_eq* __restrict__ out) {
     __shared__ double total[32];
-    reduce_partials(partials, nblocks, total);
+    __shared__ double scratch[(256 / 32) * kRow];
+    reduce_partials(partials, nblocks, scratch, total);
     if (threadIdx.x == 0) {
         double acc[kAcc];
         for (int k = 0; k < kAcc; k++) acc[k] = total[k];
@@ -262,12 +283,22 @@ struct AlignArgs {
     float* out_pose;       // device pose7
     lo_align_stats* stats; // device, nullable
     float max_dist;
+    long long* trace;      // nullable: (tag, clock64) pairs written by block 0 thread 0 (LO_ALIGN_TRACE=1)
 };
 
-__global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
+#define LO_TRACE(tag)                                                          \
+    do {                                                                       \
+        if (a.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < 500) { \
+            a.trace[2 * trace_n] = (tag);                                      \
+            a.trace[2 * trace_n + 1] = clock64();                              \
+            trace_n++;                                                         \
+        }                                                                      \
+    } while (0)
+
+__global__ void __launch_bounds__(kAlignThreads, 1) align_kernel(AlignArgs a) {
     cg::grid_group grid = cg::this_grid();
     if (a.m_dev) a.m = min(a.m, *a.m_dev);
-    __shared__ double rows[(kAlignThreads / 32) * kAcc];
+    __shared__ double rows[(kAlignThreads / 32) * kRow];
     __shared__ double total[32];
     __shared__ LmState lm;
     __shared__ EvalPoint ep_s;
@@ -275,12 +306,12 @@ __global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
     __shared__ int flag_s;
 
     const int lane = threadIdx.x & 31;
-    const uint32_t gthread = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t gwarp = gthread >> 5;
+    // consecutive queries / tiles go to different SMs: warp w of block b is global warp w * gridDim.x + b
+    const uint32_t gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
     const int nblocks = gridDim.x;
-    double* row = rows + (threadIdx.x >> 5) * kAcc;
-    for (int k = threadIdx.x; k < (kAlignThreads / 32) * kAcc; k += blockDim.x) rows[k] = 0.0;
+    double* row = rows + (threadIdx.x >> 5) * kRow;
+    for (int k = threadIdx.x; k < (kAlignThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
     if (threadIdx.x < 7) pose_s[threadIdx.x] = a.guess[threadIdx.x];
     __syncthreads();
     const double prior_b[3] = {static_cast<double>(a.guess[0]), static_cast<double>(a.guess[1]), static_cast<double>(a.guess[2])};
@@ -288,6 +319,8 @@ __global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
     int buf = 0;
     int lm_total = 0;
     bool cont = false;  // meaningful in thread 0 only
+    int trace_n = 0;
+    LO_TRACE(0);
 
     for (int outer = 0; outer < 35; outer++) {  // cloud_matcher.cpp:117
         // ---- correspondences at the current (float) pose + evaluation at x0 = double(pose) ----
@@ -311,15 +344,29 @@ __global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
                 }
             }
         }
+        LO_TRACE(1);
         block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
         grid.sync();
-        reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, total);
+        LO_TRACE(2);
+        // this warp's first tile of pairs stays in registers for every LM evaluation of this outer iteration
+        const uint32_t i0 = gwarp * 32 + lane;
+        bool valid0 = false;
+        float pq0[3] = {0.f, 0.f, 0.f}, of0[3] = {0.f, 0.f, 0.f}, nf0[3] = {0.f, 0.f, 0.f};
+        if (i0 < a.m) {
+            const float4 o = __ldcg(a.pair_o + i0);
+            const float4 nv = __ldcg(a.pair_n + i0);
+            const PointXYZ q = a.queries[i0];
+            valid0 = o.w != 0.f;
+            pq0[0] = q.x; pq0[1] = q.y; pq0[2] = q.z;
+            of0[0] = o.x; of0[1] = o.y; of0[2] = o.z;
+            nf0[0] = nv.x; nf0[1] = nv.y; nf0[2] = nv.z;
+        }
+        reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, rows, total);
+        LO_TRACE(3);
         buf ^= 1;
         if (threadIdx.x == 0) {
-            double acc[kAcc];
-            for (int k = 0; k < kAcc; k++) acc[k] = total[k];
-            add_prior(acc, ep0.t, prior_b);
-            cont = lm_begin(lm, x0, acc);
+            add_prior(total, ep0.t, prior_b);
+            cont = lm_begin(lm, x0, total);
             if (a.stats && blockIdx.x == 0) {
                 a.stats->pairs_log[outer] = static_cast<int32_t>(total[28] + 0.5);
                 a.stats->valid_pairs = static_cast<int32_t>(total[28] + 0.5);
@@ -332,9 +379,21 @@ __global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
                 flag_s = need_eval ? 1 : 0;
                 if (need_eval) ep_s = make_eval_point(lm.cand);
             }
+            LO_TRACE(4);
             __syncthreads();
             if (!flag_s) break;
-            for (uint32_t base = gwarp * 32; base < a.m; base += total_warps * 32) {
+            if (gwarp * 32 < a.m) {
+                Terms t;
+                if (valid0) {
+                    t = pair_terms(ep_s, pq0, of0, nf0);
+                } else {
+                    for (int k = 0; k < 6; k++) t.j[k] = 0.0;
+                    t.rc = 0.0;
+                    t.cost = 0.0;
+                }
+                accumulate_warp(row, t, valid0, lane);
+            }
+            for (uint32_t base = (gwarp + total_warps) * 32; base < a.m; base += total_warps * 32) {
                 const uint32_t i = base + lane;
                 bool valid = false;
                 Terms t;
@@ -355,16 +414,18 @@ __global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
                 }
                 accumulate_warp(row, t, valid, lane);
             }
+            LO_TRACE(5);
             block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
             grid.sync();
-            reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, total);
+            LO_TRACE(6);
+            reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, rows, total);
+            LO_TRACE(7);
             buf ^= 1;
             if (threadIdx.x == 0) {
-                double acc[kAcc];
-                for (int k = 0; k < kAcc; k++) acc[k] = total[k];
-                add_prior(acc, ep_s.t, prior_b);
-                cont = lm_update(lm, acc);
+                add_prior(total, ep_s.t, prior_b);
+                cont = lm_update(lm, total);
             }
+            LO_TRACE(8);
         }
         // ---- float round trip of the pose (cloud_matcher.cpp:161-167) and the outer stop rule (:169) ----
         if (threadIdx.x == 0) {
@@ -386,6 +447,8 @@ __global__ void __launch_bounds__(kAlignThreads, 2) align_kernel(AlignArgs a) {
         if (flag_s) break;
         __syncthreads();  // flag_s is rewritten by thread 0 at the top of the next solve
     }
+    LO_TRACE(9);
+    if (a.trace && blockIdx.x == 0 && threadIdx.x == 0) a.trace[1000] = trace_n;
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // cloud_matcher.cpp:175 Quaternionf::normalize()
         const float w = pose_s[3], x = pose_s[4], y = pose_s[5], z = pose_s[6];
         const float nrm = sqrtf((x * x + z * z) + (y * y + w * w));
@@ -426,6 +489,12 @@ int align_enqueue(lo_grid* kf, const PointXYZ* d_queries, uint32_t m, const uint
     args.out_pose = d_out7;
     args.stats = d_stats;
     args.max_dist = 0.3f;  // cloud_matcher.cpp:139
+    static const bool want_trace = getenv("LO_ALIGN_TRACE") != nullptr;
+    args.trace = nullptr;
+    if (want_trace) {
+        LO_TRY(ctx->tmp_d.ensure(1001 * sizeof(long long)));
+        args.trace = ctx->tmp_d.as<long long>();
+    }
     void* kargs[] = {&args};
     LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(align_kernel), dim3(blocks), dim3(kAlignThreads), kargs, 0, ctx->stream));
     ctx->launches++;
@@ -515,6 +584,11 @@ extern "C" int lo_align_dev(lo_grid* kf, const void* d_xyz16, size_t m, const fl
     LO_CUDA(cudaMemcpyAsync(out7, d_out, 7 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     if (stats) LO_CUDA(cudaMemcpyAsync(stats, d_stats, sizeof(lo_align_stats), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (getenv("LO_ALIGN_TRACE")) {  // developer aid: phase timeline of block 0 in SM clocks
+        static long long h[1001];
+        LO_CUDA(cudaMemcpy(h, ctx->tmp_d.p, sizeof(h), cudaMemcpyDeviceToHost));
+        for (long long k = 1; k < h[1000]; k++) fprintf(stderr, "trace %lld %lld\n", h[2 * k], h[2 * k + 1] - h[2 * (k - 1) + 1]);
+    }
     return LO_OK;
 }
 
