@@ -16,7 +16,7 @@
 //   ceres::Solve                             mini_ceres.h (third-party, absent: PARITY UNPINNED for that part)
 //   PCL NormalEstimation (test only)         orc_pca_normals below (third-party, absent: PARITY UNPINNED)
 //
-// Pinning: tests/test_oracle_vs_ref.py compares every function below with oracle/_ref/liblo_ref.so (the
+// Pinning: tests/test_oracle_cpu.py compares every function below with oracle/_ref/liblo_ref.so (the
 // reference's own headers compiled from /root/reference) bit for bit on randomised inputs, and
 // tests/golden/ holds vectors generated from that library. Float evaluation orders follow Eigen 3.4 as
 // documented in oracle/shim/eigen3/Eigen/Eigen (unverifiable here: Eigen is not installed).

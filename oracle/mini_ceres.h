@@ -15,7 +15,7 @@
 // residual_block.cc, corrector.cc, loss_function.cc, manifold.cc/QuaternionPlusImpl, normal_prior.cc,
 // trust_region_step_evaluator.cc) from knowledge of that code. It could not be diffed against a Ceres
 // build. The reference's only test of this path is CloudMatcher.MatchingTest (test/test.cpp:191-264,
-// 0.05 m / 0.01), which the oracle satisfies on the substitute fixture (tests/test_oracle_matching.py).
+// 0.05 m / 0.01), which the oracle satisfies on the substitute fixture (tests/test_oracle_cpu.py::test_golden_config1).
 #ifndef LO_ORACLE_MINI_CERES_H
 #define LO_ORACLE_MINI_CERES_H
 
