@@ -2,28 +2,12 @@
 // enqueued on the context's stream, poses and counts stay in device memory, and the host synchronises once
 // per scan to read back the pose and the per-scan counters (28 + 64 bytes).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
-#include "lo_points.cuh"
+#include "lo_odometry.cuh"
 
 namespace lo {
-
-struct OdomDev {          // device-resident state of one LidarOdometry
-    Pose previous;        // previous_transform_  (lidar_odometry.h:84)
-    Pose current;         // current_transform_   (lidar_odometry.h:85)
-    Pose relative, relative_inv, guess, next, identity;
-    float center[4];      // current translation for radiusCleanup
-    uint32_t n_planar, n_update, n_query, unstable;
-    uint32_t pad[4];
-    lo_align_stats align;
-};
-
-__device__ inline Pose identity_pose() {
-    Pose p;
-    p.t[0] = p.t[1] = p.t[2] = 0.f;
-    p.w = 1.f; p.x = p.y = p.z = 0.f;
-    return p;
-}
 
 __global__ void odom_init_kernel(OdomDev* s) {
     s->previous = identity_pose();
@@ -86,14 +70,9 @@ __global__ void odom_gate_kernel(OdomDev* s, float threshold) {
     s->center[0] = out.t[0]; s->center[1] = out.t[1]; s->center[2] = out.t[2];
 }
 
-struct ScanReadback {   // one D2H per scan
-    float pose[7];
-    uint32_t n_planar, n_update, n_query, unstable;
-    int32_t outer_iterations;
-    uint32_t kf_counters[GC_COUNT];
-};
-
-__global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counters, ScanReadback* out) {
+__global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counters, ScanReadback* out, uint32_t* minmax) {
+    minmax[0] = 0xFFFFFFFFu;  // re-arm the time min/max of the fused pipeline's next scan
+    minmax[1] = 0u;
     pose_to7(s->current, out->pose);
     out->n_planar = s->n_planar;
     out->n_update = s->n_update;
@@ -107,20 +86,11 @@ __global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counte
 
 using namespace lo;
 
-struct lo_odometry {
-    lo_ctx* ctx = nullptr;
-    lo_params params;
-    lo_grid* keyframe = nullptr;
-    lo_grid* update_ds = nullptr;    // VoxelGrid(keyframe_update_voxel_size, 1)   lidar_odometry.cpp:37
-    lo_grid* match_ds = nullptr;     // VoxelGrid(keyframe_matching_voxel_size, 1) lidar_odometry.cpp:46
-    OdomDev* d_state = nullptr;
-    ScanReadback* d_readback = nullptr;
-    ScanReadback* h_readback = nullptr;  // pinned
-    DevBuf scan, deskewed, filtered, update, query;
-    uint32_t n_last = 0;             // points in the deskewed cloud
-    lo_scan_stats stats;
-    float pose[7] = {0, 0, 0, 1, 0, 0, 0};
-};
+int lo::odom_gate_enqueue(lo_odometry* h) {
+    odom_gate_kernel<<<1, 1, 0, h->ctx->stream>>>(h->d_state, h->params.angular_divergence_threshold);
+    LO_LAUNCHED(h->ctx);
+    return LO_OK;
+}
 
 static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P) {
     lo_ctx* ctx = h->ctx;
@@ -153,7 +123,7 @@ static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P
 
 static int finish_scan(lo_odometry* h, uint32_t n_points) {
     lo_ctx* ctx = h->ctx;
-    odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback);
+    odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
     LO_LAUNCHED(ctx);
     LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -196,6 +166,9 @@ extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odome
     LO_CUDA(cudaMemsetAsync(h->d_state, 0, sizeof(OdomDev), ctx->stream));
     LO_CUDA(cudaMalloc(&h->d_readback, sizeof(ScanReadback)));
     LO_CUDA(cudaMallocHost(&h->h_readback, sizeof(ScanReadback)));
+    LO_CUDA(cudaMalloc(&h->d_minmax, 2 * sizeof(uint32_t)));
+    const uint32_t minmax_init[2] = {0xFFFFFFFFu, 0u};
+    LO_CUDA(cudaMemcpyAsync(h->d_minmax, minmax_init, sizeof(minmax_init), cudaMemcpyHostToDevice, ctx->stream));
     odom_init_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state);
     LO_LAUNCHED(ctx);
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -213,6 +186,8 @@ extern "C" void lo_odometry_destroy(lo_odometry* h) {
     if (h->d_state) cudaFree(h->d_state);
     if (h->d_readback) cudaFree(h->d_readback);
     if (h->h_readback) cudaFreeHost(h->h_readback);
+    if (h->d_minmax) cudaFree(h->d_minmax);
+    fused_release(h);
     for (DevBuf* b : {&h->scan, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
     delete h;
 }
@@ -223,6 +198,15 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
     LO_CUDA(cudaSetDevice(ctx->device));
     OdomDev* s = h->d_state;
     const uint32_t nn = static_cast<uint32_t>(n);
+    static const bool staged = getenv("LO_B200_STAGED") != nullptr;  // developer switch: stage-by-stage pipeline
+    if (!staged && nn <= kFusedMaxPoints) {
+        h->n_last = nn;
+        LO_TRY(fused_process_enqueue(h, static_cast<const PointXYZIRT*>(d_xyzirt32), nn));
+        const uint32_t ticket_after = h->keyframe->h_counters[GC_TICKET];
+        const int st = finish_scan(h, nn);
+        preserve_ticket(h->keyframe, ticket_after);
+        return st;
+    }
     const uint32_t kf_ticket = h->keyframe->h_counters[GC_TICKET];
     LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
     LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));

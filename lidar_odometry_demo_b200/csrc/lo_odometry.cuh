@@ -1,0 +1,60 @@
+// Shared between lo_odometry.cu (entry points, generic stage-by-stage pipeline) and lo_pipeline.cu (the fused
+// per-scan pipeline): device-resident odometry state and the lo_odometry object.
+#pragma once
+
+#include "lo_points.cuh"
+
+namespace lo {
+
+struct OdomDev {          // device-resident state of one LidarOdometry
+    Pose previous;        // previous_transform_  (lidar_odometry.h:84)
+    Pose current;         // current_transform_   (lidar_odometry.h:85)
+    Pose relative, relative_inv, guess, next, identity;
+    float center[4];      // current translation for radiusCleanup
+    uint32_t n_planar, n_update, n_query, unstable;
+    uint32_t pad[4];
+    lo_align_stats align;
+};
+
+__device__ inline Pose identity_pose() {
+    Pose p;
+    p.t[0] = p.t[1] = p.t[2] = 0.f;
+    p.w = 1.f; p.x = p.y = p.z = 0.f;
+    return p;
+}
+
+struct ScanReadback {   // one D2H per scan
+    float pose[7];
+    uint32_t n_planar, n_update, n_query, unstable;
+    int32_t outer_iterations;
+    uint32_t kf_counters[GC_COUNT];
+};
+
+}  // namespace lo
+
+struct lo_odometry {
+    lo_ctx* ctx = nullptr;
+    lo_params params;
+    lo_grid* keyframe = nullptr;
+    lo_grid* update_ds = nullptr;    // VoxelGrid(keyframe_update_voxel_size, 1)   lidar_odometry.cpp:37
+    lo_grid* match_ds = nullptr;     // VoxelGrid(keyframe_matching_voxel_size, 1) lidar_odometry.cpp:46
+    lo::OdomDev* d_state = nullptr;
+    lo::ScanReadback* d_readback = nullptr;
+    lo::ScanReadback* h_readback = nullptr;  // pinned
+    lo::DevBuf scan, deskewed, filtered, update, query;
+    lo::DevBuf fused;                // scratch of the fused pipeline (lo_pipeline.cu)
+    uint32_t* d_minmax = nullptr;    // [2] ordered min / max of `time`, re-armed by the read-back kernel
+    uint32_t n_last = 0;             // points in the deskewed cloud
+    lo_scan_stats stats;
+    float pose[7] = {0, 0, 0, 1, 0, 0, 0};
+};
+
+
+namespace lo {
+// lo_pipeline.cu: LidarOdometry::processCloud with the per-scan stages fused into ~16 launches. Requires
+// n <= kFusedMaxPoints; returns LO_OK after enqueueing everything up to (not including) the read-back.
+constexpr uint32_t kFusedMaxPoints = 32768;
+int fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n);
+void fused_release(lo_odometry* h);
+int odom_gate_enqueue(lo_odometry* h);   // lo_odometry.cu: the divergence gate of lidar_odometry.cpp:53-65
+}  // namespace lo

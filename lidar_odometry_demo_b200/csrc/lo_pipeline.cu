@@ -1,0 +1,571 @@
+// LidarOdometry::processCloud (src/lidar_odometry.cpp:22-76) as a fused device pipeline for scans of up to
+// kFusedMaxPoints points (a VLP16 revolution is ~30 k): the stages in front of and behind CloudMatcher::align
+// are folded into a dozen launches. Per scan, in stream order:
+//
+//   P1 prep        constant-velocity prediction (cpp:27-28,51) | min/max of `time` | zero classifier cells |
+//                  clear the two down-sampler tables
+//   P2 deskew      pointTimeNormalize + transformNonRigid (cpp:25,30) | ring histogram of the classifier
+//   P3 cell_fill   classifier grid: ring x azimuth bin, last writer wins (cloud_classifier.h:21-71)
+//   P4 curvature   gather cell points + LOAM curvature (cloud_classifier.h:81-105)
+//   P5 planar      planar test + normals (cloud_classifier.h:107-165) fused with rangeFilter (cpp:35) -> flags, block counts
+//   P6 scatter     ordered compaction into the filtered planar cloud | insert every point into both
+//                  VoxelGrid(vs,1) down-samplers (cpp:37-38,46-47): find-or-create voxel, atomicMin of the arrival index
+//   P7 select      which points are the first of their voxel (winners), block counts
+//   P8 emit        query cloud M (arrival order) | list of update winners U with their robin_map bucket
+//   P9 robin       one block: the update set in the reference's tsl::robin_map iteration order
+//   align_kernel   CloudMatcher::align (lo_match.cu)
+//   gate, clean-up, key-frame insert (cpp:53-70) and the read-back as in lo_odometry.cu
+//
+// Every per-point formula is the shared code of lo_stages.cuh, so the fused and the stage-by-stage paths
+// (lo_points.cu, lo_grid.cu) produce identical bits; tests/test_gpu_pipeline.py runs both against the oracle.
+#include <algorithm>
+#include <cstring>
+
+#include "lo_odometry.cuh"
+#include "lo_stages.cuh"
+
+namespace lo {
+
+constexpr int kPipeThreads = 256;
+constexpr uint32_t kMaxPipeBlocks = 512;   // upper bound of the chunked grids (block_counts rows)
+
+struct alignas(16) DsSlot {                // slot of a VoxelGrid(vs, 1) down-sampler: the voxel's first point
+    unsigned long long key;                // packed voxel key or kKeyEmpty
+    uint32_t ticket;                       // smallest arrival index (position in the filtered cloud) seen so far
+    uint32_t pad;
+};
+
+struct PipeBufs {                          // carved out of lo_odometry::fused
+    uint32_t* hist;                        // [256] ring populations
+    uint32_t* layout;                      // [4]   W, H, overflow, W*H
+    uint32_t* block_counts;                // [3][kMaxPipeBlocks] planar / U winners / M winners per block
+    uint32_t* cell_idx;                    // [cell_cap] 1 + index of the point that owns the cell
+    float* curv;                           // [cell_cap]
+    float4* cellp;                         // [cell_cap] x,y,z,intensity of the cell's point
+    float4* cnormal;                       // [cell_cap] normal, w = 1 if the cell is planar and in range
+    DsSlot* ds_u;                          // [ds_cap] keyframe_downsampler   (cpp:37)
+    DsSlot* ds_m;                          // [ds_cap] matching_downsampler   (cpp:46)
+    uint32_t* slot_u;                      // [n] slot of filtered point i in ds_u
+    uint32_t* slot_m;                      // [n]
+    uint32_t* ulist;                       // [n] update winners (index into filtered), arrival order
+    uint32_t* ubucket;                     // [n] their ideal robin_map bucket
+    uint32_t* usorted;                     // [n] scratch of P9
+    uint32_t cell_cap, ds_cap;
+};
+
+static size_t carve(PipeBufs& b, char* base, uint32_t n) {
+    b.cell_cap = std::max<uint32_t>(8u * n, 65536u);
+    uint32_t cap = 1024;
+    while (cap < 2u * n) cap <<= 1;
+    b.ds_cap = cap;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        char* p = base ? base + off : nullptr;
+        off += (bytes + 255) & ~static_cast<size_t>(255);
+        return p;
+    };
+    b.hist = reinterpret_cast<uint32_t*>(take(256 * 4));
+    b.layout = reinterpret_cast<uint32_t*>(take(16));
+    b.block_counts = reinterpret_cast<uint32_t*>(take(3 * kMaxPipeBlocks * 4));
+    b.cell_idx = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(b.cell_cap) * 4));
+    b.curv = reinterpret_cast<float*>(take(static_cast<size_t>(b.cell_cap) * 4));
+    b.cellp = reinterpret_cast<float4*>(take(static_cast<size_t>(b.cell_cap) * 16));
+    b.cnormal = reinterpret_cast<float4*>(take(static_cast<size_t>(b.cell_cap) * 16));
+    b.ds_u = reinterpret_cast<DsSlot*>(take(static_cast<size_t>(b.ds_cap) * 16));
+    b.ds_m = reinterpret_cast<DsSlot*>(take(static_cast<size_t>(b.ds_cap) * 16));
+    b.slot_u = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.slot_m = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.ulist = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.ubucket = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.usorted = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    return off;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// P1. One thread does the pose prediction; everybody reduces min/max(time) and clears scratch.
+__global__ void __launch_bounds__(kPipeThreads) pipe_prep_kernel(OdomDev* s, const PointXYZIRT* __restrict__ in, uint32_t n,
+                                                                  uint32_t* __restrict__ minmax, PipeBufs b) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    if (tid == 0) {  // lidar_odometry.cpp:27-30,51
+        const Pose rel = pose_relative_to(s->previous, s->current);
+        s->previous = s->current;
+        s->relative = rel;
+        s->relative_inv = pose_inverse(rel);
+        s->guess = pose_compose(s->current, rel);
+        s->unstable = 0;
+        s->n_planar = s->n_update = s->n_query = 0;
+        s->align.outer_iterations = 0;
+    }
+    uint32_t lo_v = 0xFFFFFFFFu, hi_v = 0u;
+    for (uint32_t i = tid; i < n; i += nthreads) {
+        const float t = in[i].time;
+        if (t == t) {  // std::min / std::max keep the running value when the operand is NaN
+            const uint32_t o = float_to_ordered(t);
+            lo_v = min(lo_v, o);
+            hi_v = max(hi_v, o);
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        lo_v = min(lo_v, __shfl_xor_sync(0xFFFFFFFFu, lo_v, off));
+        hi_v = max(hi_v, __shfl_xor_sync(0xFFFFFFFFu, hi_v, off));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(&minmax[0], lo_v);
+        atomicMax(&minmax[1], hi_v);
+    }
+    if (tid < 256) b.hist[tid] = 0;
+    for (uint32_t c = tid; c < b.cell_cap; c += nthreads) b.cell_idx[c] = 0;
+    const uint4 empty = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+    uint4* u = reinterpret_cast<uint4*>(b.ds_u);
+    uint4* m = reinterpret_cast<uint4*>(b.ds_m);
+    for (uint32_t c = tid; c < b.ds_cap; c += nthreads) {
+        u[c] = empty;
+        m[c] = empty;
+    }
+}
+
+// P2. deskew + ring histogram (the reference keys its ring map by uint8_t, cloud_classifier.h:21-23)
+__global__ void __launch_bounds__(kPipeThreads) pipe_deskew_kernel(const OdomDev* __restrict__ s, const PointXYZIRT* __restrict__ in, uint32_t n,
+                                                                    const uint32_t* __restrict__ minmax, PointXYZIRT* __restrict__ out,
+                                                                    uint32_t* __restrict__ hist) {
+    __shared__ uint32_t local[256];
+    local[threadIdx.x] = 0;  // blockDim.x == 256
+    __syncthreads();
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const Pose st = s->relative_inv, en = s->identity;   // transformNonRigid(cloud, relative.inverse(), Pose3D()) cpp:30
+        const float t_min = time_min_of(minmax), t_max = time_max_of(minmax);
+        const float4 a = reinterpret_cast<const float4*>(in)[2 * i];
+        float4 bb = reinterpret_cast<const float4*>(in)[2 * i + 1];
+        const float4 o = deskew_point(st, en, t_min, t_max - t_min, a, bb);
+        reinterpret_cast<float4*>(out)[2 * i] = o;
+        reinterpret_cast<float4*>(out)[2 * i + 1] = bb;
+        atomicAdd(&local[__float_as_uint(bb.y) & 0xFF], 1u);   // ring is the low 16 bits of the second word
+    }
+    __syncthreads();
+    if (local[threadIdx.x]) atomicAdd(&hist[threadIdx.x], local[threadIdx.x]);
+}
+
+// Block-wide layout of the classifier grid from the ring histogram: W = largest ring population, row of ring r =
+// number of populated rings below r (std::map order), H = populated rings. Needs blockDim.x == 256.
+__device__ inline void block_layout(const uint32_t* __restrict__ hist, uint32_t* row_of_s, uint32_t* wh_s) {
+    __shared__ uint32_t warp_cnt[8], warp_max[8];
+    const uint32_t c = hist[threadIdx.x];
+    const unsigned present = __ballot_sync(0xFFFFFFFFu, c != 0);
+    uint32_t mx = c;
+    for (int off = 16; off > 0; off >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        warp_cnt[warp] = __popc(present);
+        warp_max[warp] = mx;
+    }
+    __syncthreads();
+    uint32_t before = 0, total = 0, width = 0;
+    for (int w = 0; w < 8; w++) {
+        if (w < warp) before += warp_cnt[w];
+        total += warp_cnt[w];
+        width = max(width, warp_max[w]);
+    }
+    row_of_s[threadIdx.x] = before + __popc(present & ((1u << lane) - 1u));
+    if (threadIdx.x == 0) {
+        wh_s[0] = width;
+        wh_s[1] = total;
+    }
+    __syncthreads();
+}
+
+// P3. cloud_classifier.h:44-56: cell (ring row, azimuth bin) <- point, last writer (largest input index) wins
+__global__ void __launch_bounds__(kPipeThreads) pipe_cell_fill_kernel(const PointXYZIRT* __restrict__ desk, uint32_t n, PipeBufs b) {
+    __shared__ uint32_t row_of[256], wh[2];
+    block_layout(b.hist, row_of, wh);
+    const uint32_t W = wh[0], H = wh[1];
+    const bool overflow = static_cast<unsigned long long>(W) * H > b.cell_cap;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        b.layout[0] = W;
+        b.layout[1] = H;
+        b.layout[2] = overflow ? 1u : 0u;
+        b.layout[3] = overflow ? 0u : W * H;
+    }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || overflow) return;
+    const float4 a = reinterpret_cast<const float4*>(desk)[2 * i];
+    const uint32_t ring = desk[i].ring & 0xFF;
+    uint32_t col;
+    if (!azimuth_column(a.x, a.y, W, col)) return;
+    atomicMax(&b.cell_idx[row_of[ring] * W + col], i + 1);
+}
+
+__device__ inline float4 cell_point(const PointXYZIRT* __restrict__ desk, const uint32_t* __restrict__ cell_idx, uint32_t c) {
+    const uint32_t idx = cell_idx[c];
+    if (!idx) return make_float4(0.f, 0.f, 0.f, 0.f);  // PointType(): value-initialised
+    const float4 a = reinterpret_cast<const float4*>(desk)[2 * (idx - 1)];
+    const float4 bb = reinterpret_cast<const float4*>(desk)[2 * (idx - 1) + 1];
+    return make_float4(a.x, a.y, a.z, bb.x);
+}
+
+// P4. gather + curvature
+__global__ void __launch_bounds__(kPipeThreads) pipe_curvature_kernel(const PointXYZIRT* __restrict__ desk, PipeBufs b) {
+    const uint32_t total = b.layout[3];
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < total; c += gridDim.x * blockDim.x) {
+        b.cellp[c] = cell_point(desk, b.cell_idx, c);
+        b.curv[c] = cell_curvature(c, total, [&](uint32_t k) { return cell_point(desk, b.cell_idx, k); });
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Ordered (stable) compaction in two passes over contiguous per-block chunks: pass A counts the kept items of
+// each block, pass B adds the counts of the preceding blocks and ranks inside the block.
+__device__ inline void chunk_range(uint32_t total, uint32_t& begin, uint32_t& end) {
+    uint32_t per = (total + gridDim.x - 1) / gridDim.x;
+    per = (per + blockDim.x - 1) / blockDim.x * blockDim.x;  // whole tiles of blockDim.x items
+    begin = min(total, blockIdx.x * per);
+    end = min(total, begin + per);
+}
+
+// sum of counts[0..blockIdx.x) and of all gridDim.x counts; result valid in every thread
+__device__ inline void block_prefix(const uint32_t* __restrict__ counts, uint32_t& before, uint32_t& all) {
+    __shared__ uint32_t sh[2];
+    if (threadIdx.x < 32) {
+        uint32_t b = 0, a = 0;
+        for (uint32_t k = threadIdx.x; k < gridDim.x; k += 32) {
+            const uint32_t v = counts[k];
+            a += v;
+            if (k < blockIdx.x) b += v;
+        }
+        for (int off = 16; off > 0; off >>= 1) {
+            b += __shfl_xor_sync(0xFFFFFFFFu, b, off);
+            a += __shfl_xor_sync(0xFFFFFFFFu, a, off);
+        }
+        if (threadIdx.x == 0) {
+            sh[0] = b;
+            sh[1] = a;
+        }
+    }
+    __syncthreads();
+    before = sh[0];
+    all = sh[1];
+    __syncthreads();
+}
+
+// number of threads with flag set before this thread in the block, and the block's total (blockDim.x == 256)
+__device__ inline uint32_t block_rank(bool flag, uint32_t& tile_total) {
+    __shared__ uint32_t warp_cnt[8];
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, flag);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warp_cnt[warp] = __popc(m);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+    for (int w = 0; w < 8; w++) {
+        if (w < warp) before += warp_cnt[w];
+        total += warp_cnt[w];
+    }
+    __syncthreads();
+    tile_total = total;
+    return before + __popc(m & ((1u << lane) - 1u));
+}
+
+// P5. planar test + normal + range filter -> cnormal.w flag, per-block counts
+__global__ void __launch_bounds__(kPipeThreads) pipe_planar_kernel(PipeBufs b, float lo2, float hi2) {
+    const uint32_t total = b.layout[3], W = b.layout[0];
+    uint32_t begin, end;
+    chunk_range(total, begin, end);
+    uint32_t count = 0;
+    for (uint32_t base = begin; base < end; base += blockDim.x) {
+        const uint32_t c = base + threadIdx.x;
+        bool flag = false;
+        if (c < end) {
+            float nv[3] = {0.f, 0.f, 0.f};
+            if (cell_planar(c, W, b.cellp, b.curv, nv)) {
+                const float4 p = b.cellp[c];
+                flag = in_range(p.x, p.y, p.z, lo2, hi2);
+            }
+            b.cnormal[c] = make_float4(nv[0], nv[1], nv[2], flag ? 1.f : 0.f);
+        }
+        count += __syncthreads_count(flag);
+    }
+    if (threadIdx.x == 0) b.block_counts[blockIdx.x] = count;
+}
+
+// find-or-create the voxel of (x,y,z) in a down-sampler table and record arrival index `pos`; returns the slot
+__device__ inline uint32_t ds_insert(DsSlot* __restrict__ slots, uint32_t mask, float voxel_size, float x, float y, float z, uint32_t pos,
+                                     uint32_t* __restrict__ range_err) {
+    const long long ix = axis_index(x, voxel_size), iy = axis_index(y, voxel_size), iz = axis_index(z, voxel_size);
+    if (!axis_in_range(ix) || !axis_in_range(iy) || !axis_in_range(iz)) {
+        *range_err = 1;
+        return 0xFFFFFFFFu;
+    }
+    const unsigned long long key = pack_key(ix, iy, iz);
+    uint32_t h = probe_hash(key) & mask;
+    while (true) {
+        unsigned long long k = slots[h].key;
+        if (k == kKeyEmpty) k = atomicCAS(&slots[h].key, kKeyEmpty, key);
+        if (k == kKeyEmpty || k == key) break;
+        h = (h + 1) & mask;
+    }
+    atomicMin(&slots[h].ticket, pos);   // VoxelGrid(vs,1): the first arrival owns the voxel (voxel_grid.h:82-91)
+    return h;
+}
+
+// P6. filtered planar cloud in cell order (cloud_classifier.h:114-165 walks rays then columns) + both down-samplers
+__global__ void __launch_bounds__(kPipeThreads) pipe_scatter_kernel(OdomDev* s, PipeBufs b, PointNormal* __restrict__ filtered, float vs_u,
+                                                                     float vs_m, int with_match, uint32_t* __restrict__ range_err) {
+    const uint32_t total = b.layout[3];
+    uint32_t begin, end, before, all;
+    chunk_range(total, begin, end);
+    block_prefix(b.block_counts, before, all);
+    if (blockIdx.x == 0 && threadIdx.x == 0) s->n_planar = all;
+    uint32_t running = before;
+    for (uint32_t base = begin; base < end; base += blockDim.x) {
+        const uint32_t c = base + threadIdx.x;
+        float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < end) nv = b.cnormal[c];
+        const bool flag = nv.w != 0.f;
+        uint32_t tile_total;
+        const uint32_t pos = running + block_rank(flag, tile_total);
+        running += tile_total;
+        if (flag) {
+            const float4 p = b.cellp[c];
+            float4* o = reinterpret_cast<float4*>(filtered + pos);
+            o[0] = make_float4(p.x, p.y, p.z, 1.f);
+            o[1] = make_float4(nv.x, nv.y, nv.z, 0.f);
+            o[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+            b.slot_u[pos] = ds_insert(b.ds_u, b.ds_cap - 1, vs_u, p.x, p.y, p.z, pos, range_err);
+            if (with_match) b.slot_m[pos] = ds_insert(b.ds_m, b.ds_cap - 1, vs_m, p.x, p.y, p.z, pos, range_err);
+        }
+    }
+}
+
+// P7. winners of the two down-samplers, per-block counts
+__global__ void __launch_bounds__(kPipeThreads) pipe_select_kernel(PipeBufs b, int with_match) {
+    uint32_t before, total;
+    block_prefix(b.block_counts, before, total);   // total = n_planar
+    uint32_t begin, end;
+    chunk_range(total, begin, end);
+    uint32_t cu = 0, cm = 0;
+    for (uint32_t base = begin; base < end; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        bool wu = false, wm = false;
+        if (i < end) {
+            const uint32_t su = b.slot_u[i];
+            wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+            if (with_match) {
+                const uint32_t sm = b.slot_m[i];
+                wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
+            }
+        }
+        cu += __syncthreads_count(wu);
+        cm += __syncthreads_count(wm);
+    }
+    if (threadIdx.x == 0) {
+        b.block_counts[kMaxPipeBlocks + blockIdx.x] = cu;
+        b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
+    }
+}
+
+__device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map after n insertions: 2 * pow2ceil(n)
+    uint32_t c = 2;
+    while (c < 2 * n) c <<= 1;
+    return c;
+}
+
+// P8. query cloud (matching_downsampler.getCloudWithoutNormals(), cpp:50 — emitted in arrival order: its order only
+// decides the order of the residual sum) and the update winners with their ideal robin_map bucket
+__global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
+                                                                  PointXYZ* __restrict__ query, int with_match) {
+    uint32_t before, total, bu, nu, bm, nm;
+    block_prefix(b.block_counts, before, total);
+    block_prefix(b.block_counts + kMaxPipeBlocks, bu, nu);
+    block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        s->n_update = nu;
+        s->n_query = nm;
+    }
+    const uint32_t buckets = robin_bucket_count(nu);
+    uint32_t begin, end;
+    chunk_range(total, begin, end);
+    for (uint32_t base = begin; base < end; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        bool wu = false, wm = false;
+        uint32_t su = 0;
+        if (i < end) {
+            su = b.slot_u[i];
+            wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+            if (with_match) {
+                const uint32_t sm = b.slot_m[i];
+                wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
+            }
+        }
+        uint32_t tu, tm;
+        const uint32_t ru = block_rank(wu, tu), rm = block_rank(wm, tm);
+        if (wu) {
+            long long ix, iy, iz;
+            unpack_key(b.ds_u[su].key, ix, iy, iz);
+            b.ulist[bu + ru] = i;
+            b.ubucket[bu + ru] = reference_hash22(ix, iy, iz) & (buckets - 1);
+        }
+        if (wm) {
+            const float4 p = *reinterpret_cast<const float4*>(filtered + i);
+            reinterpret_cast<float4*>(query)[bm + rm] = make_float4(p.x, p.y, p.z, 1.f);
+        }
+        bu += tu;
+        bm += tm;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// P9. keyframe_downsampler.getCloud() (cpp:38,42,69): the update set in tsl::robin_map iteration order, by one
+// block with the bucket array in shared memory. For n inserted keys the map has C = 2*pow2ceil(n) buckets;
+// iteration is ascending bucket position; robin-hood probing keeps elements sorted by ideal bucket
+// b = hash22 & (C-1); a cluster that runs past the last bucket wraps to the front (lo_robin.cu states the same
+// rule for the stage-by-stage path). Counting sort by b: per-bucket counters (16 bit, two per word), exclusive
+// scan, placement, then each tie group is ordered by arrival.
+constexpr int kRobinThreads = 1024;
+
+__device__ inline uint32_t half_of(uint32_t word, uint32_t b) { return (b & 1u) ? (word >> 16) : (word & 0xFFFFu); }
+
+__global__ void __launch_bounds__(kRobinThreads, 1) pipe_robin_kernel(const OdomDev* __restrict__ s, PipeBufs b,
+                                                                       const PointNormal* __restrict__ filtered, PointNormal* __restrict__ update) {
+    extern __shared__ uint32_t sm[];
+    __shared__ uint32_t scan_sh[kRobinThreads / 32];
+    __shared__ int shift_sh[kRobinThreads / 32];
+    const uint32_t n = s->n_update;
+    if (n == 0) return;
+    const uint32_t C = robin_bucket_count(n);
+    const uint32_t words = C / 2;                    // C >= 2
+    uint32_t* cnt = sm;                              // [words] two 16-bit counters per word
+    unsigned short* tmp = reinterpret_cast<unsigned short*>(sm + words);  // [n] placement (index into ulist)
+    const uint32_t tid = threadIdx.x;
+    for (uint32_t w = tid; w < words; w += kRobinThreads) cnt[w] = 0;
+    __syncthreads();
+    for (uint32_t j = tid; j < n; j += kRobinThreads) {
+        const uint32_t bk = b.ubucket[j];
+        atomicAdd(&cnt[bk >> 1], (bk & 1u) ? 0x10000u : 1u);
+    }
+    __syncthreads();
+    // exclusive scan over the C counters: thread t owns words [t*wpt, (t+1)*wpt)
+    const uint32_t wpt = (words + kRobinThreads - 1) / kRobinThreads;
+    const uint32_t w0 = min(words, tid * wpt), w1 = min(words, w0 + wpt);
+    uint32_t local = 0;
+    for (uint32_t w = w0; w < w1; w++) local += (cnt[w] & 0xFFFFu) + (cnt[w] >> 16);
+    uint32_t incl = local;
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+        if (lane >= off) incl += v;
+    }
+    if (lane == 31) scan_sh[warp] = incl;
+    __syncthreads();
+    uint32_t warp_before = 0;
+    for (int w = 0; w < warp; w++) warp_before += scan_sh[w];
+    uint32_t run = warp_before + incl - local;
+    for (uint32_t w = w0; w < w1; w++) {
+        const uint32_t lo_c = cnt[w] & 0xFFFFu, hi_c = cnt[w] >> 16;
+        cnt[w] = (run & 0xFFFFu) | (((run + lo_c) & 0xFFFFu) << 16);   // start of bucket 2w, 2w+1 (n <= 32768 < 65536)
+        run += lo_c + hi_c;
+    }
+    __syncthreads();
+    // placement: the counter of bucket b advances from its start to its end (= start of bucket b+1)
+    for (uint32_t j = tid; j < n; j += kRobinThreads) {
+        const uint32_t bk = b.ubucket[j];
+        const uint32_t old = atomicAdd(&cnt[bk >> 1], (bk & 1u) ? 0x10000u : 1u);
+        tmp[half_of(old, bk)] = static_cast<unsigned short>(j);
+    }
+    __syncthreads();
+    // order every tie group by arrival (ulist is in arrival order, so by j)
+    for (uint32_t p = tid; p < n; p += kRobinThreads) {
+        const uint32_t j = tmp[p];
+        const uint32_t bk = b.ubucket[j];
+        const uint32_t seg_end = half_of(cnt[bk >> 1], bk);
+        const uint32_t seg_begin = bk == 0 ? 0u : half_of(cnt[(bk - 1) >> 1], bk - 1);
+        uint32_t rank = 0;
+        for (uint32_t q = seg_begin; q < seg_end; q++) rank += tmp[q] < j ? 1u : 0u;
+        b.usorted[seg_begin + rank] = j;
+    }
+    __syncthreads();
+    // wrap: sorted element i sits at bucket position i + max_{k<=i}(b_k - k); the last one at n-1+max_shift; positions
+    // >= C wrap to the front of the bucket array and are therefore iterated first
+    int shift = INT_MIN;
+    for (uint32_t p = tid; p < n; p += kRobinThreads) shift = max(shift, static_cast<int>(b.ubucket[b.usorted[p]]) - static_cast<int>(p));
+    for (int off = 16; off > 0; off >>= 1) shift = max(shift, __shfl_xor_sync(0xFFFFFFFFu, shift, off));
+    if (lane == 0) shift_sh[warp] = shift;
+    __syncthreads();
+    int max_shift = INT_MIN;
+    for (int w = 0; w < kRobinThreads / 32; w++) max_shift = max(max_shift, shift_sh[w]);
+    const long long over = static_cast<long long>(n) + max_shift - static_cast<long long>(C);
+    const uint32_t rot = over > 0 ? static_cast<uint32_t>(over) : 0u;
+    for (uint32_t p = tid; p < n; p += kRobinThreads) {
+        const uint32_t dst = (p + rot) % n;
+        const float4* src = reinterpret_cast<const float4*>(filtered + b.ulist[b.usorted[p]]);
+        float4* o = reinterpret_cast<float4*>(update + dst);
+        o[0] = src[0];
+        o[1] = src[1];
+        o[2] = src[2];
+    }
+}
+
+}  // namespace lo
+
+using namespace lo;
+
+int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
+    lo_ctx* ctx = h->ctx;
+    OdomDev* s = h->d_state;
+    PipeBufs b;
+    const size_t bytes = carve(b, nullptr, n);
+    LO_TRY(h->fused.ensure(bytes));
+    carve(b, h->fused.as<char>(), n);
+    LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
+    LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
+    LO_TRY(h->update.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
+    LO_TRY(h->query.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZ)));
+    const bool first = h->keyframe->h_counters[GC_VOXELS] == 0;  // cpp:40 (host mirror from the last scan's read-back)
+    const int with_match = first ? 0 : 1;
+    const unsigned G = std::min<unsigned>(static_cast<unsigned>(ctx->sm_count), kMaxPipeBlocks);
+    const unsigned per_point = blocks_for(n, kPipeThreads);
+    PointXYZIRT* desk = h->deskewed.as<PointXYZIRT>();
+    PointNormal* filtered = h->filtered.as<PointNormal>();
+    const float lo2 = h->params.lidar_min_range * h->params.lidar_min_range, hi2 = h->params.lidar_max_range * h->params.lidar_max_range;
+    uint32_t* range_err = h->keyframe->counters + GC_RANGE_ERR;
+
+    pipe_prep_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, d_scan, n, h->d_minmax, b);
+    LO_LAUNCHED(ctx);
+    if (n == 0) return LO_OK;
+    pipe_deskew_kernel<<<per_point, kPipeThreads, 0, ctx->stream>>>(s, d_scan, n, h->d_minmax, desk, b.hist);
+    LO_LAUNCHED(ctx);
+    pipe_cell_fill_kernel<<<per_point, kPipeThreads, 0, ctx->stream>>>(desk, n, b);
+    LO_LAUNCHED(ctx);
+    pipe_curvature_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(desk, b);
+    LO_LAUNCHED(ctx);
+    pipe_planar_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(b, lo2, hi2);
+    LO_LAUNCHED(ctx);
+    pipe_scatter_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->params.keyframe_update_voxel_size,
+                                                             h->params.keyframe_matching_voxel_size, with_match, range_err);
+    LO_LAUNCHED(ctx);
+    pipe_select_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(b, with_match);
+    LO_LAUNCHED(ctx);
+    pipe_emit_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->query.as<PointXYZ>(), with_match);
+    LO_LAUNCHED(ctx);
+    uint32_t cmax = 2;
+    while (cmax < 2 * n) cmax <<= 1;
+    const size_t robin_smem = static_cast<size_t>(cmax / 2) * 4 + ((static_cast<size_t>(n) * 2 + 15) & ~static_cast<size_t>(15));
+    static bool attr_set = false;
+    if (!attr_set) {
+        LO_CUDA(cudaFuncSetAttribute(pipe_robin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    pipe_robin_kernel<<<1, kRobinThreads, robin_smem, ctx->stream>>>(s, b, filtered, h->update.as<PointNormal>());
+    LO_LAUNCHED(ctx);
+    if (first) {
+        LO_TRY(grid_add_dev(h->keyframe, h->update.p, n, 1, nullptr, &s->n_update));  // cpp:42
+        return LO_OK;
+    }
+    // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
+    LO_TRY(align_enqueue(h->keyframe, h->query.as<PointXYZ>(), n, &s->n_query, reinterpret_cast<const float*>(&s->guess),
+                         reinterpret_cast<float*>(&s->next), &s->align));
+    LO_TRY(odom_gate_enqueue(h));                                                         // cpp:53-65
+    LO_TRY(grid_cleanup_dev(h->keyframe, s->center, h->params.keyframe_cleanup_range));  // cpp:67
+    LO_TRY(grid_add_dev(h->keyframe, h->update.p, n, 1, &s->current, &s->n_update));      // cpp:69-70, transform fused into the load
+    return LO_OK;
+}
+
+void lo::fused_release(lo_odometry* h) { h->fused.release(); }

@@ -3,22 +3,14 @@
 
 #include <algorithm>
 
-#include "lo_libm.cuh"
 #include "lo_points.cuh"
+#include "lo_stages.cuh"
 
 namespace lo {
 
 // ---------------------------------------------------------------------------------------------------
 // K1: utils::pointTimeNormalize (src/utils/point_time_normalize.h:14-39) fused with
 // CloudTransformer::transformNonRigid (src/utils/cloud_transform.h:15-40).
-__device__ inline uint32_t float_to_ordered(float f) {
-    const uint32_t b = __float_as_uint(f);
-    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
-__device__ inline float ordered_to_float(uint32_t o) {
-    return __uint_as_float((o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o);
-}
-
 // minmax[0] = ordered min, minmax[1] = ordered max (initialised to 0xFFFFFFFF / 0)
 __global__ void time_minmax_kernel(const PointXYZIRT* __restrict__ in, uint32_t n, uint32_t* __restrict__ minmax) {
     uint32_t lo_v = 0xFFFFFFFFu, hi_v = 0u;
@@ -40,49 +32,16 @@ __global__ void time_minmax_kernel(const PointXYZIRT* __restrict__ in, uint32_t 
     }
 }
 
-// sinf / acosf of the reference run in glibc: restated bit for bit in lo_libm.cuh
-__device__ inline float sin_as_float(float a) { return libm::sinf_glibc(a); }
-__device__ inline float acos_as_float(float a) { return libm::acosf_fdlibm(a); }
-
 __global__ void deskew_kernel(const PointXYZIRT* __restrict__ in, uint32_t n, const uint32_t* __restrict__ minmax,
                               const Pose* __restrict__ start_p, const Pose* __restrict__ end_p, PointXYZIRT* __restrict__ out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const Pose s = *start_p, e = *end_p;
-    // numeric_limits<float>::max() / lowest() when every time was NaN (loop never updated them)
-    const float t_min = minmax[0] == 0xFFFFFFFFu ? 3.402823466e+38f : ordered_to_float(minmax[0]);
-    const float t_max = minmax[1] == 0u ? -3.402823466e+38f : ordered_to_float(minmax[1]);
-    const float range = t_max - t_min;
+    const float t_min = time_min_of(minmax), t_max = time_max_of(minmax);
     // 32-byte record as two 16-byte loads
     const float4 a = reinterpret_cast<const float4*>(in)[2 * i];
     float4 b = reinterpret_cast<const float4*>(in)[2 * i + 1];  // intensity, ring|pad, time, pad
-    const float t = (b.z - t_min) / range;
-    // Quaternionf::slerp(t, end) (Eigen 3.4)
-    const float one = 1.f - 1.1920928955078125e-07f;
-    const float d = quat_dot_f(s, e);
-    const float ad = fabsf(d);
-    float s0, s1;
-    if (ad >= one) {
-        s0 = 1.f - t;
-        s1 = t;
-    } else {
-        const float theta = acos_as_float(ad);
-        const float sin_theta = sin_as_float(theta);
-        s0 = sin_as_float((1.f - t) * theta) / sin_theta;
-        s1 = sin_as_float(t * theta) / sin_theta;
-    }
-    if (d < 0.f) s1 = -s1;
-    const float qw = s0 * s.w + s1 * e.w, qx = s0 * s.x + s1 * e.x, qy = s0 * s.y + s1 * e.y, qz = s0 * s.z + s1 * e.z;
-    const float v[3] = {a.x, a.y, a.z};
-    float r[3];
-    quat_rotate_f(qw, qx, qy, qz, v, r);
-    // start.t * time + end.t * (1.0 - time): the reference's weights; (1.0 - time) is a double
-    const float w_end = static_cast<float>(1.0 - static_cast<double>(t));
-    float4 o = a;
-    o.x = (r[0] + s.t[0] * t) + e.t[0] * w_end;
-    o.y = (r[1] + s.t[1] * t) + e.t[1] * w_end;
-    o.z = (r[2] + s.t[2] * t) + e.t[2] * w_end;
-    b.z = t;
+    const float4 o = deskew_point(s, e, t_min, t_max - t_min, a, b);
     reinterpret_cast<float4*>(out)[2 * i] = o;
     reinterpret_cast<float4*>(out)[2 * i + 1] = b;
 }
@@ -151,12 +110,6 @@ static int exclusive_scan(lo_ctx* ctx, const uint32_t* d_flags, uint32_t* d_offs
     LO_CUDA(cub::DeviceScan::ExclusiveSum(ctx->tmp_d.p, bytes, d_flags, d_offsets, static_cast<int>(n), ctx->stream));
     ctx->launches += 2;
     return LO_OK;
-}
-
-// rangeFilter (src/utils/range_filter.h:12-28): plain C++ float expression, evaluated left to right
-__device__ inline bool in_range(float x, float y, float z, float lo2, float hi2) {
-    const float r2 = x * x + y * y + z * z;
-    return r2 >= lo2 && r2 <= hi2;
 }
 
 __global__ void range_flags_kernel(const PointNormal* __restrict__ in, uint32_t n, float lo2, float hi2, uint32_t* __restrict__ flags) {
@@ -230,14 +183,8 @@ __global__ void cell_fill_kernel(const PointXYZIRT* __restrict__ in, uint32_t n,
     const uint32_t W = layout[0];
     const float4 a = reinterpret_cast<const float4*>(in)[2 * i];
     const uint32_t ring = in[i].ring & 0xFF;
-    // :49-50  float azimuth = atan2(-y, x) + pi;  index = abs(azimuth * W / (2.0 * pi))
-    const float at = libm::atan2f_fdlibm(-a.y, a.x);  // glibc atan2f, bit for bit (lo_libm.cuh)
-    const float azimuth = static_cast<float>(static_cast<double>(at) + 3.141592653589793);
-    const double scaled = static_cast<double>(azimuth * static_cast<float>(W)) / (2.0 * 3.141592653589793);
-    if (!(scaled == scaled)) return;
-    const double mag = fabs(scaled);
-    if (!(mag < static_cast<double>(W))) return;
-    const uint32_t col = static_cast<uint32_t>(mag);
+    uint32_t col;
+    if (!azimuth_column(a.x, a.y, W, col)) return;
     atomicMax(&cell_idx[row_of[ring] * W + col], i + 1);  // last writer (largest input index) wins (:52-54)
 }
 
@@ -260,27 +207,7 @@ __global__ void cell_gather_kernel(const PointXYZIRT* __restrict__ in, const uin
 __global__ void curvature_kernel(const uint32_t* __restrict__ layout, const float4* __restrict__ cellp, float* __restrict__ curv) {
     const uint32_t total = layout[2] ? 0u : layout[0] * layout[1];
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < total; c += gridDim.x * blockDim.x) {
-        const float4 p = cellp[c];
-        if (c < 4 || c + 4 >= total) {
-            curv[c] = p.w;
-            continue;
-        }
-        const float range = p.x * p.x + p.y * p.y + p.z * p.z;  // powf(v, 2) == v * v
-        if (static_cast<double>(range) < 0.1) {
-            curv[c] = 1000.0f;
-            continue;
-        }
-        float dx = static_cast<float>(static_cast<double>(-p.x) * 9.0);
-        float dy = static_cast<float>(static_cast<double>(-p.y) * 9.0);
-        float dz = static_cast<float>(static_cast<double>(-p.z) * 9.0);
-#pragma unroll
-        for (int w = -4; w <= 4; w++) {
-            const float4 q = cellp[c + w];
-            dx += q.x;
-            dy += q.y;
-            dz += q.z;
-        }
-        curv[c] = sqrtf(dx * dx + dy * dy + dz * dz) / range;
+        curv[c] = cell_curvature(c, total, [&](uint32_t k) { return cellp[k]; });
     }
 }
 
@@ -293,28 +220,11 @@ __global__ void planar_kernel(const uint32_t* __restrict__ layout, const float4*
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < cell_cap; c += gridDim.x * blockDim.x) {
         uint32_t flag = 0;
         if (c < total) {
-            const uint32_t ray = c / W, col = c % W;
-            if (ray >= 1 && col >= 4 && col + 4 < W && curv[c] < 0.05f) {
-                const double gate = static_cast<double>(0.05f) * 10.0;
-                const uint32_t prev = (ray - 1) * W;
-                int left = -1, right = -1;
-                for (uint32_t k = col - 4; k < col; k++)
-                    if (static_cast<double>(curv[prev + k]) < gate) { left = static_cast<int>(k); break; }
-                for (uint32_t k = col + 4; k > col; k--)
-                    if (static_cast<double>(curv[prev + k]) < gate) { right = static_cast<int>(k); break; }
-                if (left >= 0 && right >= 0) {
-                    const float4 p = cellp[c], l = cellp[prev + left], r = cellp[prev + right];
-                    const float a[3] = {l.x - p.x, l.y - p.y, l.z - p.z}, b[3] = {r.x - p.x, r.y - p.y, r.z - p.z};
-                    float nv[3];
-                    cross3f(a, b, nv);
-                    const float n2 = nv[0] * nv[0] + (nv[1] * nv[1] + nv[2] * nv[2]);
-                    if (n2 > 0.f) {
-                        const float len = sqrtf(n2);
-                        nv[0] /= len; nv[1] /= len; nv[2] /= len;
-                    }
-                    normals[c] = make_float4(nv[0], nv[1], nv[2], 0.f);
-                    flag = (!filter || in_range(p.x, p.y, p.z, lo2, hi2)) ? 1u : 0u;
-                }
+            float nv[3];
+            if (cell_planar(c, W, cellp, curv, nv)) {
+                const float4 p = cellp[c];
+                normals[c] = make_float4(nv[0], nv[1], nv[2], 0.f);
+                flag = (!filter || in_range(p.x, p.y, p.z, lo2, hi2)) ? 1u : 0u;
             }
         }
         flags[c] = flag;
