@@ -172,12 +172,20 @@ __host__ __device__ inline void unpack_key(unsigned long long k, long long& ix, 
     iz = static_cast<long long>(k & 0x1FFFFFull) - kAxisBias;
 }
 
-// probe hash of the device table (free choice: lookups are order independent). splitmix64 finaliser.
+// probe hash of the device table (free choice: lookups are order independent). Brick-coherent: the 2x2x2 voxels that
+// share (ix>>1, iy>>1, iz>>1) get 8 consecutive home slots — one 128-byte line — chosen by a 32-bit mix of the
+// brick coordinates; the slot inside the line is the three parity bits. A query's 27 neighbours
+// therefore touch at most 8 lines instead of 27 scattered sectors, and the 27 lanes' probes coalesce.
 __host__ __device__ inline uint32_t probe_hash(unsigned long long k) {
-    k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
-    k ^= k >> 27; k *= 0x94d049bb133111ebull;
-    k ^= k >> 31;
-    return static_cast<uint32_t>(k);
+    const uint32_t local = static_cast<uint32_t>(((k >> 42) & 1ull) << 2 | ((k >> 21) & 1ull) << 1 | (k & 1ull));
+    // brick coordinates (20 bits each) mixed by three odd multipliers and murmur3's 32-bit finaliser
+    const uint32_t bx = static_cast<uint32_t>(k >> 43) & 0xFFFFFu, by = static_cast<uint32_t>(k >> 22) & 0xFFFFFu,
+                   bz = static_cast<uint32_t>(k >> 1) & 0xFFFFFu;
+    uint32_t h = (bx * 0x9E3779B1u) ^ (by * 0x85EBCA77u) ^ (bz * 0xC2B2AE3Du);
+    h ^= h >> 16; h *= 0x85EBCA6Bu;
+    h ^= h >> 13; h *= 0xC2B2AE35u;
+    h ^= h >> 16;
+    return (h << 3) | local;
 }
 
 // ---------------------------------------------------------------------------------------------------

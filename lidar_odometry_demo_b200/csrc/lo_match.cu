@@ -171,13 +171,14 @@ __device__ inline void reduce_partials(const double* partials, int nblocks, doub
 // ---------------------------------------------------------------------------------------------------
 __global__ void find_pairs_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m, QueryTransform tf, float max_d2,
                                   lo_pair* __restrict__ pairs, uint8_t* __restrict__ valid, uint32_t* __restrict__ n_valid) {
+    __shared__ uint2 work[(256 / 32) * kWorkListStride];
     const int lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= m) return;
     const PointXYZ q = queries[warp];
     float wq[3];
     transform_query(tf, q.x, q.y, q.z, wq);
-    const Found f = nn_search_warp(g, wq, max_d2, lane);
+    const Found f = nn_search_warp(g, wq, max_d2, lane, work + (threadIdx.x >> 5) * kWorkListStride);
     if (lane == 0) {
         lo_pair out;
         memset(&out, 0, sizeof(out));
@@ -198,11 +199,14 @@ __global__ void find_pairs_kernel(GridView g, const PointXYZ* __restrict__ queri
 // query, lane j keeps the correspondence of query j, then all 32 lanes evaluate their residual/Jacobian in
 // parallel and the warp reduces the 28 sums by shuffles into its shared-memory row.
 constexpr int kNnThreads = 256;
-__global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+__global__ void __launch_bounds__(kNnThreads, 4) nn_residual_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
                                                                   QueryTransform tf, EvalPoint ep, float max_d2,
                                                                   double* __restrict__ partials) {
     __shared__ double rows[(kNnThreads / 32) * kRow];
+    __shared__ uint2 work[(kNnThreads / 32) * kWorkListStride];
     const int lane = threadIdx.x & 31, warp_in_block = threadIdx.x >> 5;
+    uint2* wl = work + warp_in_block * kWorkListStride;
+    const LaneOffset lofs = lane_offset(lane);
     for (int k = threadIdx.x; k < (kNnThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
     __syncthreads();
     double* row = rows + warp_in_block * kRow;
@@ -215,23 +219,36 @@ __global__ void __launch_bounds__(kNnThreads) nn_residual_kernel(GridView g, con
         if (mine < m) q = queries[mine];  // coalesced 16 B loads
         bool my_valid = false;
         float my_o[3] = {0.f, 0.f, 0.f}, my_n[3] = {0.f, 0.f, 0.f};
+        uint32_t my_at = 0;
         uint32_t visited = 0, occupied = 0;
         const uint32_t in_tile = min(32u, m - base);
+        // Lane l transforms query l once (findMatchingPairs, voxel_grid.h:217-223) and takes its voxel index; the loop
+        // broadcasts them. Software pipeline: the slot loads of query j+1 are in flight while query j is scanned.
+        float own[3];
+        transform_query(tf, q.x, q.y, q.z, own);
+        const int oi[3] = {clamp_axis(axis_index(own[0], g.voxel_size)), clamp_axis(axis_index(own[1], g.voxel_size)),
+                           clamp_axis(axis_index(own[2], g.voxel_size))};
+        Probe next = probe_issue_at(g, __shfl_sync(kFullMask, oi[0], 0), __shfl_sync(kFullMask, oi[1], 0), __shfl_sync(kFullMask, oi[2], 0), lofs);
         for (uint32_t j = 0; j < in_tile; j++) {
-            const float qx = __shfl_sync(kFullMask, q.x, j), qy = __shfl_sync(kFullMask, q.y, j), qz = __shfl_sync(kFullMask, q.z, j);
-            float wq[3];
-            transform_query(tf, qx, qy, qz, wq);
-            uint32_t cnt = 0;
-            const Found f = nn_search_warp(g, wq, max_d2, lane, &cnt);
+            uint32_t vid, cnt;
+            probe_resolve(g, next, vid, cnt);
+            const int jj = static_cast<int>(j);
+            const float cur[3] = {__shfl_sync(kFullMask, own[0], jj), __shfl_sync(kFullMask, own[1], jj), __shfl_sync(kFullMask, own[2], jj)};
+            if (j + 1 < in_tile)
+                next = probe_issue_at(g, __shfl_sync(kFullMask, oi[0], jj + 1), __shfl_sync(kFullMask, oi[1], jj + 1),
+                                      __shfl_sync(kFullMask, oi[2], jj + 1), lofs);
+            const Hit hit = scan_candidates(g, cur, max_d2, lane, wl, vid, cnt);
             visited += cnt;
             occupied += cnt ? 1u : 0u;
             if (lane == static_cast<int>(j)) {
-                my_valid = f.valid;
-                for (int k = 0; k < 3; k++) {
-                    my_o[k] = f.o[k];
-                    my_n[k] = f.n[k];
-                }
+                my_valid = hit.valid;
+                my_at = hit.at;
+                for (int k = 0; k < 3; k++) my_o[k] = hit.o[k];
             }
+        }
+        if (my_valid) {  // the 32 winning normals of the tile in one round of loads
+            const float4 nv = __ldg(g.normals + my_at);
+            my_n[0] = nv.x; my_n[1] = nv.y; my_n[2] = nv.z;
         }
         const float pf[3] = {q.x, q.y, q.z};
         const Terms t = pair_terms(ep, pf, my_o, my_n);
@@ -304,6 +321,8 @@ __global__ void __launch_bounds__(kAlignThreads, 1) align_kernel(AlignArgs a) {
     __shared__ EvalPoint ep_s;
     __shared__ float pose_s[7];
     __shared__ int flag_s;
+    __shared__ uint2 work[(kAlignThreads / 32) * kWorkListStride];
+    uint2* wl = work + (threadIdx.x >> 5) * kWorkListStride;
 
     const int lane = threadIdx.x & 31;
     // consecutive queries / tiles go to different SMs: warp w of block b is global warp w * gridDim.x + b
@@ -334,7 +353,7 @@ __global__ void __launch_bounds__(kAlignThreads, 1) align_kernel(AlignArgs a) {
             const PointXYZ q = a.queries[qi];
             float wq[3];
             transform_query(tf, q.x, q.y, q.z, wq);
-            const Found f = nn_search_warp(a.g, wq, max_d2, lane);
+            const Found f = nn_search_warp(a.g, wq, max_d2, lane, wl);
             if (lane == 0) {
                 a.pair_o[qi] = make_float4(f.o[0], f.o[1], f.o[2], f.valid ? 1.f : 0.f);
                 a.pair_n[qi] = make_float4(f.n[0], f.n[1], f.n[2], 0.f);
