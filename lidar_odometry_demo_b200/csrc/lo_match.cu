@@ -210,18 +210,21 @@ __global__ void __launch_bounds__(kNnThreads, 4) nn_residual_kernel(GridView g, 
     for (int k = threadIdx.x; k < (kNnThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
     __syncthreads();
     double* row = rows + warp_in_block * kRow;
+    // every warp owns one contiguous range of ceil(m / warps) queries (balanced: no partial last wave) and walks it in
+    // tiles of 32
     const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t tiles = (m + 31) / 32;
-    for (uint32_t tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; tile < tiles; tile += total_warps) {
-        const uint32_t base = tile * 32;
+    const uint32_t per_warp = (m + total_warps - 1) / total_warps;
+    const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t range_begin = min(m, gw * per_warp), range_end = min(m, range_begin + per_warp);
+    for (uint32_t base = range_begin; base < range_end; base += 32) {
         const uint32_t mine = base + lane;
         PointXYZ q{0.f, 0.f, 0.f, 0.f};
-        if (mine < m) q = queries[mine];  // coalesced 16 B loads
+        if (mine < range_end) q = queries[mine];  // coalesced 16 B loads
         bool my_valid = false;
         float my_o[3] = {0.f, 0.f, 0.f}, my_n[3] = {0.f, 0.f, 0.f};
         uint32_t my_at = 0;
         uint32_t visited = 0, occupied = 0;
-        const uint32_t in_tile = min(32u, m - base);
+        const uint32_t in_tile = min(32u, range_end - base);
         // Lane l transforms query l once (findMatchingPairs, voxel_grid.h:217-223) and takes its voxel index; the loop
         // broadcasts them. Software pipeline: the slot loads of query j+1 are in flight while query j is scanned.
         float own[3];
@@ -564,8 +567,8 @@ extern "C" int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, con
     const QueryTransform tf = make_query_transform(pose_from7(pose7));
     const EvalPoint ep = make_eval_point(x7d);
     const uint32_t tiles = static_cast<uint32_t>((m + 31) / 32);
-    // one tile per warp, capped at a few waves of the machine; the kernel grid-strides beyond that
-    const int max_blocks = ctx->sm_count * 8 * 4;
+    // at most one resident wave (4 blocks of 8 warps per SM); each warp takes an equal share of the queries
+    const int max_blocks = ctx->sm_count * 4;
     const int blocks = std::max(1, std::min<int>(max_blocks, static_cast<int>((tiles + kNnThreads / 32 - 1) / (kNnThreads / 32))));
     LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(blocks) * 32 * sizeof(double)));
     lo_normal_eq* d_out = reinterpret_cast<lo_normal_eq*>(ctx->small.as<char>() + 1024);
