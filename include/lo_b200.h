@@ -123,6 +123,30 @@ int lo_align(lo_grid* keyframe, const float* xyz16, size_t m, const float guess7
 int lo_align_dev(lo_grid* keyframe, const void* d_xyz16, size_t m, const float guess7[7], float out7[7],
                  lo_align_stats* stats /* nullable */);
 
+/* ---- key-frame map sharded by voxel-hash range over several GPUs (BASELINE.json config 4) ----
+ * The reference is single-process; these phases split CloudMatcher::align (src/cloud_matcher.cpp:105-178) and
+ * VoxelGrid::findMatchingPairs (src/voxel_grid.h:206-234) at the two points where ranks must exchange data. The
+ * library issues no collective itself: the host places an all-reduce(MIN, u64[m]) after lo_shard_search_dev and an
+ * all-reduce(SUM, f64[32]) after lo_shard_evaluate_dev, on the context's stream (host/lo_b200.hpp
+ * ShardedCloudMatcher; lidar_odometry_demo_b200/sharded.py uses torch.distributed / NCCL). */
+/* Call on an empty grid: add_cloud then keeps only the voxels whose 22-bit hash falls in this rank's range. */
+int lo_grid_set_shard(lo_grid* g, uint32_t rank, uint32_t world);
+/* d_packed[i] = (float bits of d2 << 32 | probe << 24 | slot) of query i's nearest stored point among THIS rank's
+ * voxels, ~0 if none; d_hit16[i] = that point (x,y,z) + its slab index (device scratch the caller owns, 16 B each). */
+int lo_shard_search_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], float max_dist, uint64_t* d_packed, void* d_hit16);
+/* Sums (21 upper JtJ, 6 Jtr, cost, count; 32 doubles, no prior) over the queries whose reduced packed value equals
+ * this rank's local one, evaluated at x7d = {qw,qx,qy,qz,tx,ty,tz}. */
+int lo_shard_evaluate_dev(lo_grid* g, const void* d_xyz16, size_t m, const uint64_t* d_packed_local, const uint64_t* d_packed_global,
+                          const void* d_hit16, const double x7d[7], double* d_acc32);
+/* ceres::Solve's trust-region logic on the host for the sharded path (every rank runs it on identical sums). */
+typedef struct lo_lm lo_lm;
+lo_lm* lo_lm_create(void);
+void lo_lm_destroy(lo_lm* h);
+int lo_lm_begin(lo_lm* h, const double x0[7], const double acc32[32], const double prior_b[3]);   /* 1: continue */
+int lo_lm_propose(lo_lm* h, double cand7[7]);                                                      /* 1: evaluate cand7 */
+int lo_lm_update(lo_lm* h, const double acc32[32]);                                                /* 1: continue */
+int lo_lm_result(const lo_lm* h, double x7[7], double* last_step_norm, double* cost, int32_t* termination, int32_t* recorded);
+
 /* ---- CloudTransformer / utils (src/utils) ------------------------------------------------------ */
 /* pointTimeNormalize (point_time_normalize.h:14-39) followed by transformNonRigid
  * (cloud_transform.h:15-40) with (start7, end7); out may alias in. */

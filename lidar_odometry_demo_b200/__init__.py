@@ -68,6 +68,11 @@ SIGNATURES = {
     "lo_nn_residual": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
     "lo_nn_residual_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
     "lo_align": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]), "lo_align_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]),
+    "lo_grid_set_shard": (_i, [_vp, C.c_uint32, C.c_uint32]),
+    "lo_shard_search_dev": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]),
+    "lo_shard_evaluate_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
+    "lo_lm_create": (_vp, []), "lo_lm_destroy": (None, [_vp]), "lo_lm_begin": (_i, [_vp, _vp, _vp, _vp]),
+    "lo_lm_propose": (_i, [_vp, _vp]), "lo_lm_update": (_i, [_vp, _vp]), "lo_lm_result": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "lo_deskew": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]),
     "lo_transform_xyz": (_i, [_vp, _vp, _sz, _vp, _vp]), "lo_transform_with_normals": (_i, [_vp, _vp, _sz, _vp, _vp]),
     "lo_range_filter": (_i, [_vp, _vp, _sz, _fl, _fl, _vp, C.POINTER(_sz)]),

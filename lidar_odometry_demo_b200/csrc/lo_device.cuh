@@ -204,7 +204,15 @@ struct GridView {            // passed by value to kernels
     uint32_t mask;           // capacity - 1
     uint32_t width;          // max(max_points, 1)
     float voxel_size;
+    uint32_t shard_rank;     // this grid keeps only the voxels whose hash range it owns (lo_grid_set_shard);
+    uint32_t shard_world;    // world <= 1: unsharded
 };
+
+// Owner of a voxel in a key-frame map partitioned by voxel-hash range over `world` ranks (BASELINE.json config 4):
+// the reference's 22-bit voxel hash (src/voxel_grid.h:31-38) cut into `world` equal contiguous ranges.
+__host__ __device__ inline uint32_t shard_owner(long long ix, long long iy, long long iz, uint32_t world) {
+    return static_cast<uint32_t>((static_cast<unsigned long long>(reference_hash22(ix, iy, iz)) * world) >> 22);
+}
 
 // returns slot index or 0xFFFFFFFF
 __device__ inline uint32_t table_find(const GridView& g, unsigned long long key) {

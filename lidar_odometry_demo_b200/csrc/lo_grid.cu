@@ -63,6 +63,10 @@ __global__ void grid_locate_kernel(PointSource src, uint32_t n_bound, const uint
         slot_of[i] = kInvalid;
         return;
     }
+    if (g.shard_world > 1 && shard_owner(ix, iy, iz, g.shard_world) != g.shard_rank) {  // another rank's voxel
+        slot_of[i] = kInvalid;
+        return;
+    }
     const unsigned long long key = pack_key(ix, iy, iz);
     uint32_t h = probe_hash(key) & g.mask;
     while (true) {

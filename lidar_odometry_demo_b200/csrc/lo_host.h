@@ -94,6 +94,7 @@ struct lo_grid {
     lo_ctx* ctx = nullptr;
     float voxel_size = 0.5f;
     size_t max_points = 10;
+    uint32_t shard_rank = 0, shard_world = 1;  // lo_grid_set_shard
     uint32_t width = 10;         // max(max_points, 1)
     uint32_t capacity = 0;       // slots (power of two)
     uint32_t payload_cap = 0;    // payload ids allocated
@@ -109,6 +110,7 @@ struct lo_grid {
         lo::GridView v;
         v.slots = slots; v.points = points; v.normals = normals;
         v.mask = capacity - 1; v.width = width; v.voxel_size = voxel_size;
+        v.shard_rank = shard_rank; v.shard_world = shard_world;
         return v;
     }
 };

@@ -621,3 +621,174 @@ extern "C" int lo_align(lo_grid* kf, const float* xyz16, size_t m, const float g
     LO_TRY(stage_queries(ctx, xyz16, m));
     return lo_align_dev(kf, ctx->in_a.p, m, guess7, out7, stats);
 }
+
+// ---------------------------------------------------------------------------------------------------
+// BASELINE.json config 4 / SURVEY.md 8(e): CloudMatcher::align against a key-frame map that is partitioned by
+// voxel-hash range over several GPUs. The library stays collective-free: it offers the per-rank phases, and the host
+// (host/lo_b200.hpp ShardedCloudMatcher in C++; lidar_odometry_demo_b200/sharded.py over torch.distributed / NCCL in
+// the tests and the bench) places two all-reduces between them per evaluation:
+//
+//   lo_shard_search_dev    every rank: 27-neighbour search of the replicated queries in ITS voxels ->
+//                          packed[i] = (d2 bits << 32 | probe << 24 | slot), ~0 if none          [exchange 1: MIN over u64]
+//   lo_shard_evaluate_dev  the rank whose packed[i] equals the reduced value owns query i's correspondence
+//                          (VoxelGrid::getCorrespondence's first strict minimum, voxel_grid.h:175-190) and adds
+//                          its residual / Jacobian terms -> 32 doubles                            [exchange 2: SUM over f64]
+//   lo_lm_*                ceres::Solve's trust-region step logic (csrc/lo_lm.cuh) on the host, run redundantly and
+//                          deterministically by every rank on the identical reduced sums
+namespace lo {
+
+constexpr int kShardThreads = 256;
+
+__global__ void __launch_bounds__(kShardThreads) shard_search_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m, QueryTransform tf,
+                                                                      float max_d2, unsigned long long* __restrict__ packed,
+                                                                      float4* __restrict__ hit) {
+    __shared__ uint2 work[(kShardThreads / 32) * kWorkListStride];
+    const int lane = threadIdx.x & 31;
+    uint2* wl = work + (threadIdx.x >> 5) * kWorkListStride;
+    const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+    const LaneOffset lofs = lane_offset(lane);
+    for (uint32_t qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; qi < m; qi += total_warps) {
+        const PointXYZ q = queries[qi];
+        float wq[3];
+        transform_query(tf, q.x, q.y, q.z, wq);
+        uint32_t vid, count;
+        probe_resolve(g, probe_issue_at(g, clamp_axis(axis_index(wq[0], g.voxel_size)), clamp_axis(axis_index(wq[1], g.voxel_size)),
+                                        clamp_axis(axis_index(wq[2], g.voxel_size)), lofs), vid, count);
+        const Hit h = scan_candidates(g, wq, max_d2, lane, wl, vid, count);
+        if (lane == 0) {
+            packed[qi] = h.key;
+            hit[qi] = make_float4(h.o[0], h.o[1], h.o[2], __uint_as_float(h.at));
+        }
+    }
+}
+
+// terms of the correspondences this rank owns; per-block partial sums in a fixed order
+__global__ void __launch_bounds__(kShardThreads) shard_evaluate_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m, EvalPoint ep,
+                                                                        const unsigned long long* __restrict__ local,
+                                                                        const unsigned long long* __restrict__ global,
+                                                                        const float4* __restrict__ hit, double* __restrict__ partials) {
+    __shared__ double rows[(kShardThreads / 32) * kRow];
+    const int lane = threadIdx.x & 31;
+    for (int k = threadIdx.x; k < (kShardThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
+    __syncthreads();
+    double* row = rows + (threadIdx.x >> 5) * kRow;
+    const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < m; base += total_warps * 32) {
+        const uint32_t i = base + lane;
+        bool mine = false;
+        Terms t;
+        if (i < m) {
+            const unsigned long long gl = global[i];
+            mine = gl != ~0ull && local[i] == gl;
+            if (mine) {
+                const float4 o = hit[i];
+                const float4 nv = __ldg(g.normals + __float_as_uint(o.w));
+                const PointXYZ q = queries[i];
+                const float pq[3] = {q.x, q.y, q.z}, of[3] = {o.x, o.y, o.z}, nf[3] = {nv.x, nv.y, nv.z};
+                t = pair_terms(ep, pq, of, nf);
+            }
+        }
+        if (!mine) {
+            for (int k = 0; k < 6; k++) t.j[k] = 0.0;
+            t.rc = 0.0;
+            t.cost = 0.0;
+        }
+        accumulate_warp(row, t, mine, lane);
+    }
+    block_rows_to_global(rows, partials + blockIdx.x * 32);
+}
+
+__global__ void shard_sum_kernel(const double* __restrict__ partials, int nblocks, double* __restrict__ acc32) {
+    __shared__ double total[32];
+    __shared__ double scratch[(256 / 32) * kRow];
+    reduce_partials(partials, nblocks, scratch, total);
+    if (threadIdx.x < 32) acc32[threadIdx.x] = threadIdx.x < kAcc ? total[threadIdx.x] : 0.0;
+}
+
+}  // namespace lo
+
+extern "C" int lo_grid_set_shard(lo_grid* g, uint32_t rank, uint32_t world) {
+    if (!g || world == 0 || rank >= world) return LO_E_ARG;
+    LO_TRY(grid_refresh_counters(g));
+    if (g->h_counters[GC_VOXELS] != 0) {
+        set_error("lo_grid_set_shard must be called on an empty grid");
+        return LO_E_ARG;
+    }
+    g->shard_rank = rank;
+    g->shard_world = world;
+    return LO_OK;
+}
+
+extern "C" int lo_shard_search_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], float max_dist, uint64_t* d_packed,
+                                   void* d_hit16) {
+    if (!g || (!d_xyz16 && m) || !pose7 || (!d_packed && m) || (!d_hit16 && m)) return LO_E_ARG;
+    if (m == 0) return LO_OK;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const QueryTransform tf = make_query_transform(pose_from7(pose7));
+    const int blocks = std::max(1, std::min<int>(ctx->sm_count * 8, static_cast<int>((m * 32 + kShardThreads - 1) / kShardThreads)));
+    shard_search_kernel<<<blocks, kShardThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m), tf,
+                                                                   max_dist * max_dist, reinterpret_cast<unsigned long long*>(d_packed),
+                                                                   static_cast<float4*>(d_hit16));
+    LO_LAUNCHED(ctx);
+    return LO_OK;
+}
+
+extern "C" int lo_shard_evaluate_dev(lo_grid* g, const void* d_xyz16, size_t m, const uint64_t* d_packed_local, const uint64_t* d_packed_global,
+                                     const void* d_hit16, const double x7d[7], double* d_acc32) {
+    if (!g || !x7d || !d_acc32 || (m && (!d_xyz16 || !d_packed_local || !d_packed_global || !d_hit16))) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const EvalPoint ep = make_eval_point(x7d);
+    const int blocks = std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
+    LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(blocks) * 32 * sizeof(double)));
+    shard_evaluate_kernel<<<blocks, kShardThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m), ep,
+                                                                     reinterpret_cast<const unsigned long long*>(d_packed_local),
+                                                                     reinterpret_cast<const unsigned long long*>(d_packed_global),
+                                                                     static_cast<const float4*>(d_hit16), ctx->tmp_c.as<double>());
+    LO_LAUNCHED(ctx);
+    shard_sum_kernel<<<1, 256, 0, ctx->stream>>>(ctx->tmp_c.as<double>(), blocks, d_acc32);
+    LO_LAUNCHED(ctx);
+    return LO_OK;
+}
+
+// ---- ceres::Solve's step logic on the host (the same lo_lm.cuh the device kernels use) -------------------------
+struct lo_lm {
+    lo::LmState s;
+    double prior_b[3];
+};
+extern "C" lo_lm* lo_lm_create(void) { return new lo_lm(); }
+extern "C" void lo_lm_destroy(lo_lm* h) { delete h; }
+// acc32: the all-reduced sums of lo_shard_evaluate_dev at x0 (21 upper JtJ, 6 Jtr, cost, count); the NormalPrior of
+// cloud_matcher.cpp:153-154 is added here, once. Returns 1 if the solve continues.
+extern "C" int lo_lm_begin(lo_lm* h, const double x0[7], const double acc32[32], const double prior_b[3]) {
+    if (!h || !x0 || !acc32 || !prior_b) return LO_E_ARG;
+    double acc[kAcc];
+    for (int k = 0; k < kAcc; k++) acc[k] = acc32[k];
+    for (int k = 0; k < 3; k++) h->prior_b[k] = prior_b[k];
+    add_prior(acc, x0 + 4, prior_b);
+    return lm_begin(h->s, x0, acc) ? 1 : 0;
+}
+// returns 1 and writes the candidate (7 doubles) when a cost/Jacobian evaluation at cand is needed, 0 when the solve ended
+extern "C" int lo_lm_propose(lo_lm* h, double cand7[7]) {
+    if (!h || !cand7) return LO_E_ARG;
+    if (!lm_propose(h->s)) return 0;
+    for (int k = 0; k < 7; k++) cand7[k] = h->s.cand[k];
+    return 1;
+}
+extern "C" int lo_lm_update(lo_lm* h, const double acc32[32]) {
+    if (!h || !acc32) return LO_E_ARG;
+    double acc[kAcc];
+    for (int k = 0; k < kAcc; k++) acc[k] = acc32[k];
+    add_prior(acc, h->s.cand + 4, h->prior_b);
+    return lm_update(h->s, acc) ? 1 : 0;
+}
+extern "C" int lo_lm_result(const lo_lm* h, double x7[7], double* last_step_norm, double* cost, int32_t* termination, int32_t* recorded) {
+    if (!h || !x7) return LO_E_ARG;
+    for (int k = 0; k < 7; k++) x7[k] = h->s.x[k];
+    if (last_step_norm) *last_step_norm = h->s.last_step_norm;
+    if (cost) *cost = h->s.x_cost;
+    if (termination) *termination = h->s.termination;
+    if (recorded) *recorded = h->s.recorded;
+    return LO_OK;
+}

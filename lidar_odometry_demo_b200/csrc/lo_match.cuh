@@ -103,6 +103,7 @@ struct Hit {          // nearest stored point of one query, identical in every l
     bool valid;
     float o[3];       // the stored point (plane_origin)
     uint32_t at;      // its index in the point / normal slabs
+    unsigned long long key;  // (d2 bits << 32 | probe << 24 | slot), ~0 when there is no correspondence
 };
 
 __device__ inline Hit scan_candidates(const GridView& g, const float wq[3], float max_d2, int lane, uint2* wl, uint32_t vid, uint32_t count) {
@@ -178,6 +179,7 @@ __device__ inline Hit scan_candidates(const GridView& g, const float wq[3], floa
     hit.valid = (m != ~0ull);
     hit.o[0] = hit.o[1] = hit.o[2] = 0.f;
     hit.at = 0;
+    hit.key = m;
     if (hit.valid) {
         const int src = __ffs(__ballot_sync(kFullMask, best == m)) - 1;   // (probe, slot) is unique: exactly one lane
         hit.o[0] = __shfl_sync(kFullMask, bx, src);
