@@ -12,7 +12,7 @@
 //                  VoxelGrid(vs,1) down-samplers (cpp:37-38,46-47): find-or-create voxel, atomicMin of the arrival index
 //   P7 select      which points are the first of their voxel (winners), block counts
 //   P8 emit        query cloud M (arrival order) | list of update winners U with their robin_map bucket
-//   P9 robin       one block: the update set in the reference's tsl::robin_map iteration order
+//   P9 robin       four small kernels: the update set in the reference's tsl::robin_map iteration order
 //   align_kernel   CloudMatcher::align (lo_match.cu)
 //   gate, clean-up, key-frame insert (cpp:53-70) and the read-back as in lo_odometry.cu
 //
@@ -49,8 +49,12 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     uint32_t* slot_m;                      // [n]
     uint32_t* ulist;                       // [n] update winners (index into filtered), arrival order
     uint32_t* ubucket;                     // [n] their ideal robin_map bucket
-    uint32_t* usorted;                     // [n] scratch of P9
-    uint32_t cell_cap, ds_cap;
+    uint32_t* usorted;                     // [n] update winners in robin_map order (index into ulist)
+    uint32_t* umember;                     // [n] bucket members before the tie groups are ordered
+    uint32_t* rb_hist;                     // [rb_cap] winners per ideal bucket, then exclusive start of each bucket
+    uint32_t* rb_fill;                     // [rb_cap] placement cursors
+    int* rb_shift;                         // [1] max over sorted elements of (bucket - position)
+    uint32_t cell_cap, ds_cap, rb_cap;
 };
 
 static size_t carve(PipeBufs& b, char* base, uint32_t n) {
@@ -78,6 +82,13 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.ulist = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.ubucket = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.usorted = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.umember = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    uint32_t rb = 2;
+    while (rb < 2u * n) rb <<= 1;
+    b.rb_cap = rb;
+    b.rb_hist = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4 + 16));
+    b.rb_fill = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
+    b.rb_shift = reinterpret_cast<int*>(take(16));
     return off;
 }
 
@@ -114,6 +125,8 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_prep_kernel(OdomDev* s, con
         atomicMax(&minmax[1], hi_v);
     }
     if (tid < 256) b.hist[tid] = 0;
+    if (tid == 0) *b.rb_shift = INT_MIN;
+    for (uint32_t c = tid; c < b.rb_cap; c += nthreads) b.rb_hist[c] = 0;
     for (uint32_t c = tid; c < b.cell_cap; c += nthreads) b.cell_idx[c] = 0;
     const uint4 empty = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
     uint4* u = reinterpret_cast<uint4*>(b.ds_u);
@@ -401,7 +414,9 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, Pip
             long long ix, iy, iz;
             unpack_key(b.ds_u[su].key, ix, iy, iz);
             b.ulist[bu + ru] = i;
-            b.ubucket[bu + ru] = reference_hash22(ix, iy, iz) & (buckets - 1);
+            const uint32_t bucket = reference_hash22(ix, iy, iz) & (buckets - 1);
+            b.ubucket[bu + ru] = bucket;
+            atomicAdd(&b.rb_hist[bucket], 1u);
         }
         if (wm) {
             const float4 p = *reinterpret_cast<const float4*>(filtered + i);
@@ -413,87 +428,72 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, Pip
 }
 
 // ---------------------------------------------------------------------------------------------------
-// P9. keyframe_downsampler.getCloud() (cpp:38,42,69): the update set in tsl::robin_map iteration order, by one
-// block with the bucket array in shared memory. For n inserted keys the map has C = 2*pow2ceil(n) buckets;
-// iteration is ascending bucket position; robin-hood probing keeps elements sorted by ideal bucket
-// b = hash22 & (C-1); a cluster that runs past the last bucket wraps to the front (lo_robin.cu states the same
-// rule for the stage-by-stage path). Counting sort by b: per-bucket counters (16 bit, two per word), exclusive
-// scan, placement, then each tie group is ordered by arrival.
-constexpr int kRobinThreads = 1024;
+// P9. keyframe_downsampler.getCloud() (cpp:38,42,69): the update set in tsl::robin_map iteration order. For n inserted
+// keys the map has C = 2*pow2ceil(n) buckets; iteration is ascending bucket position; robin-hood probing keeps
+// elements sorted by ideal bucket b = hash22 & (C-1); a cluster that runs past the last bucket wraps to the front
+// (lo_robin.cu states the same rule for the stage-by-stage path). Counting sort by b: P8 histogrammed the buckets;
+// 9a scans the histogram, 9b places the winners, 9c orders every tie group by arrival and finds the wrap, 9d emits.
+constexpr int kScanThreads = 1024;
 
-__device__ inline uint32_t half_of(uint32_t word, uint32_t b) { return (b & 1u) ? (word >> 16) : (word & 0xFFFFu); }
-
-__global__ void __launch_bounds__(kRobinThreads, 1) pipe_robin_kernel(const OdomDev* __restrict__ s, PipeBufs b,
-                                                                       const PointNormal* __restrict__ filtered, PointNormal* __restrict__ update) {
-    extern __shared__ uint32_t sm[];
-    __shared__ uint32_t scan_sh[kRobinThreads / 32];
-    __shared__ int shift_sh[kRobinThreads / 32];
+__global__ void __launch_bounds__(kScanThreads, 1) pipe_robin_scan_kernel(const OdomDev* __restrict__ s, PipeBufs b) {
+    __shared__ uint32_t warp_sums[kScanThreads / 32];
     const uint32_t n = s->n_update;
     if (n == 0) return;
     const uint32_t C = robin_bucket_count(n);
-    const uint32_t words = C / 2;                    // C >= 2
-    uint32_t* cnt = sm;                              // [words] two 16-bit counters per word
-    unsigned short* tmp = reinterpret_cast<unsigned short*>(sm + words);  // [n] placement (index into ulist)
-    const uint32_t tid = threadIdx.x;
-    for (uint32_t w = tid; w < words; w += kRobinThreads) cnt[w] = 0;
-    __syncthreads();
-    for (uint32_t j = tid; j < n; j += kRobinThreads) {
-        const uint32_t bk = b.ubucket[j];
-        atomicAdd(&cnt[bk >> 1], (bk & 1u) ? 0x10000u : 1u);
-    }
-    __syncthreads();
-    // exclusive scan over the C counters: thread t owns words [t*wpt, (t+1)*wpt)
-    const uint32_t wpt = (words + kRobinThreads - 1) / kRobinThreads;
-    const uint32_t w0 = min(words, tid * wpt), w1 = min(words, w0 + wpt);
+    const uint32_t per = (C + kScanThreads - 1) / kScanThreads;
+    const uint32_t c0 = min(C, threadIdx.x * per), c1 = min(C, c0 + per);
     uint32_t local = 0;
-    for (uint32_t w = w0; w < w1; w++) local += (cnt[w] & 0xFFFFu) + (cnt[w] >> 16);
+    for (uint32_t c = c0; c < c1; c++) local += b.rb_hist[c];
     uint32_t incl = local;
-    const int lane = tid & 31, warp = tid >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int off = 1; off < 32; off <<= 1) {
         const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, off);
         if (lane >= off) incl += v;
     }
-    if (lane == 31) scan_sh[warp] = incl;
+    if (lane == 31) warp_sums[warp] = incl;
     __syncthreads();
-    uint32_t warp_before = 0;
-    for (int w = 0; w < warp; w++) warp_before += scan_sh[w];
-    uint32_t run = warp_before + incl - local;
-    for (uint32_t w = w0; w < w1; w++) {
-        const uint32_t lo_c = cnt[w] & 0xFFFFu, hi_c = cnt[w] >> 16;
-        cnt[w] = (run & 0xFFFFu) | (((run + lo_c) & 0xFFFFu) << 16);   // start of bucket 2w, 2w+1 (n <= 32768 < 65536)
-        run += lo_c + hi_c;
+    uint32_t run = incl - local;
+    for (int w = 0; w < warp; w++) run += warp_sums[w];
+    for (uint32_t c = c0; c < c1; c++) {
+        const uint32_t v = b.rb_hist[c];
+        b.rb_hist[c] = run;    // exclusive start of bucket c
+        b.rb_fill[c] = run;
+        run += v;
     }
-    __syncthreads();
-    // placement: the counter of bucket b advances from its start to its end (= start of bucket b+1)
-    for (uint32_t j = tid; j < n; j += kRobinThreads) {
-        const uint32_t bk = b.ubucket[j];
-        const uint32_t old = atomicAdd(&cnt[bk >> 1], (bk & 1u) ? 0x10000u : 1u);
-        tmp[half_of(old, bk)] = static_cast<unsigned short>(j);
-    }
-    __syncthreads();
-    // order every tie group by arrival (ulist is in arrival order, so by j)
-    for (uint32_t p = tid; p < n; p += kRobinThreads) {
-        const uint32_t j = tmp[p];
-        const uint32_t bk = b.ubucket[j];
-        const uint32_t seg_end = half_of(cnt[bk >> 1], bk);
-        const uint32_t seg_begin = bk == 0 ? 0u : half_of(cnt[(bk - 1) >> 1], bk - 1);
-        uint32_t rank = 0;
-        for (uint32_t q = seg_begin; q < seg_end; q++) rank += tmp[q] < j ? 1u : 0u;
-        b.usorted[seg_begin + rank] = j;
-    }
-    __syncthreads();
-    // wrap: sorted element i sits at bucket position i + max_{k<=i}(b_k - k); the last one at n-1+max_shift; positions
-    // >= C wrap to the front of the bucket array and are therefore iterated first
+    if (c1 == C && c0 < c1) b.rb_hist[C] = run;  // = n
+}
+
+__global__ void __launch_bounds__(kPipeThreads) pipe_robin_place_kernel(const OdomDev* __restrict__ s, PipeBufs b) {
+    const uint32_t n = s->n_update;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+        b.umember[atomicAdd(&b.rb_fill[b.ubucket[j]], 1u)] = j;
+}
+
+__global__ void __launch_bounds__(kPipeThreads) pipe_robin_order_kernel(const OdomDev* __restrict__ s, PipeBufs b) {
+    const uint32_t n = s->n_update;
     int shift = INT_MIN;
-    for (uint32_t p = tid; p < n; p += kRobinThreads) shift = max(shift, static_cast<int>(b.ubucket[b.usorted[p]]) - static_cast<int>(p));
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const uint32_t j = b.umember[p];
+        const uint32_t bk = b.ubucket[j];
+        const uint32_t seg_begin = b.rb_hist[bk], seg_end = b.rb_hist[bk + 1];
+        uint32_t rank = 0;   // ulist is in arrival order, so arrival order inside the tie group is order by j
+        for (uint32_t q = seg_begin; q < seg_end; q++) rank += b.umember[q] < j ? 1u : 0u;
+        b.usorted[seg_begin + rank] = j;
+        // sorted element i sits at bucket position i + max_{k<=i}(b_k - k): the last one at n-1+max_shift
+        shift = max(shift, static_cast<int>(bk) - static_cast<int>(seg_begin + rank));
+    }
     for (int off = 16; off > 0; off >>= 1) shift = max(shift, __shfl_xor_sync(0xFFFFFFFFu, shift, off));
-    if (lane == 0) shift_sh[warp] = shift;
-    __syncthreads();
-    int max_shift = INT_MIN;
-    for (int w = 0; w < kRobinThreads / 32; w++) max_shift = max(max_shift, shift_sh[w]);
-    const long long over = static_cast<long long>(n) + max_shift - static_cast<long long>(C);
+    if ((threadIdx.x & 31) == 0 && shift != INT_MIN) atomicMax(b.rb_shift, shift);
+}
+
+__global__ void __launch_bounds__(kPipeThreads) pipe_robin_emit_kernel(const OdomDev* __restrict__ s, PipeBufs b,
+                                                                        const PointNormal* __restrict__ filtered, PointNormal* __restrict__ update) {
+    const uint32_t n = s->n_update;
+    if (n == 0) return;
+    // positions >= C wrap to the front of the bucket array and are therefore iterated first
+    const long long over = static_cast<long long>(n) + *b.rb_shift - static_cast<long long>(robin_bucket_count(n));
     const uint32_t rot = over > 0 ? static_cast<uint32_t>(over) : 0u;
-    for (uint32_t p = tid; p < n; p += kRobinThreads) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const uint32_t dst = (p + rot) % n;
         const float4* src = reinterpret_cast<const float4*>(filtered + b.ulist[b.usorted[p]]);
         float4* o = reinterpret_cast<float4*>(update + dst);
@@ -545,15 +545,13 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     LO_LAUNCHED(ctx);
     pipe_emit_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->query.as<PointXYZ>(), with_match);
     LO_LAUNCHED(ctx);
-    uint32_t cmax = 2;
-    while (cmax < 2 * n) cmax <<= 1;
-    const size_t robin_smem = static_cast<size_t>(cmax / 2) * 4 + ((static_cast<size_t>(n) * 2 + 15) & ~static_cast<size_t>(15));
-    static bool attr_set = false;
-    if (!attr_set) {
-        LO_CUDA(cudaFuncSetAttribute(pipe_robin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
-    pipe_robin_kernel<<<1, kRobinThreads, robin_smem, ctx->stream>>>(s, b, filtered, h->update.as<PointNormal>());
+    pipe_robin_scan_kernel<<<1, kScanThreads, 0, ctx->stream>>>(s, b);
+    LO_LAUNCHED(ctx);
+    pipe_robin_place_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b);
+    LO_LAUNCHED(ctx);
+    pipe_robin_order_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b);
+    LO_LAUNCHED(ctx);
+    pipe_robin_emit_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->update.as<PointNormal>());
     LO_LAUNCHED(ctx);
     if (first) {
         LO_TRY(grid_add_dev(h->keyframe, h->update.p, n, 1, nullptr, &s->n_update));  // cpp:42
