@@ -41,20 +41,9 @@ __global__ void odom_gate_kernel(OdomDev* s, float threshold) {
     const Pose d = pose_compose(a, pose_inverse(b));
     float r[9];
     rotation_matrix_f(d.w, d.x, d.y, d.z, r);
-    // Matrix3f::eulerAngles(0,1,2) (Eigen 3.4); libm float functions evaluated in double and rounded once
     const float pi_f = 3.14159265358979323846f;
-    float e0 = as_float(atan2(static_cast<double>(r[5]), static_cast<double>(r[8])));
-    const float c2 = sqrtf(r[0] * r[0] + r[1] * r[1]);
-    float e1;
-    if (e0 > 0.f) {
-        e0 -= pi_f;
-        e1 = as_float(atan2(static_cast<double>(-r[2]), static_cast<double>(-c2)));
-    } else {
-        e1 = as_float(atan2(static_cast<double>(-r[2]), static_cast<double>(c2)));
-    }
-    const float s1 = as_float(sin(static_cast<double>(e0))), c1 = as_float(cos(static_cast<double>(e0)));
-    const float e2 = as_float(atan2(static_cast<double>(s1 * r[6] - c1 * r[3]), static_cast<double>(c1 * r[4] - s1 * r[7])));
-    const float ang[3] = {-e0, -e1, -e2};
+    float ang[3];
+    euler_angles_012(r, ang);
     bool ok = true;
     for (int k = 0; k < 3; k++) {
         const float deg = (ang[k] * 180.0f) / pi_f;
@@ -121,12 +110,15 @@ static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P
     return LO_OK;
 }
 
-static int finish_scan(lo_odometry* h, uint32_t n_points) {
+static int finish_scan(lo_odometry* h, uint32_t n_points, bool readback_done = false) {
     lo_ctx* ctx = h->ctx;
-    odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
-    LO_LAUNCHED(ctx);
+    if (!readback_done) {
+        odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
+        LO_LAUNCHED(ctx);
+    }
     LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (readback_done) fused_trace_dump(h);
     const ScanReadback& r = *h->h_readback;
     std::memcpy(h->pose, r.pose, sizeof(h->pose));
     std::memcpy(h->keyframe->h_counters, r.kf_counters, sizeof(r.kf_counters));
@@ -203,7 +195,7 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
         h->n_last = nn;
         LO_TRY(fused_process_enqueue(h, static_cast<const PointXYZIRT*>(d_xyzirt32), nn));
         const uint32_t ticket_after = h->keyframe->h_counters[GC_TICKET];
-        const int st = finish_scan(h, nn);
+        const int st = finish_scan(h, nn, true);
         preserve_ticket(h->keyframe, ticket_after);
         return st;
     }

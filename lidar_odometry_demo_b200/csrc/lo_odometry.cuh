@@ -23,6 +23,25 @@ __device__ inline Pose identity_pose() {
     return p;
 }
 
+// Matrix3f::eulerAngles(0,1,2) (Eigen 3.4) of a row-major rotation matrix, negated as the gate uses them
+// (lidar_odometry.cpp:55); libm float functions evaluated in double and rounded once (only a 5 degree threshold
+// depends on them).
+__device__ inline void euler_angles_012(const float r[9], float ang[3]) {
+    const float pi_f = 3.14159265358979323846f;
+    float e0 = static_cast<float>(atan2(static_cast<double>(r[5]), static_cast<double>(r[8])));
+    const float c2 = sqrtf(r[0] * r[0] + r[1] * r[1]);
+    float e1;
+    if (e0 > 0.f) {
+        e0 -= pi_f;
+        e1 = static_cast<float>(atan2(static_cast<double>(-r[2]), static_cast<double>(-c2)));
+    } else {
+        e1 = static_cast<float>(atan2(static_cast<double>(-r[2]), static_cast<double>(c2)));
+    }
+    const float s1 = static_cast<float>(sin(static_cast<double>(e0))), c1 = static_cast<float>(cos(static_cast<double>(e0)));
+    const float e2 = static_cast<float>(atan2(static_cast<double>(s1 * r[6] - c1 * r[3]), static_cast<double>(c1 * r[4] - s1 * r[7])));
+    ang[0] = -e0; ang[1] = -e1; ang[2] = -e2;
+}
+
 struct ScanReadback {   // one D2H per scan
     float pose[7];
     uint32_t n_planar, n_update, n_query, unstable;
@@ -51,10 +70,11 @@ struct lo_odometry {
 
 
 namespace lo {
-// lo_pipeline.cu: LidarOdometry::processCloud with the per-scan stages fused into ~16 launches. Requires
-// n <= kFusedMaxPoints; returns LO_OK after enqueueing everything up to (not including) the read-back.
+// lo_pipeline.cu: LidarOdometry::processCloud as one persistent cooperative kernel. Requires n <= kFusedMaxPoints;
+// returns LO_OK after enqueueing the kernel, which also fills the device-side ScanReadback block.
 constexpr uint32_t kFusedMaxPoints = 32768;
 int fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n);
 void fused_release(lo_odometry* h);
+void fused_trace_dump(lo_odometry* h);
 int odom_gate_enqueue(lo_odometry* h);   // lo_odometry.cu: the divergence gate of lidar_odometry.cpp:53-65
 }  // namespace lo

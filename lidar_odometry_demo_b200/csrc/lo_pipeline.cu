@@ -1,9 +1,10 @@
-// LidarOdometry::processCloud (src/lidar_odometry.cpp:22-76) as a fused device pipeline for scans of up to
-// kFusedMaxPoints points (a VLP16 revolution is ~30 k): the stages in front of and behind CloudMatcher::align
-// are folded into a dozen launches. Per scan, in stream order:
+// LidarOdometry::processCloud (src/lidar_odometry.cpp:22-76) as ONE persistent cooperative kernel per scan, for scans
+// of up to kFusedMaxPoints points (a VLP16 revolution is ~30 k). One block per SM; the stages below are separated by
+// grid-wide barriers instead of kernel launches, poses and counts never leave the device, and the host reads back
+// 96 bytes when the kernel is done.
 //
-//   P1 prep        constant-velocity prediction (cpp:27-28,51) | min/max of `time` | zero classifier cells |
-//                  clear the two down-sampler tables
+//   P1 prep        constant-velocity prediction (cpp:27-28,51) | min/max of `time` | clear scratch and the two
+//                  down-sampler tables
 //   P2 deskew      pointTimeNormalize + transformNonRigid (cpp:25,30) | ring histogram of the classifier
 //   P3 cell_fill   classifier grid: ring x azimuth bin, last writer wins (cloud_classifier.h:21-71)
 //   P4 curvature   gather cell points + LOAM curvature (cloud_classifier.h:81-105)
@@ -11,22 +12,32 @@
 //   P6 scatter     ordered compaction into the filtered planar cloud | insert every point into both
 //                  VoxelGrid(vs,1) down-samplers (cpp:37-38,46-47): find-or-create voxel, atomicMin of the arrival index
 //   P7 select      which points are the first of their voxel (winners), block counts
-//   P8 emit        query cloud M (arrival order) | list of update winners U with their robin_map bucket
-//   P9 robin       four small kernels: the update set in the reference's tsl::robin_map iteration order
-//   align_kernel   CloudMatcher::align (lo_match.cu)
-//   gate, clean-up, key-frame insert (cpp:53-70) and the read-back as in lo_odometry.cu
+//   P8 emit        query cloud M (arrival order) | update winners U with their robin_map bucket, bucket histogram
+//   P9 a-d         the update set in the reference's tsl::robin_map iteration order: counting sort
+//   align          CloudMatcher::align (lo_align.cuh), cpp:49-51
+//   gate           Euler-angle divergence gate (cpp:53-65)
+//   clean-up       keyframe_.radiusCleanup (cpp:67)
+//   insert         transformWithNormals + keyframe_.addCloud (cpp:69-70): locate, ticket chain, write (lo_grid.cuh)
+//   read-back      pose + counters for the host
 //
-// Every per-point formula is the shared code of lo_stages.cuh, so the fused and the stage-by-stage paths
-// (lo_points.cu, lo_grid.cu) produce identical bits; tests/test_gpu_pipeline.py runs both against the oracle.
+// Every per-point formula is the shared code of lo_stages.cuh / lo_grid.cuh / lo_align.cuh, so this kernel and the
+// stage-by-stage entry points (lo_points.cu, lo_grid.cu, lo_match.cu) produce identical bits; the GPU tests run both
+// against the oracle.
 #include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
+#include "lo_align.cuh"
+#include "lo_grid.cuh"
 #include "lo_odometry.cuh"
 #include "lo_stages.cuh"
 
 namespace lo {
 
-constexpr int kPipeThreads = 256;
+constexpr int kPipeThreads = kAlignThreads;   // the whole scan runs in align's launch shape
+constexpr uint32_t kRobinBins = 256;       // coarse bins over the robin_map bucket array (<= kPipeThreads), see P9
 constexpr uint32_t kMaxPipeBlocks = 512;   // upper bound of the chunked grids (block_counts rows)
 
 struct alignas(16) DsSlot {                // slot of a VoxelGrid(vs, 1) down-sampler: the voxel's first point
@@ -53,7 +64,13 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     uint32_t* umember;                     // [n] bucket members before the tie groups are ordered
     uint32_t* rb_hist;                     // [rb_cap] winners per ideal bucket, then exclusive start of each bucket
     uint32_t* rb_fill;                     // [rb_cap] placement cursors
+    uint32_t* rb_coarse;                   // [kRobinBins] update winners per coarse bin of buckets
     int* rb_shift;                         // [1] max over sorted elements of (bucket - position)
+    uint32_t* kf_slot;                     // [n] key-frame insert: slot of update point i
+    uint32_t* kf_base;                     // [n] key-frame insert: first free entry of its voxel
+    float4* pair_o;                        // [n] align: plane origin per query (w = valid)
+    float4* pair_n;                        // [n] align: plane normal per query
+    double* partials;                      // [2][kMaxPipeBlocks][32] align: per-block partial sums
     uint32_t cell_cap, ds_cap, rb_cap;
 };
 
@@ -68,7 +85,7 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
         off += (bytes + 255) & ~static_cast<size_t>(255);
         return p;
     };
-    b.hist = reinterpret_cast<uint32_t*>(take(256 * 4));
+    b.hist = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
     b.layout = reinterpret_cast<uint32_t*>(take(16));
     b.block_counts = reinterpret_cast<uint32_t*>(take(3 * kMaxPipeBlocks * 4));
     b.cell_idx = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(b.cell_cap) * 4));
@@ -89,12 +106,18 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.rb_hist = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4 + 16));
     b.rb_fill = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
     b.rb_shift = reinterpret_cast<int*>(take(16));
+    b.rb_coarse = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
+    b.kf_slot = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.kf_base = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.pair_o = reinterpret_cast<float4*>(take(static_cast<size_t>(n) * 16));
+    b.pair_n = reinterpret_cast<float4*>(take(static_cast<size_t>(n) * 16));
+    b.partials = reinterpret_cast<double*>(take(static_cast<size_t>(2) * kMaxPipeBlocks * 32 * 8));
     return off;
 }
 
 // ---------------------------------------------------------------------------------------------------
 // P1. One thread does the pose prediction; everybody reduces min/max(time) and clears scratch.
-__global__ void __launch_bounds__(kPipeThreads) pipe_prep_kernel(OdomDev* s, const PointXYZIRT* __restrict__ in, uint32_t n,
+__device__ inline void phase_prep(OdomDev* s, const PointXYZIRT* __restrict__ in, uint32_t n,
                                                                   uint32_t* __restrict__ minmax, PipeBufs b) {
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
     if (tid == 0) {  // lidar_odometry.cpp:27-30,51
@@ -125,6 +148,7 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_prep_kernel(OdomDev* s, con
         atomicMax(&minmax[1], hi_v);
     }
     if (tid < 256) b.hist[tid] = 0;
+    if (tid < kRobinBins) b.rb_coarse[tid] = 0;
     if (tid == 0) *b.rb_shift = INT_MIN;
     for (uint32_t c = tid; c < b.rb_cap; c += nthreads) b.rb_hist[c] = 0;
     for (uint32_t c = tid; c < b.cell_cap; c += nthreads) b.cell_idx[c] = 0;
@@ -138,16 +162,15 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_prep_kernel(OdomDev* s, con
 }
 
 // P2. deskew + ring histogram (the reference keys its ring map by uint8_t, cloud_classifier.h:21-23)
-__global__ void __launch_bounds__(kPipeThreads) pipe_deskew_kernel(const OdomDev* __restrict__ s, const PointXYZIRT* __restrict__ in, uint32_t n,
+__device__ inline void phase_deskew(const OdomDev* __restrict__ s, const PointXYZIRT* __restrict__ in, uint32_t n,
                                                                     const uint32_t* __restrict__ minmax, PointXYZIRT* __restrict__ out,
                                                                     uint32_t* __restrict__ hist) {
     __shared__ uint32_t local[256];
-    local[threadIdx.x] = 0;  // blockDim.x == 256
+    if (threadIdx.x < 256) local[threadIdx.x] = 0;
     __syncthreads();
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        const Pose st = s->relative_inv, en = s->identity;   // transformNonRigid(cloud, relative.inverse(), Pose3D()) cpp:30
-        const float t_min = time_min_of(minmax), t_max = time_max_of(minmax);
+    const Pose st = s->relative_inv, en = s->identity;   // transformNonRigid(cloud, relative.inverse(), Pose3D()) cpp:30
+    const float t_min = time_min_of(minmax), t_max = time_max_of(minmax);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 a = reinterpret_cast<const float4*>(in)[2 * i];
         float4 bb = reinterpret_cast<const float4*>(in)[2 * i + 1];
         const float4 o = deskew_point(st, en, t_min, t_max - t_min, a, bb);
@@ -156,39 +179,44 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_deskew_kernel(const OdomDev
         atomicAdd(&local[__float_as_uint(bb.y) & 0xFF], 1u);   // ring is the low 16 bits of the second word
     }
     __syncthreads();
-    if (local[threadIdx.x]) atomicAdd(&hist[threadIdx.x], local[threadIdx.x]);
+    if (threadIdx.x < 256 && local[threadIdx.x]) atomicAdd(&hist[threadIdx.x], local[threadIdx.x]);
 }
 
 // Block-wide layout of the classifier grid from the ring histogram: W = largest ring population, row of ring r =
-// number of populated rings below r (std::map order), H = populated rings. Needs blockDim.x == 256.
+// number of populated rings below r (std::map order), H = populated rings. Needs blockDim.x >= 256.
 __device__ inline void block_layout(const uint32_t* __restrict__ hist, uint32_t* row_of_s, uint32_t* wh_s) {
     __shared__ uint32_t warp_cnt[8], warp_max[8];
-    const uint32_t c = hist[threadIdx.x];
-    const unsigned present = __ballot_sync(0xFFFFFFFFu, c != 0);
-    uint32_t mx = c;
-    for (int off = 16; off > 0; off >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) {
-        warp_cnt[warp] = __popc(present);
-        warp_max[warp] = mx;
+    unsigned present = 0;
+    if (threadIdx.x < 256) {   // whole warps: 8 of them
+        const uint32_t c = hist[threadIdx.x];
+        present = __ballot_sync(0xFFFFFFFFu, c != 0);
+        uint32_t mx = c;
+        for (int off = 16; off > 0; off >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
+        if (lane == 0) {
+            warp_cnt[warp] = __popc(present);
+            warp_max[warp] = mx;
+        }
     }
     __syncthreads();
-    uint32_t before = 0, total = 0, width = 0;
-    for (int w = 0; w < 8; w++) {
-        if (w < warp) before += warp_cnt[w];
-        total += warp_cnt[w];
-        width = max(width, warp_max[w]);
-    }
-    row_of_s[threadIdx.x] = before + __popc(present & ((1u << lane) - 1u));
-    if (threadIdx.x == 0) {
-        wh_s[0] = width;
-        wh_s[1] = total;
+    if (threadIdx.x < 256) {
+        uint32_t before = 0, total = 0, width = 0;
+        for (int w = 0; w < 8; w++) {
+            if (w < warp) before += warp_cnt[w];
+            total += warp_cnt[w];
+            width = max(width, warp_max[w]);
+        }
+        row_of_s[threadIdx.x] = before + __popc(present & ((1u << lane) - 1u));
+        if (threadIdx.x == 0) {
+            wh_s[0] = width;
+            wh_s[1] = total;
+        }
     }
     __syncthreads();
 }
 
 // P3. cloud_classifier.h:44-56: cell (ring row, azimuth bin) <- point, last writer (largest input index) wins
-__global__ void __launch_bounds__(kPipeThreads) pipe_cell_fill_kernel(const PointXYZIRT* __restrict__ desk, uint32_t n, PipeBufs b) {
+__device__ inline void phase_cell_fill(const PointXYZIRT* __restrict__ desk, uint32_t n, PipeBufs b) {
     __shared__ uint32_t row_of[256], wh[2];
     block_layout(b.hist, row_of, wh);
     const uint32_t W = wh[0], H = wh[1];
@@ -199,13 +227,13 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_cell_fill_kernel(const Poin
         b.layout[2] = overflow ? 1u : 0u;
         b.layout[3] = overflow ? 0u : W * H;
     }
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n || overflow) return;
-    const float4 a = reinterpret_cast<const float4*>(desk)[2 * i];
-    const uint32_t ring = desk[i].ring & 0xFF;
-    uint32_t col;
-    if (!azimuth_column(a.x, a.y, W, col)) return;
-    atomicMax(&b.cell_idx[row_of[ring] * W + col], i + 1);
+    if (overflow) return;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = reinterpret_cast<const float4*>(desk)[2 * i];
+        const uint32_t ring = desk[i].ring & 0xFF;
+        uint32_t col;
+        if (azimuth_column(a.x, a.y, W, col)) atomicMax(&b.cell_idx[row_of[ring] * W + col], i + 1);
+    }
 }
 
 __device__ inline float4 cell_point(const PointXYZIRT* __restrict__ desk, const uint32_t* __restrict__ cell_idx, uint32_t c) {
@@ -217,7 +245,7 @@ __device__ inline float4 cell_point(const PointXYZIRT* __restrict__ desk, const 
 }
 
 // P4. gather + curvature
-__global__ void __launch_bounds__(kPipeThreads) pipe_curvature_kernel(const PointXYZIRT* __restrict__ desk, PipeBufs b) {
+__device__ inline void phase_curvature(const PointXYZIRT* __restrict__ desk, PipeBufs b) {
     const uint32_t total = b.layout[3];
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < total; c += gridDim.x * blockDim.x) {
         b.cellp[c] = cell_point(desk, b.cell_idx, c);
@@ -260,15 +288,15 @@ __device__ inline void block_prefix(const uint32_t* __restrict__ counts, uint32_
     __syncthreads();
 }
 
-// number of threads with flag set before this thread in the block, and the block's total (blockDim.x == 256)
+// number of threads with flag set before this thread in the block, and the block's total
 __device__ inline uint32_t block_rank(bool flag, uint32_t& tile_total) {
-    __shared__ uint32_t warp_cnt[8];
+    __shared__ uint32_t warp_cnt[32];
     const unsigned m = __ballot_sync(0xFFFFFFFFu, flag);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     if (lane == 0) warp_cnt[warp] = __popc(m);
     __syncthreads();
     uint32_t before = 0, total = 0;
-    for (int w = 0; w < 8; w++) {
+    for (int w = 0; w < nwarps; w++) {
         if (w < warp) before += warp_cnt[w];
         total += warp_cnt[w];
     }
@@ -278,7 +306,7 @@ __device__ inline uint32_t block_rank(bool flag, uint32_t& tile_total) {
 }
 
 // P5. planar test + normal + range filter -> cnormal.w flag, per-block counts
-__global__ void __launch_bounds__(kPipeThreads) pipe_planar_kernel(PipeBufs b, float lo2, float hi2) {
+__device__ inline void phase_planar(PipeBufs b, float lo2, float hi2) {
     const uint32_t total = b.layout[3], W = b.layout[0];
     uint32_t begin, end;
     chunk_range(total, begin, end);
@@ -320,7 +348,7 @@ __device__ inline uint32_t ds_insert(DsSlot* __restrict__ slots, uint32_t mask, 
 }
 
 // P6. filtered planar cloud in cell order (cloud_classifier.h:114-165 walks rays then columns) + both down-samplers
-__global__ void __launch_bounds__(kPipeThreads) pipe_scatter_kernel(OdomDev* s, PipeBufs b, PointNormal* __restrict__ filtered, float vs_u,
+__device__ inline void phase_scatter(OdomDev* s, PipeBufs b, PointNormal* __restrict__ filtered, float vs_u,
                                                                      float vs_m, int with_match, uint32_t* __restrict__ range_err) {
     const uint32_t total = b.layout[3];
     uint32_t begin, end, before, all;
@@ -349,7 +377,7 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_scatter_kernel(OdomDev* s, 
 }
 
 // P7. winners of the two down-samplers, per-block counts
-__global__ void __launch_bounds__(kPipeThreads) pipe_select_kernel(PipeBufs b, int with_match) {
+__device__ inline void phase_select(PipeBufs b, int with_match) {
     uint32_t before, total;
     block_prefix(b.block_counts, before, total);   // total = n_planar
     uint32_t begin, end;
@@ -375,6 +403,12 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_select_kernel(PipeBufs b, i
     }
 }
 
+__device__ inline uint32_t robin_bin_shift(uint32_t buckets) {   // log2(buckets per coarse bin)
+    uint32_t shift = 0;
+    while ((buckets >> shift) > kRobinBins) shift++;
+    return shift;
+}
+
 __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map after n insertions: 2 * pow2ceil(n)
     uint32_t c = 2;
     while (c < 2 * n) c <<= 1;
@@ -383,7 +417,7 @@ __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map a
 
 // P8. query cloud (matching_downsampler.getCloudWithoutNormals(), cpp:50 — emitted in arrival order: its order only
 // decides the order of the residual sum) and the update winners with their ideal robin_map bucket
-__global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
+__device__ inline void phase_emit(OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
                                                                   PointXYZ* __restrict__ query, int with_match) {
     uint32_t before, total, bu, nu, bm, nm;
     block_prefix(b.block_counts, before, total);
@@ -393,7 +427,7 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, Pip
         s->n_update = nu;
         s->n_query = nm;
     }
-    const uint32_t buckets = robin_bucket_count(nu);
+    const uint32_t buckets = robin_bucket_count(nu), bin_shift = robin_bin_shift(buckets);
     uint32_t begin, end;
     chunk_range(total, begin, end);
     for (uint32_t base = begin; base < end; base += blockDim.x) {
@@ -417,6 +451,7 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, Pip
             const uint32_t bucket = reference_hash22(ix, iy, iz) & (buckets - 1);
             b.ubucket[bu + ru] = bucket;
             atomicAdd(&b.rb_hist[bucket], 1u);
+            atomicAdd(&b.rb_coarse[bucket >> bin_shift], 1u);
         }
         if (wm) {
             const float4 p = *reinterpret_cast<const float4*>(filtered + i);
@@ -433,43 +468,56 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_emit_kernel(OdomDev* s, Pip
 // elements sorted by ideal bucket b = hash22 & (C-1); a cluster that runs past the last bucket wraps to the front
 // (lo_robin.cu states the same rule for the stage-by-stage path). Counting sort by b: P8 histogrammed the buckets;
 // 9a scans the histogram, 9b places the winners, 9c orders every tie group by arrival and finds the wrap, 9d emits.
-constexpr int kScanThreads = 1024;
-
-__global__ void __launch_bounds__(kScanThreads, 1) pipe_robin_scan_kernel(const OdomDev* __restrict__ s, PipeBufs b) {
-    __shared__ uint32_t warp_sums[kScanThreads / 32];
-    const uint32_t n = s->n_update;
-    if (n == 0) return;
-    const uint32_t C = robin_bucket_count(n);
-    const uint32_t per = (C + kScanThreads - 1) / kScanThreads;
-    const uint32_t c0 = min(C, threadIdx.x * per), c1 = min(C, c0 + per);
-    uint32_t local = 0;
-    for (uint32_t c = c0; c < c1; c++) local += b.rb_hist[c];
-    uint32_t incl = local;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// exclusive prefix of v over the block's threads, and the block total
+__device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
+    __shared__ uint32_t warp_sums[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    uint32_t incl = v;
     for (int off = 1; off < 32; off <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, off);
-        if (lane >= off) incl += v;
+        const uint32_t u = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+        if (lane >= off) incl += u;
     }
     if (lane == 31) warp_sums[warp] = incl;
     __syncthreads();
-    uint32_t run = incl - local;
-    for (int w = 0; w < warp; w++) run += warp_sums[w];
-    for (uint32_t c = c0; c < c1; c++) {
-        const uint32_t v = b.rb_hist[c];
-        b.rb_hist[c] = run;    // exclusive start of bucket c
-        b.rb_fill[c] = run;
-        run += v;
+    uint32_t before = 0, all = 0;
+    for (int w = 0; w < nwarps; w++) {
+        const uint32_t ws = warp_sums[w];
+        if (w < warp) before += ws;
+        all += ws;
     }
-    if (c1 == C && c0 < c1) b.rb_hist[C] = run;  // = n
+    __syncthreads();
+    total = all;
+    return before + incl - v;
 }
 
-__global__ void __launch_bounds__(kPipeThreads) pipe_robin_place_kernel(const OdomDev* __restrict__ s, PipeBufs b) {
+// 9a. bucket starts. P8 also histogrammed the buckets into <= kRobinBins coarse bins, so every bin is scanned by
+// one block on its own: start of the bin = sum of the coarse counts before it.
+__device__ inline void phase_robin_scan(const OdomDev* __restrict__ s, PipeBufs b) {
+    const uint32_t n = s->n_update;
+    if (n == 0) return;
+    const uint32_t C = robin_bucket_count(n);
+    const uint32_t shift = robin_bin_shift(C), bins = C >> shift, per = 1u << shift;   // per <= kRobinBins <= blockDim.x
+    for (uint32_t bin = blockIdx.x; bin < bins; bin += gridDim.x) {
+        uint32_t base, bin_total;
+        block_exclusive_scan(threadIdx.x < bin ? b.rb_coarse[threadIdx.x] : 0u, base);
+        const uint32_t c = (bin << shift) + threadIdx.x;
+        const uint32_t v = threadIdx.x < per ? b.rb_hist[c] : 0u;
+        const uint32_t start = base + block_exclusive_scan(v, bin_total);
+        if (threadIdx.x < per) {
+            b.rb_hist[c] = start;    // exclusive start of bucket c
+            b.rb_fill[c] = start;
+        }
+        if (bin == bins - 1 && threadIdx.x == per - 1) b.rb_hist[C] = start + v;   // = n
+    }
+}
+
+__device__ inline void phase_robin_place(const OdomDev* __restrict__ s, PipeBufs b) {
     const uint32_t n = s->n_update;
     for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
         b.umember[atomicAdd(&b.rb_fill[b.ubucket[j]], 1u)] = j;
 }
 
-__global__ void __launch_bounds__(kPipeThreads) pipe_robin_order_kernel(const OdomDev* __restrict__ s, PipeBufs b) {
+__device__ inline void phase_robin_order(const OdomDev* __restrict__ s, PipeBufs b) {
     const uint32_t n = s->n_update;
     int shift = INT_MIN;
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
@@ -486,7 +534,7 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_robin_order_kernel(const Od
     if ((threadIdx.x & 31) == 0 && shift != INT_MIN) atomicMax(b.rb_shift, shift);
 }
 
-__global__ void __launch_bounds__(kPipeThreads) pipe_robin_emit_kernel(const OdomDev* __restrict__ s, PipeBufs b,
+__device__ inline void phase_robin_emit(const OdomDev* __restrict__ s, PipeBufs b,
                                                                         const PointNormal* __restrict__ filtered, PointNormal* __restrict__ update) {
     const uint32_t n = s->n_update;
     if (n == 0) return;
@@ -503,67 +551,234 @@ __global__ void __launch_bounds__(kPipeThreads) pipe_robin_emit_kernel(const Odo
     }
 }
 
+// lidar_odometry.cpp:53-65: Euler-angle divergence gate, then current = new (one thread)
+__device__ inline void phase_gate(OdomDev* s, float threshold) {
+    const Pose nw = s->next, cur = s->current;
+    Pose a = identity_pose(), c = identity_pose();   // new.rotation * current.rotation.inverse()
+    a.w = nw.w; a.x = nw.x; a.y = nw.y; a.z = nw.z;
+    c.w = cur.w; c.x = cur.x; c.y = cur.y; c.z = cur.z;
+    const Pose d = pose_compose(a, pose_inverse(c));
+    float r[9];
+    rotation_matrix_f(d.w, d.x, d.y, d.z, r);
+    float ang[3];
+    euler_angles_012(r, ang);
+    bool ok = true;
+    const float pi_f = 3.14159265358979323846f;
+    for (int k = 0; k < 3; k++) {
+        const float deg = (ang[k] * 180.0f) / pi_f;
+        const float m = fabsf(deg);
+        ok = ok && (m < threshold || m > 180 - threshold);
+    }
+    Pose out = nw;
+    if (!ok) {
+        out = s->guess;
+        s->unstable = 1;
+    }
+    s->current = out;
+    s->center[0] = out.t[0]; s->center[1] = out.t[1]; s->center[2] = out.t[2];
+}
+
+struct ScanArgs {
+    OdomDev* s;
+    const PointXYZIRT* scan;
+    PointXYZIRT* desk;
+    PointNormal* filtered;
+    PointNormal* update;
+    PointXYZ* query;
+    uint32_t* minmax;
+    PipeBufs b;
+    GridView kf;                 // key-frame grid (after the host made room for this scan's insert)
+    uint32_t kf_capacity;
+    uint32_t* kf_counters;
+    uint32_t* kf_free_list;
+    uint32_t ticket_base;        // arrival ticket of the first update point
+    ScanReadback* readback;
+    uint32_t n;
+    int first;                   // the key-frame is empty: bootstrap scan (cpp:40-44)
+    float lo2, hi2, vs_u, vs_m, cleanup_range, gate_threshold;
+    long long* trace;
+};
+
+__global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
+    cg::grid_group grid = cg::this_grid();
+    OdomDev* s = p.s;
+    const int with_match = p.first ? 0 : 1;
+    uint32_t* range_err = p.kf_counters + GC_RANGE_ERR;
+    int trace_n = 0;
+#define LO_SCAN_TRACE(tag)                                                     \
+    do {                                                                       \
+        if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < 500) { \
+            p.trace[2 * trace_n] = (tag);                                      \
+            p.trace[2 * trace_n + 1] = clock64();                              \
+            trace_n++;                                                         \
+        }                                                                      \
+    } while (0)
+    LO_SCAN_TRACE(100);
+    phase_prep(s, p.scan, p.n, p.minmax, p.b);
+    grid.sync();
+    LO_SCAN_TRACE(101);
+    phase_deskew(s, p.scan, p.n, p.minmax, p.desk, p.b.hist);
+    grid.sync();
+    LO_SCAN_TRACE(102);
+    phase_cell_fill(p.desk, p.n, p.b);
+    grid.sync();
+    LO_SCAN_TRACE(103);
+    phase_curvature(p.desk, p.b);
+    grid.sync();
+    LO_SCAN_TRACE(104);
+    phase_planar(p.b, p.lo2, p.hi2);
+    grid.sync();
+    LO_SCAN_TRACE(105);
+    phase_scatter(s, p.b, p.filtered, p.vs_u, p.vs_m, with_match, range_err);
+    grid.sync();
+    LO_SCAN_TRACE(106);
+    phase_select(p.b, with_match);
+    grid.sync();
+    LO_SCAN_TRACE(107);
+    phase_emit(s, p.b, p.filtered, p.query, with_match);
+    grid.sync();
+    LO_SCAN_TRACE(108);
+    phase_robin_scan(s, p.b);
+    grid.sync();
+    LO_SCAN_TRACE(109);
+    phase_robin_place(s, p.b);
+    grid.sync();
+    LO_SCAN_TRACE(110);
+    phase_robin_order(s, p.b);
+    grid.sync();
+    LO_SCAN_TRACE(111);
+    phase_robin_emit(s, p.b, p.filtered, p.update);
+    grid.sync();
+    LO_SCAN_TRACE(112);
+    const Pose* insert_pose = nullptr;   // first scan: inserted un-transformed (cpp:42)
+    if (!p.first) {
+        AlignArgs a;                     // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
+        a.g = p.kf;
+        a.queries = p.query;
+        a.m = p.n;
+        a.m_dev = &s->n_query;
+        a.pair_o = p.b.pair_o;
+        a.pair_n = p.b.pair_n;
+        a.partials = p.b.partials;
+        a.guess = reinterpret_cast<const float*>(&s->guess);
+        a.out_pose = reinterpret_cast<float*>(&s->next);
+        a.stats = &s->align;
+        a.max_dist = 0.3f;               // cloud_matcher.cpp:139
+        a.trace = p.trace;
+        a.trace_start = trace_n;
+        align_device(a, grid);
+        if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_n = static_cast<int>(p.trace[1000]);
+        grid.sync();
+        if (blockIdx.x == 0 && threadIdx.x == 0) phase_gate(s, p.gate_threshold);   // cpp:53-65
+        grid.sync();
+        LO_SCAN_TRACE(120);
+        for (uint32_t sl = blockIdx.x * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += gridDim.x * blockDim.x)
+            grid_cleanup_slot(sl, p.kf, s->center, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
+        grid.sync();
+        LO_SCAN_TRACE(121);
+        insert_pose = &s->current;       // transformWithNormals fused into the load (cpp:69)
+    }
+    // keyframe_.addCloud(update) (cpp:42 / cpp:70)
+    const uint32_t nu = min(p.n, s->n_update);
+    const PointSource src{reinterpret_cast<const float*>(p.update), 12u, 1};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
+        grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
+    grid.sync();
+    LO_SCAN_TRACE(122);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
+        grid_chain_item(i, p.ticket_base, p.kf, p.b.kf_slot, p.b.kf_base);
+    grid.sync();
+    LO_SCAN_TRACE(123);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
+        grid_write_item(i, src, p.ticket_base, insert_pose, p.kf, p.kf_counters, p.b.kf_slot, p.b.kf_base);
+    grid.sync();
+    LO_SCAN_TRACE(124);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // read-back block for the host; re-arm the next scan's time min/max
+        grid_fix_counters(p.kf_counters);
+        ScanReadback* out = p.readback;
+        pose_to7(s->current, out->pose);
+        out->n_planar = s->n_planar;
+        out->n_update = s->n_update;
+        out->n_query = s->n_query;
+        out->unstable = s->unstable;
+        out->outer_iterations = s->align.outer_iterations;
+        for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
+        p.minmax[0] = 0xFFFFFFFFu;
+        p.minmax[1] = 0u;
+        if (p.trace) p.trace[1000] = trace_n;
+    }
+#undef LO_SCAN_TRACE
+}
+
 }  // namespace lo
 
 using namespace lo;
 
 int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
     lo_ctx* ctx = h->ctx;
-    OdomDev* s = h->d_state;
+    lo_grid* kf = h->keyframe;
     PipeBufs b;
-    const size_t bytes = carve(b, nullptr, n);
+    const size_t bytes = carve(b, nullptr, std::max<uint32_t>(n, 1));
     LO_TRY(h->fused.ensure(bytes));
-    carve(b, h->fused.as<char>(), n);
+    carve(b, h->fused.as<char>(), std::max<uint32_t>(n, 1));
     LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
     LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     LO_TRY(h->update.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     LO_TRY(h->query.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZ)));
-    const bool first = h->keyframe->h_counters[GC_VOXELS] == 0;  // cpp:40 (host mirror from the last scan's read-back)
-    const int with_match = first ? 0 : 1;
-    const unsigned G = std::min<unsigned>(static_cast<unsigned>(ctx->sm_count), kMaxPipeBlocks);
-    const unsigned per_point = blocks_for(n, kPipeThreads);
-    PointXYZIRT* desk = h->deskewed.as<PointXYZIRT>();
-    PointNormal* filtered = h->filtered.as<PointNormal>();
-    const float lo2 = h->params.lidar_min_range * h->params.lidar_min_range, hi2 = h->params.lidar_max_range * h->params.lidar_max_range;
-    uint32_t* range_err = h->keyframe->counters + GC_RANGE_ERR;
-
-    pipe_prep_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, d_scan, n, h->d_minmax, b);
-    LO_LAUNCHED(ctx);
-    if (n == 0) return LO_OK;
-    pipe_deskew_kernel<<<per_point, kPipeThreads, 0, ctx->stream>>>(s, d_scan, n, h->d_minmax, desk, b.hist);
-    LO_LAUNCHED(ctx);
-    pipe_cell_fill_kernel<<<per_point, kPipeThreads, 0, ctx->stream>>>(desk, n, b);
-    LO_LAUNCHED(ctx);
-    pipe_curvature_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(desk, b);
-    LO_LAUNCHED(ctx);
-    pipe_planar_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(b, lo2, hi2);
-    LO_LAUNCHED(ctx);
-    pipe_scatter_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->params.keyframe_update_voxel_size,
-                                                             h->params.keyframe_matching_voxel_size, with_match, range_err);
-    LO_LAUNCHED(ctx);
-    pipe_select_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(b, with_match);
-    LO_LAUNCHED(ctx);
-    pipe_emit_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->query.as<PointXYZ>(), with_match);
-    LO_LAUNCHED(ctx);
-    pipe_robin_scan_kernel<<<1, kScanThreads, 0, ctx->stream>>>(s, b);
-    LO_LAUNCHED(ctx);
-    pipe_robin_place_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b);
-    LO_LAUNCHED(ctx);
-    pipe_robin_order_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b);
-    LO_LAUNCHED(ctx);
-    pipe_robin_emit_kernel<<<G, kPipeThreads, 0, ctx->stream>>>(s, b, filtered, h->update.as<PointNormal>());
-    LO_LAUNCHED(ctx);
-    if (first) {
-        LO_TRY(grid_add_dev(h->keyframe, h->update.p, n, 1, nullptr, &s->n_update));  // cpp:42
-        return LO_OK;
+    static int blocks_per_sm = 0;
+    if (blocks_per_sm == 0) {
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, 0));
+        if (blocks_per_sm < 1) {
+            set_error("the per-scan kernel does not fit on an SM");
+            return LO_E_CUDA;
+        }
     }
-    // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
-    LO_TRY(align_enqueue(h->keyframe, h->query.as<PointXYZ>(), n, &s->n_query, reinterpret_cast<const float*>(&s->guess),
-                         reinterpret_cast<float*>(&s->next), &s->align));
-    LO_TRY(odom_gate_enqueue(h));                                                         // cpp:53-65
-    LO_TRY(grid_cleanup_dev(h->keyframe, s->center, h->params.keyframe_cleanup_range));  // cpp:67
-    LO_TRY(grid_add_dev(h->keyframe, h->update.p, n, 1, &s->current, &s->n_update));      // cpp:69-70, transform fused into the load
+    const int blocks = std::min<int>(ctx->sm_count, kMaxPipeBlocks);   // one block per SM
+    LO_TRY(grid_reserve(kf, n));   // room for this scan's insert; may rebuild the table, so take the view afterwards
+    ScanArgs p;
+    p.s = h->d_state;
+    p.scan = d_scan;
+    p.desk = h->deskewed.as<PointXYZIRT>();
+    p.filtered = h->filtered.as<PointNormal>();
+    p.update = h->update.as<PointNormal>();
+    p.query = h->query.as<PointXYZ>();
+    p.minmax = h->d_minmax;
+    p.b = b;
+    p.kf = kf->view();
+    p.kf_capacity = kf->capacity;
+    p.kf_counters = kf->counters;
+    p.kf_free_list = kf->free_list;
+    p.ticket_base = kf->h_counters[GC_TICKET];
+    p.readback = h->d_readback;
+    p.n = n;
+    p.first = kf->h_counters[GC_VOXELS] == 0 ? 1 : 0;  // cpp:40 (host mirror from the last scan's read-back)
+    p.lo2 = h->params.lidar_min_range * h->params.lidar_min_range;
+    p.hi2 = h->params.lidar_max_range * h->params.lidar_max_range;
+    p.vs_u = h->params.keyframe_update_voxel_size;
+    p.vs_m = h->params.keyframe_matching_voxel_size;
+    p.cleanup_range = h->params.keyframe_cleanup_range;
+    p.gate_threshold = h->params.angular_divergence_threshold;
+    static const bool want_trace = getenv("LO_SCAN_TRACE") != nullptr;   // developer aid, see fused_trace_dump
+    p.trace = nullptr;
+    if (want_trace) {
+        LO_TRY(ctx->tmp_d.ensure(1001 * sizeof(long long)));
+        p.trace = ctx->tmp_d.as<long long>();
+    }
+    void* kargs[] = {&p};
+    LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream));
+    ctx->launches++;
+    kf->h_counters[GC_TICKET] = p.ticket_base + n;
+    if (!p.first) kf->cleaned = true;
     return LO_OK;
 }
 
 void lo::fused_release(lo_odometry* h) { h->fused.release(); }
+
+// LO_SCAN_TRACE=1: phase timeline of block 0 of the last scan_kernel, in SM clocks (call after the stream has drained)
+void lo::fused_trace_dump(lo_odometry* h) {
+    if (!getenv("LO_SCAN_TRACE") || !h->ctx->tmp_d.p) return;
+    static long long t[1001];
+    if (cudaMemcpy(t, h->ctx->tmp_d.p, sizeof(t), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    for (long long k = 1; k < t[1000] && k < 500; k++) fprintf(stderr, "trace %lld %lld\n", t[2 * k], t[2 * k + 1] - t[2 * (k - 1) + 1]);
+    fprintf(stderr, "trace end %lld\n", t[1000] > 0 ? t[2 * (t[1000] - 1) + 1] - t[1] : 0);
+}
