@@ -53,8 +53,10 @@ __host__ __device__ inline void quaternion_plus(const double x[4], const double 
         for (int i = 0; i < 4; i++) out[i] = x[i];
         return;
     }
-    const double s = sin(nd) / nd;
-    const double q0 = cos(nd), q1 = s * d[0], q2 = s * d[1], q3 = s * d[2];
+    double sn, q0;
+    sincos(nd, &sn, &q0);
+    const double s = sn / nd;
+    const double q1 = s * d[0], q2 = s * d[1], q3 = s * d[2];
     out[0] = q0 * x[0] - q1 * x[1] - q2 * x[2] - q3 * x[3];
     out[1] = q0 * x[1] + q1 * x[0] + q2 * x[3] - q3 * x[2];
     out[2] = q0 * x[2] - q1 * x[3] + q2 * x[0] + q3 * x[1];
@@ -109,37 +111,41 @@ __host__ __device__ inline bool lm_begin(LmState& s, const double x0[7], const d
     return lm_record(s, 0.0);
 }
 
-// Solve (Hs + diag(d2)) y = gs by Cholesky; false if not positive definite / not finite.
+// Solve (Hs + diag(d2)) y = gs by the square-root-free Cholesky factorisation A = L D L' (unit lower L); false if A is
+// not positive definite or the solution is not finite. One reciprocal per column is the only long-latency operation
+// on the dependent chain (the whole step logic runs on one thread between two evaluations).
 __host__ __device__ inline bool solve6(const double Hs[21], const double d2[6], const double gs[6], double y[6]) {
-    double L[6][6];
+    double L[6][6], LD[6][6], inv[6];   // LD[a][k] = L[a][k] * D[k]
 #pragma unroll
-    for (int a = 0; a < 6; a++)
+    for (int j = 0; j < 6; j++) {
+        double d = Hs[tri(j, j)] + d2[j];
 #pragma unroll
-        for (int b = 0; b <= a; b++) {
-            double v = Hs[tri(b, a)] + (a == b ? d2[a] : 0.0);
+        for (int k = 0; k < j; k++) d = fma(-LD[j][k], L[j][k], d);
+        if (!(d > 0.0)) return false;
+        inv[j] = 1.0 / d;
 #pragma unroll
-            for (int k = 0; k < b; k++) v -= L[a][k] * L[b][k];
-            if (a == b) {
-                if (!(v > 0.0)) return false;
-                L[a][a] = sqrt(v);
-            } else {
-                L[a][b] = v / L[b][b];
-            }
+        for (int a = j + 1; a < 6; a++) {
+            double v = Hs[tri(j, a)];
+#pragma unroll
+            for (int k = 0; k < j; k++) v = fma(-LD[a][k], L[j][k], v);
+            LD[a][j] = v;
+            L[a][j] = v * inv[j];
         }
+    }
     double z[6];
 #pragma unroll
     for (int a = 0; a < 6; a++) {
         double v = gs[a];
 #pragma unroll
-        for (int k = 0; k < a; k++) v -= L[a][k] * z[k];
-        z[a] = v / L[a][a];
+        for (int k = 0; k < a; k++) v = fma(-L[a][k], z[k], v);
+        z[a] = v;
     }
 #pragma unroll
     for (int a = 5; a >= 0; a--) {
-        double v = z[a];
+        double v = z[a] * inv[a];
 #pragma unroll
-        for (int k = a + 1; k < 6; k++) v -= L[k][a] * y[k];
-        y[a] = v / L[a][a];
+        for (int k = a + 1; k < 6; k++) v = fma(-L[k][a], y[k], v);
+        y[a] = v;
     }
 #pragma unroll
     for (int a = 0; a < 6; a++)
@@ -162,8 +168,9 @@ __host__ __device__ inline bool lm_propose(LmState& s) {
 #pragma unroll
             for (int a = 0; a < 6; a++) s.diagonal[a] = fmin(fmax(Hs[tri(a, a)], 1e-6), 1e32);
         double d2[6], y[6], step[6];
+        const double inv_radius = 1.0 / s.radius;
 #pragma unroll
-        for (int a = 0; a < 6; a++) d2[a] = s.diagonal[a] / s.radius;
+        for (int a = 0; a < 6; a++) d2[a] = s.diagonal[a] * inv_radius;
         const bool ok = solve6(Hs, d2, gs, y);
         s.reuse_diagonal = 1;
         bool valid = false;
