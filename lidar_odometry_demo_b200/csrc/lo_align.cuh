@@ -85,14 +85,18 @@ __device__ inline void accumulate_lane(double* row, const Terms& t) {
     row[28] += 1.0;
 }
 
+// sum over lanes 0 .. 2^kSteps - 1 (the other lanes are ignored), result in lane 0
+template <int kSteps = 5>
 __device__ inline double warp_sum(double v) {
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(kFullMask, v, off);
+    for (int off = (1 << kSteps) >> 1; off > 0; off >>= 1) v += __shfl_down_sync(kFullMask, v, off);
     return v;
 }
 
 // all 32 lanes hold (at most) one pair each; products are reduced by shuffles one value at a time so that
-// only j[6], rc and one temporary are live (keeps the kernel under 64 registers)
+// only j[6], rc and one temporary are live (keeps the kernel under 64 registers). kSteps < 5: only lanes below
+// 2^kSteps hold pairs.
+template <int kSteps = 5>
 __device__ inline void accumulate_warp(double* row, const Terms& t, bool valid, int lane) {
     const double m = valid ? 1.0 : 0.0;
     int at = 0;
@@ -100,17 +104,17 @@ __device__ inline void accumulate_warp(double* row, const Terms& t, bool valid, 
     for (int a = 0; a < 6; a++)
 #pragma unroll
         for (int b = a; b < 6; b++) {
-            const double v = warp_sum(m * (t.j[a] * t.j[b]));
+            const double v = warp_sum<kSteps>(m * (t.j[a] * t.j[b]));
             if (lane == 0) row[at] += v;
             at++;
         }
 #pragma unroll
     for (int a = 0; a < 6; a++) {
-        const double v = warp_sum(m * (t.j[a] * t.rc));
+        const double v = warp_sum<kSteps>(m * (t.j[a] * t.rc));
         if (lane == 0) row[21 + a] += v;
     }
-    const double c = warp_sum(m * t.cost);
-    const double k = warp_sum(m);
+    const double c = warp_sum<kSteps>(m * t.cost);
+    const double k = warp_sum<kSteps>(m);
     if (lane == 0) {
         row[27] += c;
         row[28] += k;
@@ -209,6 +213,8 @@ __device__ inline void align_device(AlignArgs a, cg::grid_group& grid) {
     const uint32_t gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
     const int nblocks = gridDim.x;
+    const LaneOffset lofs = lane_offset(lane);
+    const uint32_t my_queries = gwarp < a.m ? (a.m - gwarp + total_warps - 1) / total_warps : 0u;
     double* row = rows + (threadIdx.x >> 5) * kRow;
     for (int k = threadIdx.x; k < (kAlignThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
     if (threadIdx.x < 7) pose_s[threadIdx.x] = a.guess[threadIdx.x];
@@ -229,19 +235,53 @@ __device__ inline void align_device(AlignArgs a, cg::grid_group& grid) {
         const QueryTransform tf = make_query_transform(pf);
         double x0[7] = {pf.w, pf.x, pf.y, pf.z, pf.t[0], pf.t[1], pf.t[2]};  // cloud_matcher.cpp:122-131
         const EvalPoint ep0 = make_eval_point(x0);
-        for (uint32_t qi = gwarp; qi < a.m; qi += total_warps) {
-            const PointXYZ q = a.queries[qi];
-            float wq[3];
-            transform_query(tf, q.x, q.y, q.z, wq);
-            const Found f = nn_search_warp(a.g, wq, max_d2, lane, wl);
-            if (lane == 0) {
-                a.pair_o[qi] = make_float4(f.o[0], f.o[1], f.o[2], f.valid ? 1.f : 0.f);
-                a.pair_n[qi] = make_float4(f.n[0], f.n[1], f.n[2], 0.f);
-                if (f.valid) {
-                    const float pq[3] = {q.x, q.y, q.z};
-                    accumulate_lane(row, pair_terms(ep0, pq, f.o, f.n));
+        // every warp walks its queries (gwarp, gwarp + total_warps, ...: neighbouring queries cost about the same, so they are
+        // dealt out to different warps) in tiles of 32: lane l transforms query l (findMatchingPairs, voxel_grid.h:217-223),
+        // the 27-lane search runs once per query with the slot loads of query j+1 in flight while query j is scanned, lane j
+        // keeps the correspondence of query j; then the tile's normals are fetched in one round and all lanes evaluate
+        // their pair at x0 in parallel.
+        for (uint32_t base = 0; base < my_queries; base += 32) {
+            const uint32_t mine = gwarp + (base + lane) * total_warps;
+            const bool have = base + lane < my_queries;
+            PointXYZ q{0.f, 0.f, 0.f, 0.f};
+            if (have) q = a.queries[mine];
+            const uint32_t in_tile = min(32u, my_queries - base);
+            float own[3];
+            transform_query(tf, q.x, q.y, q.z, own);
+            const int oi[3] = {clamp_axis(axis_index(own[0], a.g.voxel_size)), clamp_axis(axis_index(own[1], a.g.voxel_size)),
+                               clamp_axis(axis_index(own[2], a.g.voxel_size))};
+            bool my_valid = false;
+            float my_o[3] = {0.f, 0.f, 0.f}, my_n[3] = {0.f, 0.f, 0.f};
+            uint32_t my_at = 0;
+            Probe next = probe_issue_at(a.g, __shfl_sync(kFullMask, oi[0], 0), __shfl_sync(kFullMask, oi[1], 0), __shfl_sync(kFullMask, oi[2], 0), lofs);
+            for (uint32_t j = 0; j < in_tile; j++) {
+                uint32_t vid, cnt;
+                probe_resolve(a.g, next, vid, cnt);
+                const int jj = static_cast<int>(j);
+                const float cur[3] = {__shfl_sync(kFullMask, own[0], jj), __shfl_sync(kFullMask, own[1], jj), __shfl_sync(kFullMask, own[2], jj)};
+                if (j + 1 < in_tile)
+                    next = probe_issue_at(a.g, __shfl_sync(kFullMask, oi[0], jj + 1), __shfl_sync(kFullMask, oi[1], jj + 1),
+                                          __shfl_sync(kFullMask, oi[2], jj + 1), lofs);
+                const Hit hit = scan_candidates(a.g, cur, max_d2, lane, wl, vid, cnt);
+                if (lane == jj) {
+                    my_valid = hit.valid;
+                    my_at = hit.at;
+                    for (int k = 0; k < 3; k++) my_o[k] = hit.o[k];
                 }
             }
+            if (my_valid) {
+                const float4 nv = __ldg(a.g.normals + my_at);
+                my_n[0] = nv.x; my_n[1] = nv.y; my_n[2] = nv.z;
+            }
+            if (have) {
+                a.pair_o[mine] = make_float4(my_o[0], my_o[1], my_o[2], my_valid ? 1.f : 0.f);
+                a.pair_n[mine] = make_float4(my_n[0], my_n[1], my_n[2], 0.f);
+            }
+            const float pq[3] = {q.x, q.y, q.z};
+            const Terms t = pair_terms(ep0, pq, my_o, my_n);
+            if (in_tile <= 4) accumulate_warp<2>(row, t, my_valid, lane);
+            else if (in_tile <= 8) accumulate_warp<3>(row, t, my_valid, lane);
+            else accumulate_warp<5>(row, t, my_valid, lane);
         }
         LO_TRACE(1);
         block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
