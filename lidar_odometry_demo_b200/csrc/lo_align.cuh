@@ -179,7 +179,8 @@ struct AlignArgs {
     float4* pair_n;        // [m] plane_normal
     double* partials;      // [2][gridDim.x][32]
     const float* guess;    // device pose7
-    float* out_pose;       // device pose7
+    float* out_pose;       // device pose7 (written by block 0)
+    float* out_pose_block = nullptr;  // nullable: 7 floats in the caller's shared memory, written in every block
     lo_align_stats* stats; // device, nullable
     float max_dist;
     long long* trace;      // nullable: (tag, clock64) pairs written by block 0 thread 0 (LO_ALIGN_TRACE=1)
@@ -388,12 +389,16 @@ __device__ inline void align_device(AlignArgs a, cg::grid_group& grid) {
     }
     LO_TRACE(9);
     if (a.trace && blockIdx.x == 0 && threadIdx.x == 0) a.trace[1000] = trace_n;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {  // cloud_matcher.cpp:175 Quaternionf::normalize()
+    if (threadIdx.x == 0) {  // cloud_matcher.cpp:175 Quaternionf::normalize()
         const float w = pose_s[3], x = pose_s[4], y = pose_s[5], z = pose_s[6];
         const float nrm = sqrtf((x * x + z * z) + (y * y + w * w));
-        a.out_pose[0] = pose_s[0]; a.out_pose[1] = pose_s[1]; a.out_pose[2] = pose_s[2];
-        a.out_pose[3] = w / nrm; a.out_pose[4] = x / nrm; a.out_pose[5] = y / nrm; a.out_pose[6] = z / nrm;
+        const float out[7] = {pose_s[0], pose_s[1], pose_s[2], w / nrm, x / nrm, y / nrm, z / nrm};
+        for (int k = 0; k < 7; k++) {
+            if (blockIdx.x == 0) a.out_pose[k] = out[k];
+            if (a.out_pose_block) a.out_pose_block[k] = out[k];
+        }
     }
+    __syncthreads();
 }
 
 }  // namespace lo

@@ -3,6 +3,7 @@
 // per scan to read back the pose and the per-scan counters (28 + 64 bytes).
 #include <algorithm>
 #include <cstdlib>
+#include <atomic>
 #include <cstring>
 
 #include "lo_odometry.cuh"
@@ -115,9 +116,28 @@ static int finish_scan(lo_odometry* h, uint32_t n_points, bool readback_done = f
     if (!readback_done) {
         odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
         LO_LAUNCHED(ctx);
+        LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
+        LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        h->h_readback->seq = 0;   // never a per-scan kernel's number
+    } else {
+        // the per-scan kernel wrote the block into pinned memory; its last store is `seq`. Poll it (the result is
+        // there a few microseconds before the stream reports the kernel as retired), checking the stream now and then
+        // so that a failed launch cannot hang the caller.
+        const volatile uint32_t* seq = &h->h_readback->seq;
+        static const char* wait_mode = getenv("LO_B200_WAIT");   // developer switch: "sync", "both" or (default) poll
+        const bool mode_sync = wait_mode && wait_mode[0] == 's', mode_both = wait_mode && wait_mode[0] == 'b';
+        if (mode_sync) LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (uint32_t spins = 0; *seq != h->scan_seq; spins++) {
+            if ((spins & 0xFFFu) == 0xFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
+        }
+        if (mode_both) LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (*seq != h->scan_seq) LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (*seq != h->scan_seq) {
+            set_error("the per-scan kernel finished without publishing its result");
+            return LO_E_CUDA;
+        }
+        std::atomic_thread_fence(std::memory_order_acquire);
     }
-    LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
-    LO_CUDA(cudaStreamSynchronize(ctx->stream));
     if (readback_done) fused_trace_dump(h);
     const ScanReadback& r = *h->h_readback;
     std::memcpy(h->pose, r.pose, sizeof(h->pose));
@@ -158,6 +178,7 @@ extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odome
     LO_CUDA(cudaMemsetAsync(h->d_state, 0, sizeof(OdomDev), ctx->stream));
     LO_CUDA(cudaMalloc(&h->d_readback, sizeof(ScanReadback)));
     LO_CUDA(cudaMallocHost(&h->h_readback, sizeof(ScanReadback)));
+    std::memset(h->h_readback, 0, sizeof(ScanReadback));
     LO_CUDA(cudaMalloc(&h->d_minmax, 2 * sizeof(uint32_t)));
     const uint32_t minmax_init[2] = {0xFFFFFFFFu, 0u};
     LO_CUDA(cudaMemcpyAsync(h->d_minmax, minmax_init, sizeof(minmax_init), cudaMemcpyHostToDevice, ctx->stream));

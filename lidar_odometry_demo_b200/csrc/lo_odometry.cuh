@@ -42,11 +42,12 @@ __device__ inline void euler_angles_012(const float r[9], float ang[3]) {
     ang[0] = -e0; ang[1] = -e1; ang[2] = -e2;
 }
 
-struct ScanReadback {   // one D2H per scan
-    float pose[7];
+struct ScanReadback {   // per scan, device -> host. The per-scan kernel writes it straight into pinned host memory and then
+    float pose[7];      // publishes `seq`; the stage-by-stage pipeline fills a device copy that is fetched with one D2H.
     uint32_t n_planar, n_update, n_query, unstable;
     int32_t outer_iterations;
     uint32_t kf_counters[GC_COUNT];
+    uint32_t seq;       // scan number, written last (after a system-scope fence)
 };
 
 }  // namespace lo
@@ -59,7 +60,8 @@ struct lo_odometry {
     lo_grid* match_ds = nullptr;     // VoxelGrid(keyframe_matching_voxel_size, 1) lidar_odometry.cpp:46
     lo::OdomDev* d_state = nullptr;
     lo::ScanReadback* d_readback = nullptr;
-    lo::ScanReadback* h_readback = nullptr;  // pinned
+    lo::ScanReadback* h_readback = nullptr;  // pinned, mapped: the per-scan kernel writes it directly
+    uint32_t scan_seq = 0;                   // scans submitted to the per-scan kernel
     lo::DevBuf scan, deskewed, filtered, update, query;
     lo::DevBuf fused;                // scratch of the fused pipeline (lo_pipeline.cu)
     uint32_t* d_minmax = nullptr;    // [2] ordered min / max of `time`, re-armed by the read-back kernel

@@ -551,9 +551,8 @@ __device__ inline void phase_robin_emit(const OdomDev* __restrict__ s, PipeBufs 
     }
 }
 
-// lidar_odometry.cpp:53-65: Euler-angle divergence gate, then current = new (one thread)
-__device__ inline void phase_gate(OdomDev* s, float threshold) {
-    const Pose nw = s->next, cur = s->current;
+// lidar_odometry.cpp:53-65: Euler-angle divergence gate; returns the pose that becomes current_transform_
+__device__ inline Pose gate_pose(const Pose& nw, const Pose& cur, const Pose& guess, float threshold, uint32_t& unstable) {
     Pose a = identity_pose(), c = identity_pose();   // new.rotation * current.rotation.inverse()
     a.w = nw.w; a.x = nw.x; a.y = nw.y; a.z = nw.z;
     c.w = cur.w; c.x = cur.x; c.y = cur.y; c.z = cur.z;
@@ -569,13 +568,8 @@ __device__ inline void phase_gate(OdomDev* s, float threshold) {
         const float m = fabsf(deg);
         ok = ok && (m < threshold || m > 180 - threshold);
     }
-    Pose out = nw;
-    if (!ok) {
-        out = s->guess;
-        s->unstable = 1;
-    }
-    s->current = out;
-    s->center[0] = out.t[0]; s->center[1] = out.t[1]; s->center[2] = out.t[2];
+    unstable = ok ? 0u : 1u;
+    return ok ? nw : guess;
 }
 
 struct ScanArgs {
@@ -592,7 +586,8 @@ struct ScanArgs {
     uint32_t* kf_counters;
     uint32_t* kf_free_list;
     uint32_t ticket_base;        // arrival ticket of the first update point
-    ScanReadback* readback;
+    ScanReadback* readback;      // pinned host memory
+    uint32_t seq;                // this scan's number, published in readback->seq when everything else is written
     uint32_t n;
     int first;                   // the key-frame is empty: bootstrap scan (cpp:40-44)
     float lo2, hi2, vs_u, vs_m, cleanup_range, gate_threshold;
@@ -650,6 +645,9 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
     phase_robin_emit(s, p.b, p.filtered, p.update);
     grid.sync();
     LO_SCAN_TRACE(112);
+    __shared__ float next_s[7];
+    __shared__ Pose current_s;
+    __shared__ uint32_t unstable_s;
     const Pose* insert_pose = nullptr;   // first scan: inserted un-transformed (cpp:42)
     if (!p.first) {
         AlignArgs a;                     // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
@@ -666,17 +664,23 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
         a.max_dist = 0.3f;               // cloud_matcher.cpp:139
         a.trace = p.trace;
         a.trace_start = trace_n;
+        a.out_pose_block = next_s;
         align_device(a, grid);
         if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_n = static_cast<int>(p.trace[1000]);
-        grid.sync();
-        if (blockIdx.x == 0 && threadIdx.x == 0) phase_gate(s, p.gate_threshold);   // cpp:53-65
-        grid.sync();
+        // every block runs the gate on the (identical) result: no grid-wide hand-over; block 0 stores the state at the end
+        if (threadIdx.x == 0) {
+            Pose nw;
+            nw.t[0] = next_s[0]; nw.t[1] = next_s[1]; nw.t[2] = next_s[2];
+            nw.w = next_s[3]; nw.x = next_s[4]; nw.y = next_s[5]; nw.z = next_s[6];
+            current_s = gate_pose(nw, s->current, s->guess, p.gate_threshold, unstable_s);   // cpp:53-65
+        }
+        __syncthreads();
         LO_SCAN_TRACE(120);
         for (uint32_t sl = blockIdx.x * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += gridDim.x * blockDim.x)
-            grid_cleanup_slot(sl, p.kf, s->center, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
+            grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
         grid.sync();
         LO_SCAN_TRACE(121);
-        insert_pose = &s->current;       // transformWithNormals fused into the load (cpp:69)
+        insert_pose = &current_s;        // transformWithNormals fused into the load (cpp:69)
     }
     // keyframe_.addCloud(update) (cpp:42 / cpp:70)
     const uint32_t nu = min(p.n, s->n_update);
@@ -695,6 +699,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
     LO_SCAN_TRACE(124);
     if (blockIdx.x == 0 && threadIdx.x == 0) {   // read-back block for the host; re-arm the next scan's time min/max
         grid_fix_counters(p.kf_counters);
+        if (!p.first) {                          // the gate's outcome becomes the state of the next scan
+            s->current = current_s;
+            s->unstable = unstable_s;
+            s->center[0] = current_s.t[0]; s->center[1] = current_s.t[1]; s->center[2] = current_s.t[2];
+        }
         ScanReadback* out = p.readback;
         pose_to7(s->current, out->pose);
         out->n_planar = s->n_planar;
@@ -705,6 +714,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
         for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
         p.minmax[0] = 0xFFFFFFFFu;
         p.minmax[1] = 0u;
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(&out->seq) = p.seq;
         if (p.trace) p.trace[1000] = trace_n;
     }
 #undef LO_SCAN_TRACE
@@ -749,7 +760,8 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.kf_counters = kf->counters;
     p.kf_free_list = kf->free_list;
     p.ticket_base = kf->h_counters[GC_TICKET];
-    p.readback = h->d_readback;
+    p.readback = h->h_readback;   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
+    p.seq = ++h->scan_seq;
     p.n = n;
     p.first = kf->h_counters[GC_VOXELS] == 0 ? 1 : 0;  // cpp:40 (host mirror from the last scan's read-back)
     p.lo2 = h->params.lidar_min_range * h->params.lidar_min_range;
