@@ -175,6 +175,7 @@ def run_ours(args):
     launches0 = ctx.kernel_launches
     t_wall0 = time.perf_counter()
     outer_total, m_total = 0, 0
+    scan_stats = []
     for i in range(K):
         k = W + i
         flush_l2()
@@ -184,6 +185,7 @@ def run_ours(args):
         st = od.stats()
         outer_total += st.outer_iterations
         m_total += st.n_query
+        scan_stats.append((st.n_points, st.n_planar, st.n_update, st.n_query, st.outer_iterations))
     barrier()
     t_wall = time.perf_counter() - t_wall0
     launches = ctx.kernel_launches - launches0
@@ -240,7 +242,7 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel + the stand-alone fused NN+residual kernel ------------------
     peak, peak_src = peaks()
-    roof, roof_nn = roofline_section(lo, ctx, torch, stream, od, scans, W, K, outer_total, m_total, peak, peak_src)
+    roof, roof_align, roof_nn = roofline_section(lo, ctx, torch, stream, od, scans, W, K, step_ms, scan_stats, peak, peak_src)
 
     # ---- CPU baseline on this box's host cores (bounded sample) --------------------------------------
     orc, kind = cpu_oracle()
@@ -274,7 +276,7 @@ def run_ours(args):
         "e2e": {"value": n * K / e2e_time, "unit": UNIT, "h2d_bytes_per_step": int(np.mean(sizes[W:]) * 32), "d2h_bytes_per_step": 80},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": roof, "roofline_nn": roof_nn,
+        "roofline": roof, "roofline_align": roof_align, "roofline_nn": roof_nn,
         "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": "reference" if kind == "reference" else "port",
                          "sample": f"scans {W}..{n_cpu - 1} of the same stream ({n_cpu - W} scans, {t_cpu:.1f} s)"},
         "parity": {"max_pose_err_m": worst_dt, "max_pose_err_rad": worst_dr, "scans_checked": n_cpu,
@@ -285,14 +287,31 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def roofline_section(lo, ctx, torch, stream, od, scans, W, K, outer_total, m_total, peak, peak_src):
-    """Algorithmic bytes / measured duration for align_kernel (inside the step) and nn_residual_kernel (alone)."""
-    orc, _ = cpu_oracle("port")
-    # a representative align call: key-frame = the pipeline's own after the run, queries = last scan's matching set
+def _exhaustive(flag):
+    """lo_nn_residual visits all 27 neighbours (the reference's candidate count) when LO_B200_NN_EXHAUSTIVE is set."""
+    if flag:
+        os.environ["LO_B200_NN_EXHAUSTIVE"] = "1"
+    else:
+        os.environ.pop("LO_B200_NN_EXHAUSTIVE", None)
+
+
+def _ncu_traffic(kernel):
+    """DRAM bytes (read + write) per launch of `kernel` from the committed `ncu --set full` summary, or None."""
+    path = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
+    try:
+        with open(path) as f:
+            return json.load(f)[kernel]["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
+def roofline_section(lo, ctx, torch, stream, od, scans, W, K, step_ms, scan_stats, peak, peak_src):
+    """Algorithmic bytes (SURVEY.md 8(d) / DESIGN.md 5) over measured duration: scan_kernel (the whole step, timed live in
+    the timed region), align_kernel alone, and the fused NN+residual kernel on a map much larger than L2."""
+    # ---- candidates per query of the reference's exhaustive 27-voxel visit, on the pipeline's own key frame ----
     kf_pn = od.getKeyFrameCloudWithNormals()
     g = lo.VoxelGrid(ctx, od.params.keyframe_voxel_size, int(od.params.keyframe_max_points_cnt), capacity_hint=max(1024, len(kf_pn) // 4))
-    # slot order inside a voxel is irrelevant for the byte count
-    g.addCloud(kf_pn)
+    g.addCloud(kf_pn)   # slot order inside a voxel is irrelevant for the byte count
     ident = np.array([0, 0, 0, 1, 0, 0, 0], np.float32)
     last = scans[W + K - 1]
     planar = ctx.classify(ctx.deskew(last, ident, ident))
@@ -302,9 +321,13 @@ def roofline_section(lo, ctx, torch, stream, od, scans, W, K, outer_total, m_tot
     q = ds.getCloudWithoutNormals()
     pose = od.getCurrentPose()
     x = np.array([pose[3], pose[4], pose[5], pose[6], pose[0], pose[1], pose[2]], np.float64)
+    _exhaustive(True)
     g.nnResidual(q, pose, x, x[4:])
+    _exhaustive(False)
     c_mean = g.last_candidates / max(len(q), 1)
-    # time align alone on these inputs (device-resident queries), L2 flushed before every launch
+    per_query_search = 464 + 16 * c_mean
+
+    # ---- align alone on these inputs (device-resident queries), L2 flushed before every launch ----
     d_q = torch.from_numpy(q.view(np.uint8).reshape(-1)).to(stream.device)
     out = np.empty(7, np.float32)
     stats = lo.AlignStats()
@@ -323,17 +346,33 @@ def roofline_section(lo, ctx, torch, stream, od, scans, W, K, outer_total, m_tot
         if i >= 3:
             ts.append(e0.elapsed_time(e1) / 1e3)
     t_align = float(np.mean(ts))
-    per_query_search = 464 + 16 * c_mean
-    evals = stats.lm_iterations  # recorded iterations ~ evaluations (one Jacobian evaluation each)
-    bytes_align = len(q) * (stats.outer_iterations * per_query_search + evals * 64)
-    roof = {"bound": "hbm", "kernel": "align_kernel (persistent cooperative: search + residual + LM, whole CloudMatcher::align)",
-            "achieved": bytes_align / t_align / 1e9, "peak": peak, "unit": "GB/s", "frac": bytes_align / t_align / 1e9 / peak,
-            "traffic": None, "peak_source": peak_src, "launch_ms": 1e3 * t_align, "queries": int(len(q)),
-            "outer_iterations": int(stats.outer_iterations), "mean_candidates_per_query": c_mean,
-            "bytes_per_query_per_search": per_query_search,
-            "note": "latency-bound: one VLP16 pass is ~20 MB, L2-resident; see roofline_nn for the bandwidth-bound configuration"}
+    evals_per_outer = stats.lm_iterations / max(stats.outer_iterations, 1)   # recorded LM iterations ~ evaluations
+    bytes_align = len(q) * (stats.outer_iterations * per_query_search + stats.lm_iterations * 48)
+    roof_align = {"bound": "hbm", "kernel": "align_kernel (persistent cooperative: search + residual + LM, whole CloudMatcher::align)",
+                  "achieved": bytes_align / t_align / 1e9, "peak": peak, "unit": "GB/s", "frac": bytes_align / t_align / 1e9 / peak,
+                  "traffic": _ncu_traffic("align_kernel"), "peak_source": peak_src, "launch_ms": 1e3 * t_align, "queries": int(len(q)),
+                  "outer_iterations": int(stats.outer_iterations), "mean_candidates_per_query": c_mean,
+                  "bytes_per_query_per_search": per_query_search}
 
-    # stand-alone fused NN+residual kernel on a large batch (config 3/4 shape): 262 144 queries on a map >> L2
+    # ---- the dominant kernel of the step: scan_kernel, one launch per scan, timed live by the per-step events ----
+    # bytes per scan: deskew 36 B/pt, classifier 32 B read + 48 B written per point / planar point, two
+    # down-sampler inserts (48 + 16 B each) per planar point, key-frame insert 96 B per update point, every search pass
+    # 464 + 16 C bytes per query, every LM evaluation 48 B per pair.
+    n_pts, n_planar, n_update, n_query, outer = (float(np.mean([st[k] for st in scan_stats])) for k in range(5))
+    bytes_scan = (36 * n_pts + 32 * n_pts + 48 * n_planar + 2 * 64 * n_planar + 96 * n_update
+                  + outer * n_query * per_query_search + outer * evals_per_outer * n_query * 48)
+    t_scan = float(np.mean(step_ms)) / 1e3
+    roof = {"bound": "hbm", "kernel": "scan_kernel (persistent cooperative, one launch per scan: deskew, classifier, both down-samplers, "
+            "robin order, align, gate, cleanup, key-frame insert)",
+            "achieved": bytes_scan / t_scan / 1e9, "peak": peak, "unit": "GB/s", "frac": bytes_scan / t_scan / 1e9 / peak,
+            "traffic": _ncu_traffic("scan_kernel"), "peak_source": peak_src, "launch_ms": 1e3 * t_scan,
+            "algorithmic_bytes_per_launch": bytes_scan,
+            "per_scan": {"points": n_pts, "planar": n_planar, "update": n_update, "queries": n_query, "outer_iterations": outer,
+                         "candidates_per_query": c_mean, "lm_evaluations_per_outer": evals_per_outer},
+            "note": "latency-bound by construction: a 30k-point scan moves ~20 MB through ~45 dependent grid-wide phases "
+                    "(SURVEY.md 8(d) H4); the bandwidth-bound configuration of the same search + residual code is roofline_nn"}
+
+    # ---- stand-alone fused NN+residual kernel on a large batch (config 3/4 shape): 262 144 queries on a map >> L2 ----
     n_map = 12_000_000
     big = S.planar_patch_map(n_map, seed=777, extent=(400.0, 400.0, 40.0))
     gb = lo.VoxelGrid(ctx, 0.2, 20, capacity_hint=n_map // 8)
@@ -347,30 +386,43 @@ def roofline_section(lo, ctx, torch, stream, od, scans, W, K, outer_total, m_tot
     neq = lo.NormalEq()
     xi = np.array([1, 0, 0, 0, 0, 0, 0], np.float64)
     zero3 = np.zeros(3)
-    ts = []
-    for i in range(10):
-        with torch.cuda.stream(stream):
-            flush.fill_(1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        rc = ctx.lib.lo_nn_residual_dev(gb.h, C.c_void_p(d_qq.data_ptr()), len(qq), ident.ctypes.data_as(C.c_void_p),
-                                        xi.ctypes.data_as(C.c_void_p), zero3.ctypes.data_as(C.c_void_p), C.c_float(0.3), None)
-        e1.record(stream)
-        torch.cuda.synchronize()
-        assert rc == 0
-        if i >= 3:
-            ts.append(e0.elapsed_time(e1) / 1e3)
-    rc = ctx.lib.lo_nn_residual_dev(gb.h, C.c_void_p(d_qq.data_ptr()), len(qq), ident.ctypes.data_as(C.c_void_p),
-                                    xi.ctypes.data_as(C.c_void_p), zero3.ctypes.data_as(C.c_void_p), C.c_float(0.3), C.byref(neq))
-    t_nn = float(np.mean(ts))
-    c_big = neq.candidates / len(qq)
-    bytes_nn = len(qq) * (464 + 16 * c_big)
-    roof_nn = {"bound": "hbm", "kernel": "nn_residual_kernel (+ 1-block finalize)", "achieved": bytes_nn / t_nn / 1e9, "peak": peak,
-               "unit": "GB/s", "frac": bytes_nn / t_nn / 1e9 / peak, "traffic": None, "peak_source": peak_src,
-               "launch_ms": 1e3 * t_nn, "queries": int(len(qq)), "mpts_per_s": len(qq) / t_nn / 1e6,
+
+    def timed_nn(n_rep):
+        ts = []
+        for i in range(n_rep):
+            with torch.cuda.stream(stream):
+                flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            rc = ctx.lib.lo_nn_residual_dev(gb.h, C.c_void_p(d_qq.data_ptr()), len(qq), ident.ctypes.data_as(C.c_void_p),
+                                            xi.ctypes.data_as(C.c_void_p), zero3.ctypes.data_as(C.c_void_p), C.c_float(0.3), None)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            assert rc == 0
+            if i >= 3:
+                ts.append(e0.elapsed_time(e1) / 1e3)
+        ctx.lib.lo_nn_residual_dev(gb.h, C.c_void_p(d_qq.data_ptr()), len(qq), ident.ctypes.data_as(C.c_void_p),
+                                   xi.ctypes.data_as(C.c_void_p), zero3.ctypes.data_as(C.c_void_p), C.c_float(0.3), C.byref(neq))
+        return float(np.mean(ts)), neq.candidates / len(qq), int(neq.n_valid), float(neq.cost)
+
+    t_nn, c_visited, valid_t, cost_t = timed_nn(10)
+    _exhaustive(True)
+    t_ex, c_big, valid_e, cost_e = timed_nn(6)
+    _exhaustive(False)
+    assert valid_t == valid_e and abs(cost_t - cost_e) <= 1e-9 * abs(cost_e), "tile search and exhaustive search disagree"
+    bytes_nn = len(qq) * (464 + 16 * c_big)                 # the reference's exhaustive visit
+    bytes_visited = len(qq) * (16 + 16 * c_visited + 32)    # what the pruned search has to touch besides table slots
+    roof_nn = {"bound": "hbm", "kernel": "nn_residual_tile_kernel (+ 1-block finalize)", "achieved": bytes_nn / t_nn / 1e9, "peak": peak,
+               "unit": "GB/s", "frac": bytes_nn / t_nn / 1e9 / peak, "traffic": _ncu_traffic("nn_residual_tile_kernel"),
+               "peak_source": peak_src, "launch_ms": 1e3 * t_nn, "queries": int(len(qq)), "mpts_per_s": len(qq) / t_nn / 1e6,
                "map_points": int(gb.numPoints()), "map_voxels": int(gb.size()), "mean_candidates_per_query": c_big,
-               "valid_pairs": int(neq.n_valid)}
-    return roof, roof_nn
+               "candidates_visited_per_query": c_visited, "visited_bytes_GBps": bytes_visited / t_nn / 1e9, "valid_pairs": valid_t,
+               "exhaustive_kernel": {"kernel": "nn_residual_kernel", "launch_ms": 1e3 * t_ex, "achieved": bytes_nn / t_ex / 1e9,
+                                     "frac": bytes_nn / t_ex / 1e9 / peak, "traffic": _ncu_traffic("nn_residual_kernel")},
+               "note": "achieved counts the ALGORITHMIC bytes of the reference's exhaustive 27-voxel visit (464 + 16 C per query); the "
+                       "tile search skips neighbours that cannot hold a nearer point (bit-identical result), so it can exceed the "
+                       "bandwidth needed to read them all; traffic is what it really moved"}
+    return roof, roof_align, roof_nn
 
 
 def main():

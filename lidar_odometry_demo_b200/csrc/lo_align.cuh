@@ -7,6 +7,7 @@
 
 #include "lo_host.h"
 #include "lo_lm.cuh"
+#include "lo_tile_search.cuh"
 
 namespace lo {
 
@@ -198,7 +199,10 @@ struct AlignArgs {
 
 // The body of align_kernel; also the middle part of the per-scan kernel of lo_pipeline.cu. Every thread of a
 // cooperative grid of kAlignThreads-wide blocks must call it.
-__device__ inline void align_device(AlignArgs a, cg::grid_group& grid) {
+// `tile_scratch`: nullable, (kAlignThreads / 32) TileScratch in shared memory; with it, large query sets (several queries
+// per warp) are searched 32 per warp with exact neighbour pruning (lo_tile_search.cuh) instead of one per warp.
+constexpr size_t kAlignTileScratchBytes = (kAlignThreads / 32) * sizeof(TileScratch);
+__device__ inline void align_device(AlignArgs a, cg::grid_group& grid, TileScratch* tile_scratch = nullptr) {
     if (a.m_dev) a.m = min(a.m, *a.m_dev);
     __shared__ double rows[(kAlignThreads / 32) * kRow];
     __shared__ double total[32];
@@ -216,6 +220,8 @@ __device__ inline void align_device(AlignArgs a, cg::grid_group& grid) {
     const int nblocks = gridDim.x;
     const LaneOffset lofs = lane_offset(lane);
     const uint32_t my_queries = gwarp < a.m ? (a.m - gwarp + total_warps - 1) / total_warps : 0u;
+    const bool tiled = tile_scratch != nullptr && a.g.width <= kTileMaxWidth && a.m >= 8 * total_warps;
+    TileScratch* ts = tile_scratch ? tile_scratch + (threadIdx.x >> 5) : nullptr;
     double* row = rows + (threadIdx.x >> 5) * kRow;
     for (int k = threadIdx.x; k < (kAlignThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
     if (threadIdx.x < 7) pose_s[threadIdx.x] = a.guess[threadIdx.x];
@@ -241,7 +247,24 @@ __device__ inline void align_device(AlignArgs a, cg::grid_group& grid) {
         // the 27-lane search runs once per query with the slot loads of query j+1 in flight while query j is scanned, lane j
         // keeps the correspondence of query j; then the tile's normals are fetched in one round and all lanes evaluate
         // their pair at x0 in parallel.
-        for (uint32_t base = 0; base < my_queries; base += 32) {
+        // large query sets: tile search, query i in lane (i & 31) of the warp that owns tile i / 32
+        for (uint32_t base = gwarp * 32; tiled && base < a.m; base += total_warps * 32) {
+            const uint32_t i = base + lane;
+            const bool have = i < a.m;
+            PointXYZ q{0.f, 0.f, 0.f, 0.f};
+            if (have) q = a.queries[i];
+            float wq[3];
+            transform_query(tf, q.x, q.y, q.z, wq);
+            const TileHit h = nn_search_tile(a.g, wq, have, max_d2, lane, ts);
+            if (have) {
+                a.pair_o[i] = make_float4(h.o[0], h.o[1], h.o[2], h.valid ? 1.f : 0.f);
+                a.pair_n[i] = make_float4(h.n[0], h.n[1], h.n[2], 0.f);
+            }
+            const float pq[3] = {q.x, q.y, q.z};
+            const Terms t = pair_terms(ep0, pq, h.o, h.n);
+            accumulate_warp<5>(row, t, h.valid, lane);
+        }
+        for (uint32_t base = 0; !tiled && base < my_queries; base += 32) {
             const uint32_t mine = gwarp + (base + lane) * total_warps;
             const bool have = base + lane < my_queries;
             PointXYZ q{0.f, 0.f, 0.f, 0.f};

@@ -111,6 +111,42 @@ __global__ void __launch_bounds__(kNnThreads, 4) nn_residual_kernel(GridView g, 
     block_rows_to_global(rows, partials + blockIdx.x * 32);
 }
 
+// The same contract with the tile search of lo_tile_search.cuh (own voxel first, neighbours pruned exactly by the best
+// distance so far): a warp takes 32 consecutive queries, lane l owns query l from the transform to the residual.
+// rows[29] / rows[30] count the stored points / occupied voxels actually visited.
+__global__ void __launch_bounds__(kNnThreads, 4) nn_residual_tile_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+                                                                       QueryTransform tf, EvalPoint ep, float max_d2,
+                                                                       double* __restrict__ partials) {
+    __shared__ double rows[(kNnThreads / 32) * kRow];
+    __shared__ TileScratch scratch[kNnThreads / 32];
+    const int lane = threadIdx.x & 31, warp_in_block = threadIdx.x >> 5;
+    TileScratch* ts = scratch + warp_in_block;
+    for (int k = threadIdx.x; k < (kNnThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
+    __syncthreads();
+    double* row = rows + warp_in_block * kRow;
+    const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    for (uint32_t base = gw * 32; base < m; base += total_warps * 32) {
+        const uint32_t i = base + lane;
+        const bool have = i < m;
+        PointXYZ q{0.f, 0.f, 0.f, 0.f};
+        if (have) q = queries[i];
+        float wq[3];
+        transform_query(tf, q.x, q.y, q.z, wq);
+        uint32_t visited = 0, occupied = 0;
+        const TileHit h = nn_search_tile(g, wq, have, max_d2, lane, ts, &visited, &occupied);
+        const float pf[3] = {q.x, q.y, q.z};
+        const Terms t = pair_terms(ep, pf, h.o, h.n);
+        accumulate_warp(row, t, h.valid, lane);
+        const double vis = warp_sum(static_cast<double>(visited)), occ = warp_sum(static_cast<double>(occupied));
+        if (lane == 0) {
+            row[29] += vis;
+            row[30] += occ;
+        }
+    }
+    block_rows_to_global(rows, partials + blockIdx.x * 32);
+}
+
 // final reduction of nn_residual_kernel's partials + the prior, by one block
 __global__ void normal_eq_finalize_kernel(const double* __restrict__ partials, int nblocks, EvalPoint ep, double b0, double b1, double b2,
                                           lo_normal_eq* __restrict__ out) {
@@ -136,8 +172,9 @@ __global__ void normal_eq_finalize_kernel(const double* __restrict__ partials, i
 // ---------------------------------------------------------------------------------------------------
 // CloudMatcher::align (src/cloud_matcher.cpp:105-178) as one persistent cooperative kernel (body: lo_align.cuh)
 __global__ void __launch_bounds__(kAlignThreads, 1) align_kernel(AlignArgs a) {
+    extern __shared__ __align__(16) unsigned char tile_scratch[];
     cg::grid_group grid = cg::this_grid();
-    align_device(a, grid);
+    align_device(a, grid, reinterpret_cast<TileScratch*>(tile_scratch));
 }
 
 // enqueue align on the context's stream; every pointer is a device pointer
@@ -146,7 +183,8 @@ int align_enqueue(lo_grid* kf, const PointXYZ* d_queries, uint32_t m, const uint
     lo_ctx* ctx = kf->ctx;
     if (ctx->align_blocks == 0) {
         int per_sm = 0;
-        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, align_kernel, kAlignThreads, 0));
+        LO_CUDA(cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kAlignTileScratchBytes)));
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, align_kernel, kAlignThreads, kAlignTileScratchBytes));
         if (per_sm < 1) {
             set_error("align kernel does not fit on an SM");
             return LO_E_CUDA;
@@ -179,7 +217,7 @@ int align_enqueue(lo_grid* kf, const PointXYZ* d_queries, uint32_t m, const uint
         args.trace = ctx->tmp_d.as<long long>();
     }
     void* kargs[] = {&args};
-    LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(align_kernel), dim3(blocks), dim3(kAlignThreads), kargs, 0, ctx->stream));
+    LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(align_kernel), dim3(blocks), dim3(kAlignThreads), kargs, kAlignTileScratchBytes, ctx->stream));
     ctx->launches++;
     return LO_OK;
 }
@@ -233,8 +271,15 @@ extern "C" int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, con
     const int blocks = std::max(1, std::min<int>(max_blocks, static_cast<int>((tiles + kNnThreads / 32 - 1) / (kNnThreads / 32))));
     LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(blocks) * 32 * sizeof(double)));
     lo_normal_eq* d_out = reinterpret_cast<lo_normal_eq*>(ctx->small.as<char>() + 1024);
-    nn_residual_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m), tf,
-                                                               ep, max_dist * max_dist, ctx->tmp_c.as<double>());
+    // LO_B200_NN_EXHAUSTIVE=1: visit all 27 neighbours of every query (lo_normal_eq::candidates is then the reference's count)
+    const bool exhaustive = g->width > kTileMaxWidth || getenv("LO_B200_NN_EXHAUSTIVE") != nullptr;
+    if (exhaustive)
+        nn_residual_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m),
+                                                                   tf, ep, max_dist * max_dist, ctx->tmp_c.as<double>());
+    else
+        nn_residual_tile_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16),
+                                                                        static_cast<uint32_t>(m), tf, ep, max_dist * max_dist,
+                                                                        ctx->tmp_c.as<double>());
     LO_LAUNCHED(ctx);
     normal_eq_finalize_kernel<<<1, 256, 0, ctx->stream>>>(ctx->tmp_c.as<double>(), blocks, ep, prior_b[0], prior_b[1], prior_b[2], d_out);
     LO_LAUNCHED(ctx);
@@ -323,6 +368,34 @@ __global__ void __launch_bounds__(kShardThreads) shard_search_kernel(GridView g,
     }
 }
 
+// the same with the tile search (lo_tile_search.cuh): a warp takes 32 consecutive queries
+__global__ void __launch_bounds__(kShardThreads) shard_search_tile_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+                                                                           QueryTransform tf, float max_d2,
+                                                                           unsigned long long* __restrict__ packed, float4* __restrict__ hit) {
+    __shared__ TileScratch scratch[kShardThreads / 32];
+    const int lane = threadIdx.x & 31;
+    TileScratch* ts = scratch + (threadIdx.x >> 5);
+    const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; base < m; base += total_warps * 32) {
+        const uint32_t i = base + lane;
+        const bool have = i < m;
+        PointXYZ q{0.f, 0.f, 0.f, 0.f};
+        if (have) q = queries[i];
+        float wq[3];
+        transform_query(tf, q.x, q.y, q.z, wq);
+        const TileBest b = nn_search_tile_best(g, wq, have, max_d2, lane, ts);
+        if (have) {
+            float4 o = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+            if (b.key != ~0ull) {
+                const float4 p = __ldg(g.points + b.at);
+                o = make_float4(p.x, p.y, p.z, __uint_as_float(b.at));
+            }
+            packed[i] = b.key;
+            hit[i] = o;
+        }
+    }
+}
+
 // terms of the correspondences this rank owns; per-block partial sums in a fixed order
 __global__ void __launch_bounds__(kShardThreads) shard_evaluate_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m, EvalPoint ep,
                                                                         const unsigned long long* __restrict__ local,
@@ -387,10 +460,18 @@ extern "C" int lo_shard_search_dev(lo_grid* g, const void* d_xyz16, size_t m, co
     lo_ctx* ctx = g->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
     const QueryTransform tf = make_query_transform(pose_from7(pose7));
-    const int blocks = std::max(1, std::min<int>(ctx->sm_count * 8, static_cast<int>((m * 32 + kShardThreads - 1) / kShardThreads)));
-    shard_search_kernel<<<blocks, kShardThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m), tf,
-                                                                   max_dist * max_dist, reinterpret_cast<unsigned long long*>(d_packed),
-                                                                   static_cast<float4*>(d_hit16));
+    if (g->width <= kTileMaxWidth) {
+        const int blocks = std::max(1, std::min<int>(ctx->sm_count * 4, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
+        shard_search_tile_kernel<<<blocks, kShardThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16),
+                                                                            static_cast<uint32_t>(m), tf, max_dist * max_dist,
+                                                                            reinterpret_cast<unsigned long long*>(d_packed),
+                                                                            static_cast<float4*>(d_hit16));
+    } else {
+        const int blocks = std::max(1, std::min<int>(ctx->sm_count * 8, static_cast<int>((m * 32 + kShardThreads - 1) / kShardThreads)));
+        shard_search_kernel<<<blocks, kShardThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m),
+                                                                       tf, max_dist * max_dist, reinterpret_cast<unsigned long long*>(d_packed),
+                                                                       static_cast<float4*>(d_hit16));
+    }
     LO_LAUNCHED(ctx);
     return LO_OK;
 }

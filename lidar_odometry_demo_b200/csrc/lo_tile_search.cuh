@@ -107,8 +107,14 @@ __device__ inline void tile_scan_round(const GridView& g, TileScratch* ts, float
     __syncwarp();
 }
 
-// Lane l holds query l of the tile (world coordinates wq; `have` = the lane has a query). All 32 lanes must call.
-__device__ inline TileHit nn_search_tile(const GridView& g, const float wq[3], bool have, float max_d2, int lane, TileScratch* ts) {
+struct TileBest {     // per lane: the lane's own query
+    unsigned long long key;   // d2 bits << 32 | probe << 24 | slot ; ~0 = no stored point within max_dist
+    uint32_t at;              // index of that point in the point / normal slabs
+};
+
+// `visited` / `occupied` (nullable): this lane's share of the stored points / occupied voxels the tile looked at.
+__device__ inline TileBest nn_search_tile_best(const GridView& g, const float wq[3], bool have, float max_d2, int lane, TileScratch* ts,
+                                               uint32_t* visited = nullptr, uint32_t* occupied = nullptr) {
     const float vs = g.voxel_size;
     const int ox = clamp_axis(axis_index(wq[0], vs)), oy = clamp_axis(axis_index(wq[1], vs)), oz = clamp_axis(axis_index(wq[2], vs));
 #ifdef LO_TILE_DEBUG
@@ -125,6 +131,8 @@ __device__ inline TileHit nn_search_tile(const GridView& g, const float wq[3], b
     centre.probing = have;
     uint32_t vid, count;
     probe_resolve(g, probe_issue_at(g, ox, oy, oz, centre), vid, count);
+    if (visited) *visited += count;
+    if (occupied) *occupied += count ? 1u : 0u;
     LO_TILE_STAGE(4);
     tile_scan_round(g, ts, max_d2, lane, vid, count, static_cast<uint32_t>(lane), 13u);
     LO_TILE_STAGE(5);
@@ -195,25 +203,35 @@ __device__ inline TileHit nn_search_tile(const GridView& g, const float wq[3], b
         lo.probing = t < total;
         LO_TILE_STAGE(7);
         probe_resolve(g, probe_issue_at(g, qx, qy, qz, lo), vid, count);
+        if (visited) *visited += count;
+        if (occupied) *occupied += count ? 1u : 0u;
         LO_TILE_STAGE(8);
         tile_scan_round(g, ts, max_d2, lane, vid, count, static_cast<uint32_t>(q), static_cast<uint32_t>(l));
         LO_TILE_STAGE(9);
     }
     LO_TILE_STAGE(10);
+    TileBest b;
+    b.key = have ? ts->best[lane] : ~0ull;
+    b.at = b.key != ~0ull ? ts->best_at[lane] : 0u;
+    __syncwarp();   // the scratch is reused by the warp's next tile
+    return b;
+}
+
+// Lane l holds query l of the tile (world coordinates wq; `have` = the lane has a query). All 32 lanes must call.
+__device__ inline TileHit nn_search_tile(const GridView& g, const float wq[3], bool have, float max_d2, int lane, TileScratch* ts,
+                                         uint32_t* visited = nullptr, uint32_t* occupied = nullptr) {
+    const TileBest b = nn_search_tile_best(g, wq, have, max_d2, lane, ts, visited, occupied);
     // D. the winner's point and normal
     TileHit hit;
     hit.valid = false;
     hit.o[0] = hit.o[1] = hit.o[2] = 0.f;
     hit.n[0] = hit.n[1] = hit.n[2] = 0.f;
-    if (have && ts->best[lane] != ~0ull) {
-        const uint32_t at = ts->best_at[lane];
-        const float4 p = __ldg(g.points + at), nv = __ldg(g.normals + at);
+    if (b.key != ~0ull) {
+        const float4 p = __ldg(g.points + b.at), nv = __ldg(g.normals + b.at);
         hit.valid = true;
         hit.o[0] = p.x; hit.o[1] = p.y; hit.o[2] = p.z;
         hit.n[0] = nv.x; hit.n[1] = nv.y; hit.n[2] = nv.z;
     }
-    LO_TILE_STAGE(11);
-    __syncwarp();   // the scratch is reused by the warp's next tile
     return hit;
 }
 

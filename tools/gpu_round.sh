@@ -10,7 +10,7 @@ if [ "$1" = "ncu" ]; then
 timeout 600 python bench.py --steps 5 --warmup 3 > gpurun_out/plain.log 2>&1 &&
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 > gpurun_out/ncu_launches.log 2>&1 &&
 timeout 600 python tools/profile_hot.py > gpurun_out/plain_hot.log 2>&1 &&
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'align_kernel|nn_residual_kernel' -s 3 -c 4 -o gpurun_out/prof python tools/profile_hot.py > gpurun_out/ncu_full.log 2>&1
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|align_kernel|nn_residual' -c 16 -o gpurun_out/prof python tools/profile_hot.py > gpurun_out/ncu_full.log 2>&1
 echo "ncu rc=$?" >> gpurun_out/ncu_full.log
 fi
 tail -5 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err

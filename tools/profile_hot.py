@@ -1,7 +1,7 @@
 #!/usr/bin/env python
-"""Short driver for `ncu --set full`: a few scans through the pipeline (align_kernel launches) and the
-stand-alone fused NN+residual kernel on a map much larger than L2. Not a benchmark."""
-import ctypes as C
+"""Short driver for `ncu --set full`: a few scans through the pipeline (scan_kernel), one stand-alone align
+(align_kernel) and the fused NN+residual kernels (tile search and exhaustive) on a map much larger than L2.
+Not a benchmark."""
 import os
 import sys
 
@@ -13,11 +13,24 @@ from lidar_odometry_demo_b200 import synthetic as S  # noqa: E402
 
 n_map = int(sys.argv[1]) if len(sys.argv) > 1 else 12_000_000
 ctx = lo.Context(0)
-scans, _, _ = S.vlp16_stream(6)
+scans, _, _ = S.vlp16_stream(8)
 od = lo.LidarOdometry(ctx)
 for s in scans:
     od.processCloud(s)
 print("pose", od.getCurrentPose(), "outer", od.stats().outer_iterations)
+
+# CloudMatcher::align alone, on the pipeline's key frame and the last scan's matching set
+kf = od.getKeyFrameCloudWithNormals()
+g = lo.VoxelGrid(ctx, od.params.keyframe_voxel_size, int(od.params.keyframe_max_points_cnt))
+g.addCloud(kf)
+ident = np.array([0, 0, 0, 1, 0, 0, 0], np.float32)
+planar = ctx.range_filter(ctx.classify(ctx.deskew(scans[-1], ident, ident)), od.params.lidar_min_range, od.params.lidar_max_range)
+ds = lo.VoxelGrid(ctx, od.params.keyframe_matching_voxel_size, 1)
+ds.addCloud(planar)
+q = ds.getCloudWithoutNormals()
+for _ in range(2):
+    pose, st = lo.CloudMatcher().align(g, q, od.getCurrentPose(), with_stats=True)
+print("align", pose, st.outer_iterations)
 
 big = S.planar_patch_map(n_map, seed=777, extent=(400.0, 400.0, 40.0))
 gb = lo.VoxelGrid(ctx, 0.2, 20, capacity_hint=n_map // 8)
@@ -27,8 +40,10 @@ rng = np.random.default_rng(5)
 sel = rng.choice(len(big), 262144, replace=False)
 qq = np.zeros(len(sel), S.XYZ)
 qq["x"], qq["y"], qq["z"] = big["x"][sel] + 0.03, big["y"][sel] - 0.02, big["z"][sel] + 0.01
-ident = np.array([0, 0, 0, 1, 0, 0, 0], np.float32)
 x = np.array([1, 0, 0, 0, 0, 0, 0], np.float64)
-for _ in range(4):
-    cost, g, h, nv = gb.nnResidual(qq, ident, x, np.zeros(3))
-print("nn_residual", cost, nv, gb.last_candidates / len(qq))
+for mode in ("tile", "exhaustive"):
+    if mode == "exhaustive":
+        os.environ["LO_B200_NN_EXHAUSTIVE"] = "1"
+    for _ in range(3):
+        cost, grad, hess, nv = gb.nnResidual(qq, ident, x, np.zeros(3))
+    print("nn_residual", mode, cost, nv, gb.last_candidates / len(qq))
