@@ -127,8 +127,9 @@ int lo_align_dev(lo_grid* keyframe, const void* d_xyz16, size_t m, const float g
  * The reference is single-process; these phases split CloudMatcher::align (src/cloud_matcher.cpp:105-178) and
  * VoxelGrid::findMatchingPairs (src/voxel_grid.h:206-234) at the two points where ranks must exchange data. The
  * library issues no collective itself: the host places an all-reduce(MIN, u64[m]) after lo_shard_search_dev and an
- * all-reduce(SUM, f64[32]) after lo_shard_evaluate_dev, on the context's stream (host/lo_b200.hpp
- * ShardedCloudMatcher; lidar_odometry_demo_b200/sharded.py uses torch.distributed / NCCL). */
+ * all-reduce(SUM, f64[32]) after lo_shard_evaluate_dev, on the context's stream
+ * (lidar_odometry_demo_b200/sharded.py: ShardedCloudMatcher over torch.distributed / NCCL; a C++ caller does the
+ * same with two ncclAllReduce calls). */
 /* Call on an empty grid: add_cloud then keeps only the voxels whose 22-bit hash falls in this rank's range. */
 int lo_grid_set_shard(lo_grid* g, uint32_t rank, uint32_t world);
 /* d_packed[i] = (float bits of d2 << 32 | probe << 24 | slot) of query i's nearest stored point among THIS rank's

@@ -331,8 +331,8 @@ extern "C" int lo_align(lo_grid* kf, const float* xyz16, size_t m, const float g
 // ---------------------------------------------------------------------------------------------------
 // BASELINE.json config 4 / SURVEY.md 8(e): CloudMatcher::align against a key-frame map that is partitioned by
 // voxel-hash range over several GPUs. The library stays collective-free: it offers the per-rank phases, and the host
-// (host/lo_b200.hpp ShardedCloudMatcher in C++; lidar_odometry_demo_b200/sharded.py over torch.distributed / NCCL in
-// the tests and the bench) places two all-reduces between them per evaluation:
+// (lidar_odometry_demo_b200/sharded.py over torch.distributed / NCCL in the tests and the bench; two ncclAllReduce calls
+// for a C++ caller) places two all-reduces between them per evaluation:
 //
 //   lo_shard_search_dev    every rank: 27-neighbour search of the replicated queries in ITS voxels ->
 //                          packed[i] = (d2 bits << 32 | probe << 24 | slot), ~0 if none          [exchange 1: MIN over u64]

@@ -4,7 +4,7 @@ Host-side orchestration of the per-rank phases of include/lo_b200.h (lo_shard_se
 lo_lm_*): per evaluation one all-reduce(MIN) over the packed (d2, probe, slot) keys of the M replicated queries and
 one all-reduce(SUM) over 32 doubles (21 JtJ + 6 Jtr + cost + count). The loop mirrors
 /root/reference/src/cloud_matcher.cpp:105-178 (35 outer iterations, float round trip of the pose, stop rule on the
-last recorded step norm); the C++ twin is ShardedCloudMatcher in host/lo_b200.hpp.
+last recorded step norm). A C++ caller replaces the two collectives below by ncclAllReduce.
 
 A process may hold several shards (a list of backends): they are reduced locally first, then across processes with
 torch.distributed (NCCL on GPUs; gloo in the CPU test, where the backend is built on the oracle instead of CUDA).
