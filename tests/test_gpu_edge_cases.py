@@ -1,0 +1,104 @@
+"""Edge cases of LidarOdometry::processCloud through the per-scan kernel (and its stage-by-stage twin) against the CPU
+oracle: empty scans, scans with no usable point, ragged ring sets, non-finite returns, the size where the two
+pipelines hand over, empty query sets for align / the NN kernel."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import lidar_odometry_demo_b200 as lo
+from lidar_odometry_demo_b200 import synthetic as S
+from util import pose_error
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def run_both(ctx, port, scans):
+    od, oc = lo.LidarOdometry(ctx), port.odometry()
+    worst = (0.0, 0.0)
+    for k, sc in enumerate(scans):
+        od.processCloud(sc)
+        counts, _ = oc.process(sc)
+        dt, dr = pose_error(od.getCurrentPose(), oc.pose())
+        worst = (max(worst[0], dt), max(worst[1], dr))
+        st = od.stats()
+        assert (st.n_planar, st.n_update, st.n_query) == (counts[1], counts[2], counts[3]), f"scan {k}: planar/update/query counts differ"
+    return worst, od, oc
+
+
+def test_empty_and_unusable_scans(ctx, port, stream12):
+    scans = stream12[0]
+    empty = np.zeros(0, scans[0].dtype)
+    near = scans[2].copy()                      # every return inside lidar_min_range: nothing survives the range filter
+    for k in "xyz":
+        near[k] *= np.float32(0.01)
+    seq = [empty, scans[0], empty, scans[1], near, scans[3], scans[4]]
+    (dt, dr), od, oc = run_both(ctx, port, seq)
+    assert dt < 1e-4 and dr < 1e-4
+
+
+def test_ragged_rings_and_non_finite_returns(ctx, port, stream12):
+    scans = stream12[0]
+    two = scans[2][(scans[2]["ring"] == 3) | (scans[2]["ring"] == 7)]
+    holes = scans[3].copy()
+    holes["x"][::97] = np.nan                   # dropped returns as NaN / inf, as real drivers deliver them
+    holes["y"][5::131] = np.inf
+    few = scans[4][:40]                         # fewer points than a ring has columns
+    (dt, dr), od, oc = run_both(ctx, port, [scans[0], scans[1], two, holes, few, scans[5]])
+    assert dt < 1e-4 and dr < 1e-4
+
+
+def test_pipeline_handover_size(ctx, port, stream12):
+    """Scans up to 32 768 points run in the per-scan kernel, larger ones stage by stage: same results on both sides."""
+    scans = stream12[0]
+    base = np.concatenate([scans[0], scans[0][:5000]])
+    assert len(base) > 32769
+    a, b = base[:32768].copy(), base[:32769].copy()
+    (dt, dr), od, oc = run_both(ctx, port, [a, b, a])
+    assert dt < 1e-4 and dr < 1e-4
+
+
+def test_stage_by_stage_pipeline_matches_oracle():
+    """LO_B200_STAGED=1 (read once per process) routes every scan through the stage-by-stage kernels."""
+    code = """
+import numpy as np, oracle, lidar_odometry_demo_b200 as lo
+from lidar_odometry_demo_b200 import synthetic as S
+import sys; sys.path.insert(0, 'tests')
+from util import pose_error
+scans, _, _ = S.vlp16_stream(6)
+ctx = lo.Context(0); od = lo.LidarOdometry(ctx); oc = oracle.load('port').odometry()
+for sc in scans:
+    od.processCloud(sc); oc.process(sc)
+    dt, dr = pose_error(od.getCurrentPose(), oc.pose())
+    assert dt < 1e-4 and dr < 1e-4, (dt, dr)
+print('ok', ctx.kernel_launches)
+"""
+    env = dict(os.environ, LO_B200_STAGED="1")
+    r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert int(r.stdout.split()[-1]) > 6 * 10          # many launches per scan: it really took the staged path
+
+
+def test_empty_query_sets(ctx, port, stream12):
+    from util import planar_scene
+    kf = planar_scene(port, stream12[0], 0)
+    g = lo.VoxelGrid(ctx, 0.2, 20)
+    g.addCloud(kf)
+    none = np.zeros(0, S.XYZ)
+    guess = np.array([0.1, 0.0, 0.0, 1, 0, 0, 0], np.float32)
+    pose, st = lo.CloudMatcher().align(g, none, guess, with_stats=True)
+    o = port.grid(0.2, 20)
+    o.add_cloud(kf)
+    pose_o, log = o.align(none, guess)
+    dt, dr = pose_error(pose, pose_o)
+    assert dt < 1e-6 and dr < 1e-6 and st.valid_pairs == 0 and st.outer_iterations == len(log)
+    x = np.array([1, 0, 0, 0, 0.1, 0, 0], np.float64)
+    cost, grad, hess, nv = g.nnResidual(none, guess, x, x[4:])
+    assert nv == 0 and cost == 0.0
+    empty_grid = lo.VoxelGrid(ctx, 0.2, 20)
+    q = np.zeros(100, S.XYZ)
+    pose, st = lo.CloudMatcher().align(empty_grid, q, guess, with_stats=True)     # prior-only solve (cloud_matcher.cpp:153)
+    assert st.valid_pairs == 0 and np.allclose(pose[:3], guess[:3], atol=1e-6)
