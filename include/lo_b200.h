@@ -193,6 +193,11 @@ void lo_odometry_destroy(lo_odometry* h);
 /* processCloud (lidar_odometry.cpp:22-76) */
 int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t n);
 int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);
+/* processCloud on `xyzirt32` while the NEXT scan (`next_xyzirt32`, nullable; pinned host memory for a real overlap) is
+ * uploaded on a copy stream behind it; a later call that passes that same pointer and count as its current scan
+ * finds it in HBM. The caller must not modify the next scan's buffer until that call. Same results as
+ * lo_odometry_process. */
+int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, size_t n, const void* next_xyzirt32, size_t next_n);
 /* same pipeline entered after CloudClassifier::classify (lidar_odometry.cpp:35 onwards) with a planar cloud */
 int lo_odometry_process_planar(lo_odometry* h, const float* pn48_planar, size_t n);
 int lo_odometry_pose(lo_odometry* h, float out7[7]);                       /* getCurrentPose */

@@ -81,6 +81,7 @@ SIGNATURES = {
     "lo_params_default": (None, [_vp]), "lo_params_from_yaml": (_i, [C.c_char_p, _vp]),
     "lo_odometry_create": (_i, [_vp, _vp, C.POINTER(_vp)]), "lo_odometry_destroy": (None, [_vp]),
     "lo_odometry_process": (_i, [_vp, _vp, _sz]), "lo_odometry_process_dev": (_i, [_vp, _vp, _sz]),
+    "lo_odometry_process_next": (_i, [_vp, _vp, _sz, _vp, _sz]),
     "lo_odometry_process_planar": (_i, [_vp, _vp, _sz]), "lo_odometry_pose": (_i, [_vp, _vp]),
     "lo_odometry_stats": (_i, [_vp, _vp]),
     "lo_odometry_keyframe": (_i, [_vp, _i, _vp, _sz, C.POINTER(_sz)]),
@@ -312,6 +313,10 @@ class LidarOdometry:
     def processCloud(self, cloud):
         cloud = np.ascontiguousarray(cloud, dtype=XYZIRT)
         _check(self.lib.lo_odometry_process(self.h, _p(cloud), len(cloud)))
+
+    def processCloudWithNext(self, cloud_ptr, n, next_ptr, next_n):
+        """processCloud on a host scan while the next one (pinned host memory) is uploaded behind it."""
+        _check(self.lib.lo_odometry_process_next(self.h, C.c_void_p(cloud_ptr), n, C.c_void_p(next_ptr) if next_ptr else None, next_n))
 
     def processCloudDevice(self, device_ptr, n):
         _check(self.lib.lo_odometry_process_dev(self.h, C.c_void_p(device_ptr), n))

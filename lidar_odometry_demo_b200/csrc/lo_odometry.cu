@@ -201,7 +201,12 @@ extern "C" void lo_odometry_destroy(lo_odometry* h) {
     if (h->h_readback) cudaFreeHost(h->h_readback);
     if (h->d_minmax) cudaFree(h->d_minmax);
     fused_release(h);
-    for (DevBuf* b : {&h->scan, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    if (h->copy_stream) {
+        cudaStreamSynchronize(h->copy_stream);
+        cudaStreamDestroy(h->copy_stream);
+    }
+    if (h->copy_done) cudaEventDestroy(h->copy_done);
+    for (DevBuf* b : {&h->scan, &h->scan_next, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
     delete h;
 }
 
@@ -245,6 +250,33 @@ extern "C" int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t 
     LO_CUDA(cudaSetDevice(ctx->device));
     LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
     if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, ctx->stream));
+    return lo_odometry_process_dev(h, h->scan.p, n);
+}
+
+extern "C" int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, size_t n, const void* next_xyzirt32, size_t next_n) {
+    if (!h || (!xyzirt32 && n) || (!next_xyzirt32 && next_n)) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    if (!h->copy_stream) {
+        LO_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        LO_CUDA(cudaEventCreateWithFlags(&h->copy_done, cudaEventDisableTiming));
+    }
+    if (h->next_ptr && h->next_ptr == xyzirt32 && h->next_n == n) {
+        std::swap(h->scan, h->scan_next);                                   // uploaded (or arriving) behind the previous scan
+        LO_CUDA(cudaStreamWaitEvent(ctx->stream, h->copy_done, 0));
+    } else {
+        LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
+        if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    h->next_ptr = nullptr;
+    if (next_xyzirt32 && next_n) {
+        // scan_next was last read by a scan that has completed (every process call returns after its scan)
+        LO_TRY(h->scan_next.ensure(next_n * sizeof(PointXYZIRT)));
+        LO_CUDA(cudaMemcpyAsync(h->scan_next.p, next_xyzirt32, next_n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, h->copy_stream));
+        LO_CUDA(cudaEventRecord(h->copy_done, h->copy_stream));
+        h->next_ptr = next_xyzirt32;
+        h->next_n = next_n;
+    }
     return lo_odometry_process_dev(h, h->scan.p, n);
 }
 

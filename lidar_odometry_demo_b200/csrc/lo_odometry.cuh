@@ -63,6 +63,11 @@ struct lo_odometry {
     lo::ScanReadback* h_readback = nullptr;  // pinned, mapped: the per-scan kernel writes it directly
     uint32_t scan_seq = 0;                   // scans submitted to the per-scan kernel
     lo::DevBuf scan, deskewed, filtered, update, query;
+    lo::DevBuf scan_next;                    // lo_odometry_process_next: the scan being uploaded behind the current one
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_done = nullptr;
+    const void* next_ptr = nullptr;          // host pointer / count whose copy sits (or is arriving) in scan_next
+    size_t next_n = 0;
     lo::DevBuf fused;                // scratch of the fused pipeline (lo_pipeline.cu)
     uint32_t* d_minmax = nullptr;    // [2] ordered min / max of `time`, re-armed by the read-back kernel
     uint32_t n_last = 0;             // points in the deskewed cloud

@@ -410,6 +410,12 @@ public:
     LidarOdometry& operator=(const LidarOdometry&) = delete;
 
     void processCloud(const CloudType& input_cloud) { lo::check(lo_odometry_process(h_, input_cloud.points.data(), input_cloud.points.size())); }
+    // Extension: process `input_cloud` while `next_cloud` (the scan the caller will pass next, unchanged until then; pinned
+    // memory for a real overlap) is uploaded behind it.
+    void processCloud(const CloudType& input_cloud, const CloudType& next_cloud) {
+        lo::check(lo_odometry_process_next(h_, input_cloud.points.data(), input_cloud.points.size(), next_cloud.points.data(),
+                                           next_cloud.points.size()));
+    }
 
     pcl::PointCloud<pcl::PointXYZ>::Ptr getKeyFrameCloud() const { return keyframe(0); }
     pcl::PointCloud<pcl::PointXYZ>::Ptr getFullKeyFrameCloud() const { return keyframe(1); }

@@ -102,3 +102,17 @@ def test_empty_query_sets(ctx, port, stream12):
     q = np.zeros(100, S.XYZ)
     pose, st = lo.CloudMatcher().align(empty_grid, q, guess, with_stats=True)     # prior-only solve (cloud_matcher.cpp:153)
     assert st.valid_pairs == 0 and np.allclose(pose[:3], guess[:3], atol=1e-6)
+
+
+def test_process_next_equals_process(ctx, stream12):
+    """lo_odometry_process_next (next scan uploaded behind the current one) gives the poses of lo_odometry_process, also
+    when the announced next scan is not the one that arrives."""
+    scans = [np.ascontiguousarray(s) for s in stream12[0][:8]]
+    a, b = lo.LidarOdometry(ctx), lo.LidarOdometry(ctx)
+    for k, sc in enumerate(scans):
+        a.processCloud(sc)
+        nxt = scans[k + 1] if k + 1 < len(scans) else None
+        if k == 3:
+            nxt = scans[0]          # wrong announcement: must be ignored at the next call
+        b.processCloudWithNext(sc.ctypes.data, len(sc), nxt.ctypes.data if nxt is not None else None, len(nxt) if nxt is not None else 0)
+        assert np.array_equal(a.getCurrentPose(), b.getCurrentPose()), k
