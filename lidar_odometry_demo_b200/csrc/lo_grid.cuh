@@ -12,9 +12,16 @@ struct PointSource {       // AoS input: pcl::PointNormal (48 B) or pcl::PointXY
     const float* base;
     uint32_t stride_f;     // floats per record: 12 or 4
     int has_normals;
+    const uint32_t* gather = nullptr;   // optional: item i is record gather[(i + gather_shift) % gather_n]
+    uint32_t gather_n = 0, gather_shift = 0;
 };
 
 __device__ inline void load_point(const PointSource& src, uint32_t i, const Pose* pose, float p[3], float nrm[3]) {
+    if (src.gather) {
+        uint32_t at = i + src.gather_shift;
+        if (at >= src.gather_n) at -= src.gather_n;
+        i = src.gather[at];
+    }
     const float4 a = *reinterpret_cast<const float4*>(src.base + static_cast<size_t>(i) * src.stride_f);
     p[0] = a.x; p[1] = a.y; p[2] = a.z;
     if (src.has_normals) {

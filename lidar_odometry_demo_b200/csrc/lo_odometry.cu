@@ -128,7 +128,7 @@ static int finish_scan(lo_odometry* h, uint32_t n_points, bool readback_done = f
         const bool mode_sync = wait_mode && wait_mode[0] == 's', mode_both = wait_mode && wait_mode[0] == 'b';
         if (mode_sync) LO_CUDA(cudaStreamSynchronize(ctx->stream));
         for (uint32_t spins = 0; *seq != h->scan_seq; spins++) {
-            if ((spins & 0xFFFu) == 0xFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
+            if ((spins & 0xFFFFFu) == 0xFFFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
         }
         if (mode_both) LO_CUDA(cudaStreamSynchronize(ctx->stream));
         if (*seq != h->scan_seq) LO_CUDA(cudaStreamSynchronize(ctx->stream));

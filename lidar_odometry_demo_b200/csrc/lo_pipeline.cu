@@ -58,12 +58,12 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     DsSlot* ds_m;                          // [ds_cap] matching_downsampler   (cpp:46)
     uint32_t* slot_u;                      // [n] slot of filtered point i in ds_u
     uint32_t* slot_m;                      // [n]
-    uint32_t* ulist;                       // [n] update winners (index into filtered), arrival order
-    uint32_t* ubucket;                     // [n] their ideal robin_map bucket
-    uint32_t* usorted;                     // [n] update winners in robin_map order (index into ulist)
-    uint32_t* umember;                     // [n] bucket members before the tie groups are ordered
+    uint32_t* ubucket;                     // [n] ideal robin_map bucket of filtered point i if it is an update winner, else ~0
+    uint32_t* usorted;                     // [n] update winners in robin_map order (index into filtered)
+    uint32_t* umember;                     // [n] bucket members before a tie group is ordered
     uint32_t* rb_hist;                     // [rb_cap] winners per ideal bucket, then exclusive start of each bucket
     uint32_t* rb_fill;                     // [rb_cap] placement cursors
+    uint32_t* rb_done;                     // [rb_cap] members of a tie group that have been placed
     uint32_t* rb_coarse;                   // [kRobinBins] update winners per coarse bin of buckets
     int* rb_shift;                         // [1] max over sorted elements of (bucket - position)
     uint32_t* kf_slot;                     // [n] key-frame insert: slot of update point i
@@ -96,7 +96,6 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.ds_m = reinterpret_cast<DsSlot*>(take(static_cast<size_t>(b.ds_cap) * 16));
     b.slot_u = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.slot_m = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
-    b.ulist = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.ubucket = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.usorted = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.umember = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
@@ -105,6 +104,7 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.rb_cap = rb;
     b.rb_hist = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4 + 16));
     b.rb_fill = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
+    b.rb_done = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
     b.rb_shift = reinterpret_cast<int*>(take(16));
     b.rb_coarse = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
     b.kf_slot = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
@@ -150,7 +150,10 @@ __device__ inline void phase_prep(OdomDev* s, const PointXYZIRT* __restrict__ in
     if (tid < 256) b.hist[tid] = 0;
     if (tid < kRobinBins) b.rb_coarse[tid] = 0;
     if (tid == 0) *b.rb_shift = INT_MIN;
-    for (uint32_t c = tid; c < b.rb_cap; c += nthreads) b.rb_hist[c] = 0;
+    for (uint32_t c = tid; c < b.rb_cap; c += nthreads) {
+        b.rb_hist[c] = 0;
+        b.rb_done[c] = 0;
+    }
     for (uint32_t c = tid; c < b.cell_cap; c += nthreads) b.cell_idx[c] = 0;
     const uint4 empty = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
     uint4* u = reinterpret_cast<uint4*>(b.ds_u);
@@ -327,9 +330,11 @@ __device__ inline void phase_planar(PipeBufs b, float lo2, float hi2) {
     if (threadIdx.x == 0) b.block_counts[blockIdx.x] = count;
 }
 
-// find-or-create the voxel of (x,y,z) in a down-sampler table and record arrival index `pos`; returns the slot
+// find-or-create the voxel of (x,y,z) in a down-sampler table and record arrival index `pos`; returns the slot.
+// `created`: this call created the voxel (exactly one call per voxel does).
 __device__ inline uint32_t ds_insert(DsSlot* __restrict__ slots, uint32_t mask, float voxel_size, float x, float y, float z, uint32_t pos,
-                                     uint32_t* __restrict__ range_err) {
+                                     uint32_t* __restrict__ range_err, bool& created) {
+    created = false;
     const long long ix = axis_index(x, voxel_size), iy = axis_index(y, voxel_size), iz = axis_index(z, voxel_size);
     if (!axis_in_range(ix) || !axis_in_range(iy) || !axis_in_range(iz)) {
         *range_err = 1;
@@ -339,7 +344,10 @@ __device__ inline uint32_t ds_insert(DsSlot* __restrict__ slots, uint32_t mask, 
     uint32_t h = probe_hash(key) & mask;
     while (true) {
         unsigned long long k = slots[h].key;
-        if (k == kKeyEmpty) k = atomicCAS(&slots[h].key, kKeyEmpty, key);
+        if (k == kKeyEmpty) {
+            k = atomicCAS(&slots[h].key, kKeyEmpty, key);
+            created = k == kKeyEmpty;
+        }
         if (k == kKeyEmpty || k == key) break;
         h = (h + 1) & mask;
     }
@@ -355,7 +363,7 @@ __device__ inline void phase_scatter(OdomDev* s, PipeBufs b, PointNormal* __rest
     chunk_range(total, begin, end);
     block_prefix(b.block_counts, before, all);
     if (blockIdx.x == 0 && threadIdx.x == 0) s->n_planar = all;
-    uint32_t running = before;
+    uint32_t running = before, made_u = 0, made_m = 0;
     for (uint32_t base = begin; base < end; base += blockDim.x) {
         const uint32_t c = base + threadIdx.x;
         float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -364,44 +372,27 @@ __device__ inline void phase_scatter(OdomDev* s, PipeBufs b, PointNormal* __rest
         uint32_t tile_total;
         const uint32_t pos = running + block_rank(flag, tile_total);
         running += tile_total;
+        bool new_u = false, new_m = false;
         if (flag) {
             const float4 p = b.cellp[c];
             float4* o = reinterpret_cast<float4*>(filtered + pos);
             o[0] = make_float4(p.x, p.y, p.z, 1.f);
             o[1] = make_float4(nv.x, nv.y, nv.z, 0.f);
             o[2] = make_float4(0.f, 0.f, 0.f, 0.f);
-            b.slot_u[pos] = ds_insert(b.ds_u, b.ds_cap - 1, vs_u, p.x, p.y, p.z, pos, range_err);
-            if (with_match) b.slot_m[pos] = ds_insert(b.ds_m, b.ds_cap - 1, vs_m, p.x, p.y, p.z, pos, range_err);
+            b.slot_u[pos] = ds_insert(b.ds_u, b.ds_cap - 1, vs_u, p.x, p.y, p.z, pos, range_err, new_u);
+            if (with_match) b.slot_m[pos] = ds_insert(b.ds_m, b.ds_cap - 1, vs_m, p.x, p.y, p.z, pos, range_err, new_m);
         }
+        made_u += __syncthreads_count(new_u);
+        made_m += __syncthreads_count(new_m);
+    }
+    // the sizes of the two voxel sets = voxels created (known one phase before their winners are)
+    if (threadIdx.x == 0) {
+        if (made_u) atomicAdd(&s->n_update, made_u);
+        if (made_m) atomicAdd(&s->n_query, made_m);
     }
 }
 
-// P7. winners of the two down-samplers, per-block counts
-__device__ inline void phase_select(PipeBufs b, int with_match) {
-    uint32_t before, total;
-    block_prefix(b.block_counts, before, total);   // total = n_planar
-    uint32_t begin, end;
-    chunk_range(total, begin, end);
-    uint32_t cu = 0, cm = 0;
-    for (uint32_t base = begin; base < end; base += blockDim.x) {
-        const uint32_t i = base + threadIdx.x;
-        bool wu = false, wm = false;
-        if (i < end) {
-            const uint32_t su = b.slot_u[i];
-            wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
-            if (with_match) {
-                const uint32_t sm = b.slot_m[i];
-                wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
-            }
-        }
-        cu += __syncthreads_count(wu);
-        cm += __syncthreads_count(wm);
-    }
-    if (threadIdx.x == 0) {
-        b.block_counts[kMaxPipeBlocks + blockIdx.x] = cu;
-        b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
-    }
-}
+constexpr uint32_t kNoBucket = 0xFFFFFFFFu;
 
 __device__ inline uint32_t robin_bin_shift(uint32_t buckets) {   // log2(buckets per coarse bin)
     uint32_t shift = 0;
@@ -415,59 +406,39 @@ __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map a
     return c;
 }
 
-// P8. query cloud (matching_downsampler.getCloudWithoutNormals(), cpp:50 — emitted in arrival order: its order only
-// decides the order of the residual sum) and the update winners with their ideal robin_map bucket
-__device__ inline void phase_emit(OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
-                                                                  PointXYZ* __restrict__ query, int with_match) {
-    uint32_t before, total, bu, nu, bm, nm;
-    block_prefix(b.block_counts, before, total);
-    block_prefix(b.block_counts + kMaxPipeBlocks, bu, nu);
-    block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        s->n_update = nu;
-        s->n_query = nm;
-    }
-    const uint32_t buckets = robin_bucket_count(nu), bin_shift = robin_bin_shift(buckets);
+// P7. winners of the two down-samplers: update winners get their ideal robin_map bucket (histogrammed), matching
+// winners are counted per block for the ordered compaction of P8
+__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match) {
+    uint32_t before, total;
+    block_prefix(b.block_counts, before, total);   // total = n_planar
+    const uint32_t buckets = robin_bucket_count(s->n_update), bin_shift = robin_bin_shift(buckets);
     uint32_t begin, end;
     chunk_range(total, begin, end);
+    uint32_t cm = 0;
     for (uint32_t base = begin; base < end; base += blockDim.x) {
         const uint32_t i = base + threadIdx.x;
-        bool wu = false, wm = false;
-        uint32_t su = 0;
+        bool wm = false;
         if (i < end) {
-            su = b.slot_u[i];
-            wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+            const uint32_t su = b.slot_u[i];
+            uint32_t bucket = kNoBucket;
+            if (su != 0xFFFFFFFFu && b.ds_u[su].ticket == i) {
+                long long ix, iy, iz;
+                unpack_key(b.ds_u[su].key, ix, iy, iz);
+                bucket = reference_hash22(ix, iy, iz) & (buckets - 1);
+                atomicAdd(&b.rb_hist[bucket], 1u);
+                atomicAdd(&b.rb_coarse[bucket >> bin_shift], 1u);
+            }
+            b.ubucket[i] = bucket;
             if (with_match) {
                 const uint32_t sm = b.slot_m[i];
                 wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
             }
         }
-        uint32_t tu, tm;
-        const uint32_t ru = block_rank(wu, tu), rm = block_rank(wm, tm);
-        if (wu) {
-            long long ix, iy, iz;
-            unpack_key(b.ds_u[su].key, ix, iy, iz);
-            b.ulist[bu + ru] = i;
-            const uint32_t bucket = reference_hash22(ix, iy, iz) & (buckets - 1);
-            b.ubucket[bu + ru] = bucket;
-            atomicAdd(&b.rb_hist[bucket], 1u);
-            atomicAdd(&b.rb_coarse[bucket >> bin_shift], 1u);
-        }
-        if (wm) {
-            const float4 p = *reinterpret_cast<const float4*>(filtered + i);
-            reinterpret_cast<float4*>(query)[bm + rm] = make_float4(p.x, p.y, p.z, 1.f);
-        }
-        bu += tu;
-        bm += tm;
+        cm += __syncthreads_count(wm);
     }
+    if (threadIdx.x == 0) b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
 }
 
-// ---------------------------------------------------------------------------------------------------
-// P9. keyframe_downsampler.getCloud() (cpp:38,42,69): the update set in tsl::robin_map iteration order. For n inserted
-// keys the map has C = 2*pow2ceil(n) buckets; iteration is ascending bucket position; robin-hood probing keeps
-// elements sorted by ideal bucket b = hash22 & (C-1); a cluster that runs past the last bucket wraps to the front
-// (lo_robin.cu states the same rule for the stage-by-stage path). Counting sort by b: P8 histogrammed the buckets;
-// 9a scans the histogram, 9b places the winners, 9c orders every tie group by arrival and finds the wrap, 9d emits.
 // exclusive prefix of v over the block's threads, and the block total
 __device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
     __shared__ uint32_t warp_sums[32];
@@ -490,9 +461,39 @@ __device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
     return before + incl - v;
 }
 
-// 9a. bucket starts. P8 also histogrammed the buckets into <= kRobinBins coarse bins, so every bin is scanned by
-// one block on its own: start of the bin = sum of the coarse counts before it.
-__device__ inline void phase_robin_scan(const OdomDev* __restrict__ s, PipeBufs b) {
+// ---------------------------------------------------------------------------------------------------
+// P8. (a) query cloud (matching_downsampler.getCloudWithoutNormals(), cpp:50) in arrival order — its order only decides
+// the order of the residual sum; (b) start of every robin_map bucket.
+// keyframe_downsampler.getCloud() (cpp:38,42,69) is the update set in tsl::robin_map iteration order. For n inserted keys the
+// map has C = 2*pow2ceil(n) buckets; iteration is ascending bucket position; robin-hood probing keeps elements sorted
+// by ideal bucket b = hash22 & (C-1); a cluster that runs past the last bucket wraps to the front (lo_robin.cu states
+// the same rule for the stage-by-stage path). Counting sort by b: P7 histogrammed the buckets, also into <= kRobinBins
+// coarse bins, so every bin is scanned here by one block on its own (start of the bin = sum of the coarse counts before
+// it); P9 places the winners and orders every tie group by arrival; the insert reads them through the wrap rotation.
+__device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
+                                  PointXYZ* __restrict__ query, int with_match) {
+    uint32_t before, total, bm, nm;
+    block_prefix(b.block_counts, before, total);
+    if (with_match) {
+        block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
+        uint32_t begin, end;
+        chunk_range(total, begin, end);
+        for (uint32_t base = begin; base < end; base += blockDim.x) {
+            const uint32_t i = base + threadIdx.x;
+            bool wm = false;
+            if (i < end) {
+                const uint32_t sm = b.slot_m[i];
+                wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
+            }
+            uint32_t tm;
+            const uint32_t rm = block_rank(wm, tm);
+            if (wm) {
+                const float4 p = *reinterpret_cast<const float4*>(filtered + i);
+                reinterpret_cast<float4*>(query)[bm + rm] = make_float4(p.x, p.y, p.z, 1.f);
+            }
+            bm += tm;
+        }
+    }
     const uint32_t n = s->n_update;
     if (n == 0) return;
     const uint32_t C = robin_bucket_count(n);
@@ -511,44 +512,36 @@ __device__ inline void phase_robin_scan(const OdomDev* __restrict__ s, PipeBufs 
     }
 }
 
-__device__ inline void phase_robin_place(const OdomDev* __restrict__ s, PipeBufs b) {
-    const uint32_t n = s->n_update;
-    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
-        b.umember[atomicAdd(&b.rb_fill[b.ubucket[j]], 1u)] = j;
-}
-
-__device__ inline void phase_robin_order(const OdomDev* __restrict__ s, PipeBufs b) {
-    const uint32_t n = s->n_update;
+// P9. every update winner goes to its bucket's segment; the member that completes a tie group orders it by arrival
+// (= index in the filtered cloud). Sorted element k sits at bucket position k + max_{j<=k}(b_j - j): rb_shift collects
+// the maximum, which gives the wrap of the last cluster.
+__device__ inline void phase_robin_place(PipeBufs b) {
+    uint32_t before, total;
+    block_prefix(b.block_counts, before, total);   // total = n_planar
     int shift = INT_MIN;
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-        const uint32_t j = b.umember[p];
-        const uint32_t bk = b.ubucket[j];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t bk = b.ubucket[i];
+        if (bk == kNoBucket) continue;
         const uint32_t seg_begin = b.rb_hist[bk], seg_end = b.rb_hist[bk + 1];
-        uint32_t rank = 0;   // ulist is in arrival order, so arrival order inside the tie group is order by j
-        for (uint32_t q = seg_begin; q < seg_end; q++) rank += b.umember[q] < j ? 1u : 0u;
-        b.usorted[seg_begin + rank] = j;
-        // sorted element i sits at bucket position i + max_{k<=i}(b_k - k): the last one at n-1+max_shift
-        shift = max(shift, static_cast<int>(bk) - static_cast<int>(seg_begin + rank));
+        if (seg_end - seg_begin == 1) {
+            b.usorted[seg_begin] = i;
+            shift = max(shift, static_cast<int>(bk) - static_cast<int>(seg_begin));
+            continue;
+        }
+        b.umember[atomicAdd(&b.rb_fill[bk], 1u)] = i;
+        __threadfence();
+        if (atomicAdd(&b.rb_done[bk], 1u) + 1 != seg_end - seg_begin) continue;
+        __threadfence();   // the last member to arrive sees all the others
+        for (uint32_t a = seg_begin; a < seg_end; a++) {
+            const uint32_t ma = __ldcg(b.umember + a);
+            uint32_t rank = 0;
+            for (uint32_t q = seg_begin; q < seg_end; q++) rank += __ldcg(b.umember + q) < ma ? 1u : 0u;
+            b.usorted[seg_begin + rank] = ma;
+            shift = max(shift, static_cast<int>(bk) - static_cast<int>(seg_begin + rank));
+        }
     }
     for (int off = 16; off > 0; off >>= 1) shift = max(shift, __shfl_xor_sync(0xFFFFFFFFu, shift, off));
     if ((threadIdx.x & 31) == 0 && shift != INT_MIN) atomicMax(b.rb_shift, shift);
-}
-
-__device__ inline void phase_robin_emit(const OdomDev* __restrict__ s, PipeBufs b,
-                                                                        const PointNormal* __restrict__ filtered, PointNormal* __restrict__ update) {
-    const uint32_t n = s->n_update;
-    if (n == 0) return;
-    // positions >= C wrap to the front of the bucket array and are therefore iterated first
-    const long long over = static_cast<long long>(n) + *b.rb_shift - static_cast<long long>(robin_bucket_count(n));
-    const uint32_t rot = over > 0 ? static_cast<uint32_t>(over) : 0u;
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-        const uint32_t dst = (p + rot) % n;
-        const float4* src = reinterpret_cast<const float4*>(filtered + b.ulist[b.usorted[p]]);
-        float4* o = reinterpret_cast<float4*>(update + dst);
-        o[0] = src[0];
-        o[1] = src[1];
-        o[2] = src[2];
-    }
 }
 
 // lidar_odometry.cpp:53-65: Euler-angle divergence gate; returns the pose that becomes current_transform_
@@ -627,24 +620,15 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
     phase_scatter(s, p.b, p.filtered, p.vs_u, p.vs_m, with_match, range_err);
     grid.sync();
     LO_SCAN_TRACE(106);
-    phase_select(p.b, with_match);
+    phase_select(s, p.b, with_match);
     grid.sync();
     LO_SCAN_TRACE(107);
     phase_emit(s, p.b, p.filtered, p.query, with_match);
     grid.sync();
     LO_SCAN_TRACE(108);
-    phase_robin_scan(s, p.b);
+    phase_robin_place(p.b);
     grid.sync();
     LO_SCAN_TRACE(109);
-    phase_robin_place(s, p.b);
-    grid.sync();
-    LO_SCAN_TRACE(110);
-    phase_robin_order(s, p.b);
-    grid.sync();
-    LO_SCAN_TRACE(111);
-    phase_robin_emit(s, p.b, p.filtered, p.update);
-    grid.sync();
-    LO_SCAN_TRACE(112);
     __shared__ float next_s[7];
     __shared__ Pose current_s;
     __shared__ uint32_t unstable_s;
@@ -683,8 +667,16 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
         insert_pose = &current_s;        // transformWithNormals fused into the load (cpp:69)
     }
     // keyframe_.addCloud(update) (cpp:42 / cpp:70)
+    // the update cloud is read in place: output position d of the robin_map order is sorted element (d - rot) mod n,
+    // rot = how far the last cluster runs past the last bucket (positions >= C wrap to the front and are iterated first)
     const uint32_t nu = min(p.n, s->n_update);
-    const PointSource src{reinterpret_cast<const float*>(p.update), 12u, 1};
+    uint32_t gather_shift = 0;
+    if (nu) {
+        const long long over = static_cast<long long>(nu) + *p.b.rb_shift - static_cast<long long>(robin_bucket_count(nu));
+        const uint32_t rot = over > 0 ? static_cast<uint32_t>(over % nu) : 0u;
+        gather_shift = (nu - rot) % nu;
+    }
+    const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
         grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
     grid.sync();

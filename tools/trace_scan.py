@@ -1,5 +1,6 @@
 """Phase timeline of the per-scan kernel (LO_SCAN_TRACE=1): runs the bench stream for a few scans and aggregates the
-block-0 clock deltas per tag. Tags 100-112: pipeline phases before align; 0-9: align_device (see lo_align.cuh);
+block-0 clock deltas per tag. Tags 101-109: pipeline phases before align (prep, deskew, cell fill, curvature, planar, scatter, select, emit+bucket scan,
+bucket placement); 0-9: align_device (see lo_align.cuh);
 120-124: gate, cleanup, locate, chain, write."""
 import os, subprocess, sys, collections, re
 env = dict(os.environ, LO_SCAN_TRACE="1")
