@@ -38,7 +38,8 @@ enum {
     LO_E_ARG = -2,       /* bad argument */
     LO_E_CAPACITY = -3,  /* caller buffer too small; the needed count is returned through the size out-param */
     LO_E_RANGE = -4,     /* a voxel index fell outside the supported +-2^20 range */
-    LO_E_IO = -5         /* file could not be read / parsed */
+    LO_E_IO = -5,        /* file could not be read / parsed */
+    LO_E_BUSY = -6       /* lo_odometry_submit: two scans already in flight / scans in flight during a synchronous call */
 };
 
 typedef struct lo_ctx lo_ctx;
@@ -198,6 +199,15 @@ int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);
  * finds it in HBM. The caller must not modify the next scan's buffer until that call. Same results as
  * lo_odometry_process. */
 int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, size_t n, const void* next_xyzirt32, size_t next_n);
+/* processCloud split in two for recorded streams: lo_odometry_submit queues a scan (its upload and its kernel run behind
+ * the scan in flight, so the GPU goes from one scan to the next without waiting for the host) and returns at once;
+ * lo_odometry_wait blocks until the OLDEST queued scan is done, after which lo_odometry_pose / _stats describe that
+ * scan. At most two scans in flight (LO_E_BUSY otherwise); a host buffer must stay untouched until the wait that
+ * matches its submit; scans of more than 32 768 points are not accepted here. submit + wait == lo_odometry_process:
+ * same poses, same key frame. */
+int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n);
+int lo_odometry_submit_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);
+int lo_odometry_wait(lo_odometry* h);
 /* same pipeline entered after CloudClassifier::classify (lidar_odometry.cpp:35 onwards) with a planar cloud */
 int lo_odometry_process_planar(lo_odometry* h, const float* pn48_planar, size_t n);
 int lo_odometry_pose(lo_odometry* h, float out7[7]);                       /* getCurrentPose */

@@ -16,7 +16,7 @@ from .synthetic import PN, XYZ, XYZIRT  # noqa: F401  (wire dtypes)
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "liblo_b200.so")
 
-LO_OK, LO_E_CUDA, LO_E_ARG, LO_E_CAPACITY, LO_E_RANGE, LO_E_IO = 0, -1, -2, -3, -4, -5
+LO_OK, LO_E_CUDA, LO_E_ARG, LO_E_CAPACITY, LO_E_RANGE, LO_E_IO, LO_E_BUSY = 0, -1, -2, -3, -4, -5, -6
 
 
 class LoError(RuntimeError):
@@ -82,6 +82,7 @@ SIGNATURES = {
     "lo_odometry_create": (_i, [_vp, _vp, C.POINTER(_vp)]), "lo_odometry_destroy": (None, [_vp]),
     "lo_odometry_process": (_i, [_vp, _vp, _sz]), "lo_odometry_process_dev": (_i, [_vp, _vp, _sz]),
     "lo_odometry_process_next": (_i, [_vp, _vp, _sz, _vp, _sz]),
+    "lo_odometry_submit": (_i, [_vp, _vp, _sz]), "lo_odometry_submit_dev": (_i, [_vp, _vp, _sz]), "lo_odometry_wait": (_i, [_vp]),
     "lo_odometry_process_planar": (_i, [_vp, _vp, _sz]), "lo_odometry_pose": (_i, [_vp, _vp]),
     "lo_odometry_stats": (_i, [_vp, _vp]),
     "lo_odometry_keyframe": (_i, [_vp, _i, _vp, _sz, C.POINTER(_sz)]),
@@ -317,6 +318,17 @@ class LidarOdometry:
     def processCloudWithNext(self, cloud_ptr, n, next_ptr, next_n):
         """processCloud on a host scan while the next one (pinned host memory) is uploaded behind it."""
         _check(self.lib.lo_odometry_process_next(self.h, C.c_void_p(cloud_ptr), n, C.c_void_p(next_ptr) if next_ptr else None, next_n))
+
+    def submit(self, host_ptr, n):
+        """Queue a host scan (lo_odometry_submit); at most two in flight."""
+        _check(self.lib.lo_odometry_submit(self.h, C.c_void_p(host_ptr), n))
+
+    def submitDevice(self, device_ptr, n):
+        _check(self.lib.lo_odometry_submit_dev(self.h, C.c_void_p(device_ptr), n))
+
+    def wait(self):
+        """Block until the oldest queued scan is done; getCurrentPose() / stats() then describe it."""
+        _check(self.lib.lo_odometry_wait(self.h))
 
     def processCloudDevice(self, device_ptr, n):
         _check(self.lib.lo_odometry_process_dev(self.h, C.c_void_p(device_ptr), n))

@@ -111,35 +111,8 @@ static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P
     return LO_OK;
 }
 
-static int finish_scan(lo_odometry* h, uint32_t n_points, bool readback_done = false) {
-    lo_ctx* ctx = h->ctx;
-    if (!readback_done) {
-        odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
-        LO_LAUNCHED(ctx);
-        LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
-        LO_CUDA(cudaStreamSynchronize(ctx->stream));
-        h->h_readback->seq = 0;   // never a per-scan kernel's number
-    } else {
-        // the per-scan kernel wrote the block into pinned memory; its last store is `seq`. Poll it (the result is
-        // there a few microseconds before the stream reports the kernel as retired), checking the stream now and then
-        // so that a failed launch cannot hang the caller.
-        const volatile uint32_t* seq = &h->h_readback->seq;
-        static const char* wait_mode = getenv("LO_B200_WAIT");   // developer switch: "sync", "both" or (default) poll
-        const bool mode_sync = wait_mode && wait_mode[0] == 's', mode_both = wait_mode && wait_mode[0] == 'b';
-        if (mode_sync) LO_CUDA(cudaStreamSynchronize(ctx->stream));
-        for (uint32_t spins = 0; *seq != h->scan_seq; spins++) {
-            if ((spins & 0xFFFFFu) == 0xFFFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
-        }
-        if (mode_both) LO_CUDA(cudaStreamSynchronize(ctx->stream));
-        if (*seq != h->scan_seq) LO_CUDA(cudaStreamSynchronize(ctx->stream));
-        if (*seq != h->scan_seq) {
-            set_error("the per-scan kernel finished without publishing its result");
-            return LO_E_CUDA;
-        }
-        std::atomic_thread_fence(std::memory_order_acquire);
-    }
-    if (readback_done) fused_trace_dump(h);
-    const ScanReadback& r = *h->h_readback;
+// copy a scan's result block into the handle (pose, stats, host mirror of the key-frame counters)
+static int adopt_readback(lo_odometry* h, const ScanReadback& r, uint32_t n_points) {
     std::memcpy(h->pose, r.pose, sizeof(h->pose));
     std::memcpy(h->keyframe->h_counters, r.kf_counters, sizeof(r.kf_counters));
     // arrival tickets are tracked on the host
@@ -154,6 +127,60 @@ static int finish_scan(lo_odometry* h, uint32_t n_points, bool readback_done = f
         set_error("a key-frame point was not finite or outside the +-2^20 voxel index range");
         return LO_E_RANGE;
     }
+    return LO_OK;
+}
+
+// stage-by-stage pipeline: read-back kernel + one D2H
+static int finish_scan(lo_odometry* h, uint32_t n_points) {
+    lo_ctx* ctx = h->ctx;
+    odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
+    LO_LAUNCHED(ctx);
+    LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    h->h_readback[0].seq = 0;   // never a per-scan kernel's number
+    h->keyframe->cleaned = true;
+    return adopt_readback(h, h->h_readback[0], n_points);
+}
+
+// per-scan kernel: wait for the oldest scan in flight. The kernel wrote the block into pinned memory; its last store
+// is `seq`. Poll it (the result is there a few microseconds before the stream reports the kernel as retired),
+// checking the stream now and then so that a failed launch cannot hang the caller.
+static int wait_oldest(lo_odometry* h) {
+    lo_ctx* ctx = h->ctx;
+    const uint32_t want = h->wait_seq + 1, slot = want & 1u;
+    const volatile uint32_t* seq = &h->h_readback[slot].seq;
+    static const char* wait_mode = getenv("LO_B200_WAIT");   // developer switch: "sync" waits on the stream first
+    if (wait_mode && wait_mode[0] == 's') LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (uint32_t spins = 0; *seq != want; spins++) {
+        if ((spins & 0xFFFFFu) == 0xFFFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
+    }
+    if (*seq != want) LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (*seq != want) {
+        set_error("the per-scan kernel finished without publishing its result");
+        return LO_E_CUDA;
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    h->wait_seq = want;
+    h->pending_points -= h->queued_n[slot];
+    if (h->wait_seq == h->scan_seq) fused_trace_dump(h);
+    const ScanReadback& r = h->h_readback[slot];
+    if (!r.bootstrap) h->keyframe->cleaned = true;   // radiusCleanup ran: reference iteration order can no longer be emulated
+    const int st = adopt_readback(h, r, h->queued_n[slot]);
+    h->keyframe->h_counters[GC_TICKET] = h->queued_ticket[(h->scan_seq) & 1u];   // tickets: as of the newest scan submitted
+    return st;
+}
+
+static int submit_fused(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
+    if (h->scan_seq - h->wait_seq >= 2) {
+        set_error("two scans are already in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
+    LO_TRY(fused_process_enqueue(h, d_scan, n));
+    const uint32_t slot = h->scan_seq & 1u;
+    h->queued_n[slot] = n;
+    h->queued_ticket[slot] = h->keyframe->h_counters[GC_TICKET];
+    h->pending_points += n;
+    h->n_last = n;
     return LO_OK;
 }
 
@@ -177,8 +204,8 @@ extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odome
     LO_CUDA(cudaMalloc(&h->d_state, sizeof(OdomDev)));
     LO_CUDA(cudaMemsetAsync(h->d_state, 0, sizeof(OdomDev), ctx->stream));
     LO_CUDA(cudaMalloc(&h->d_readback, sizeof(ScanReadback)));
-    LO_CUDA(cudaMallocHost(&h->h_readback, sizeof(ScanReadback)));
-    std::memset(h->h_readback, 0, sizeof(ScanReadback));
+    LO_CUDA(cudaMallocHost(&h->h_readback, 2 * sizeof(ScanReadback)));
+    std::memset(h->h_readback, 0, 2 * sizeof(ScanReadback));
     LO_CUDA(cudaMalloc(&h->d_minmax, 2 * sizeof(uint32_t)));
     const uint32_t minmax_init[2] = {0xFFFFFFFFu, 0u};
     LO_CUDA(cudaMemcpyAsync(h->d_minmax, minmax_init, sizeof(minmax_init), cudaMemcpyHostToDevice, ctx->stream));
@@ -206,7 +233,9 @@ extern "C" void lo_odometry_destroy(lo_odometry* h) {
         cudaStreamDestroy(h->copy_stream);
     }
     if (h->copy_done) cudaEventDestroy(h->copy_done);
-    for (DevBuf* b : {&h->scan, &h->scan_next, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    for (DevBuf* b : {&h->scan, &h->scan_next, &h->scan_q[0], &h->scan_q[1], &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    for (cudaEvent_t e : h->scan_q_done)
+        if (e) cudaEventDestroy(e);
     delete h;
 }
 
@@ -217,13 +246,13 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
     OdomDev* s = h->d_state;
     const uint32_t nn = static_cast<uint32_t>(n);
     static const bool staged = getenv("LO_B200_STAGED") != nullptr;  // developer switch: stage-by-stage pipeline
+    if (h->scan_seq != h->wait_seq) {
+        set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
     if (!staged && nn <= kFusedMaxPoints) {
-        h->n_last = nn;
-        LO_TRY(fused_process_enqueue(h, static_cast<const PointXYZIRT*>(d_xyzirt32), nn));
-        const uint32_t ticket_after = h->keyframe->h_counters[GC_TICKET];
-        const int st = finish_scan(h, nn, true);
-        preserve_ticket(h->keyframe, ticket_after);
-        return st;
+        LO_TRY(submit_fused(h, static_cast<const PointXYZIRT*>(d_xyzirt32), nn));
+        return wait_oldest(h);
     }
     const uint32_t kf_ticket = h->keyframe->h_counters[GC_TICKET];
     LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
@@ -280,12 +309,63 @@ extern "C" int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, si
     return lo_odometry_process_dev(h, h->scan.p, n);
 }
 
+extern "C" int lo_odometry_submit_dev(lo_odometry* h, const void* d_xyzirt32, size_t n) {
+    if (!h || (!d_xyzirt32 && n)) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    if (n > kFusedMaxPoints) {
+        set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", kFusedMaxPoints);
+        return LO_E_ARG;
+    }
+    return submit_fused(h, static_cast<const PointXYZIRT*>(d_xyzirt32), static_cast<uint32_t>(n));
+}
+
+extern "C" int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n) {
+    if (!h || (!xyzirt32 && n)) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    if (n > kFusedMaxPoints) {
+        set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", kFusedMaxPoints);
+        return LO_E_ARG;
+    }
+    if (h->scan_seq - h->wait_seq >= 2) {
+        set_error("two scans are already in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
+    if (!h->copy_stream) {
+        LO_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        LO_CUDA(cudaEventCreateWithFlags(&h->copy_done, cudaEventDisableTiming));
+    }
+    // the slot's device copy was last read by scan (seq - 1), which has been waited for; the upload runs on the copy
+    // stream, i.e. under the kernel of the scan in flight
+    const uint32_t slot = (h->scan_seq + 1) & 1u;
+    if (!h->scan_q_done[slot]) LO_CUDA(cudaEventCreateWithFlags(&h->scan_q_done[slot], cudaEventDisableTiming));
+    LO_TRY(h->scan_q[slot].ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
+    if (n) LO_CUDA(cudaMemcpyAsync(h->scan_q[slot].p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, h->copy_stream));
+    LO_CUDA(cudaEventRecord(h->scan_q_done[slot], h->copy_stream));
+    LO_CUDA(cudaStreamWaitEvent(ctx->stream, h->scan_q_done[slot], 0));
+    return submit_fused(h, h->scan_q[slot].as<PointXYZIRT>(), static_cast<uint32_t>(n));
+}
+
+extern "C" int lo_odometry_wait(lo_odometry* h) {
+    if (!h) return LO_E_ARG;
+    if (h->scan_seq == h->wait_seq) {
+        set_error("lo_odometry_wait: no scan in flight");
+        return LO_E_ARG;
+    }
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    return wait_oldest(h);
+}
+
 extern "C" int lo_odometry_process_planar(lo_odometry* h, const float* pn48_planar, size_t n) {
     if (!h || (!pn48_planar && n)) return LO_E_ARG;
     lo_ctx* ctx = h->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
     OdomDev* s = h->d_state;
     const uint32_t nn = static_cast<uint32_t>(n);
+    if (h->scan_seq != h->wait_seq) {
+        set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
     LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, pn48_planar, n * sizeof(PointNormal), cudaMemcpyHostToDevice, ctx->stream));

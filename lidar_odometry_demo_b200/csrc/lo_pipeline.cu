@@ -582,7 +582,6 @@ struct ScanArgs {
     ScanReadback* readback;      // pinned host memory
     uint32_t seq;                // this scan's number, published in readback->seq when everything else is written
     uint32_t n;
-    int first;                   // the key-frame is empty: bootstrap scan (cpp:40-44)
     float lo2, hi2, vs_u, vs_m, cleanup_range, gate_threshold;
     long long* trace;
 };
@@ -590,7 +589,10 @@ struct ScanArgs {
 __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
     cg::grid_group grid = cg::this_grid();
     OdomDev* s = p.s;
-    const int with_match = p.first ? 0 : 1;
+    // the key frame is empty: bootstrap scan (cpp:40-44). Read on the device, so the host can queue a scan before the
+    // previous one has reported back; nothing changes the counter before the insert at the end.
+    const int first = __ldcg(p.kf_counters + GC_VOXELS) == 0 ? 1 : 0;
+    const int with_match = first ? 0 : 1;
     uint32_t* range_err = p.kf_counters + GC_RANGE_ERR;
     int trace_n = 0;
 #define LO_SCAN_TRACE(tag)                                                     \
@@ -633,7 +635,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
     __shared__ Pose current_s;
     __shared__ uint32_t unstable_s;
     const Pose* insert_pose = nullptr;   // first scan: inserted un-transformed (cpp:42)
-    if (!p.first) {
+    if (!first) {
         AlignArgs a;                     // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
         a.g = p.kf;
         a.queries = p.query;
@@ -691,7 +693,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
     LO_SCAN_TRACE(124);
     if (blockIdx.x == 0 && threadIdx.x == 0) {   // read-back block for the host; re-arm the next scan's time min/max
         grid_fix_counters(p.kf_counters);
-        if (!p.first) {                          // the gate's outcome becomes the state of the next scan
+        if (!first) {                            // the gate's outcome becomes the state of the next scan
             s->current = current_s;
             s->unstable = unstable_s;
             s->center[0] = current_s.t[0]; s->center[1] = current_s.t[1]; s->center[2] = current_s.t[2];
@@ -703,6 +705,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
         out->n_query = s->n_query;
         out->unstable = s->unstable;
         out->outer_iterations = s->align.outer_iterations;
+        out->bootstrap = static_cast<uint32_t>(first);
         for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
         p.minmax[0] = 0xFFFFFFFFu;
         p.minmax[1] = 0u;
@@ -737,7 +740,9 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
         }
     }
     const int blocks = std::min<int>(ctx->sm_count, kMaxPipeBlocks);   // one block per SM
-    LO_TRY(grid_reserve(kf, n));   // room for this scan's insert; may rebuild the table, so take the view afterwards
+    // room for this scan's insert and for those of the scans still in flight (the host mirror of the counters is as old
+    // as the last scan waited for); may rebuild the table, so take the view afterwards
+    LO_TRY(grid_reserve(kf, static_cast<size_t>(n) + h->pending_points));
     ScanArgs p;
     p.s = h->d_state;
     p.scan = d_scan;
@@ -752,10 +757,9 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.kf_counters = kf->counters;
     p.kf_free_list = kf->free_list;
     p.ticket_base = kf->h_counters[GC_TICKET];
-    p.readback = h->h_readback;   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
     p.seq = ++h->scan_seq;
+    p.readback = h->h_readback + (p.seq & 1u);   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
     p.n = n;
-    p.first = kf->h_counters[GC_VOXELS] == 0 ? 1 : 0;  // cpp:40 (host mirror from the last scan's read-back)
     p.lo2 = h->params.lidar_min_range * h->params.lidar_min_range;
     p.hi2 = h->params.lidar_max_range * h->params.lidar_max_range;
     p.vs_u = h->params.keyframe_update_voxel_size;
@@ -772,7 +776,6 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream));
     ctx->launches++;
     kf->h_counters[GC_TICKET] = p.ticket_base + n;
-    if (!p.first) kf->cleaned = true;
     return LO_OK;
 }
 

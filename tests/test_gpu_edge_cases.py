@@ -116,3 +116,39 @@ def test_process_next_equals_process(ctx, stream12):
             nxt = scans[0]          # wrong announcement: must be ignored at the next call
         b.processCloudWithNext(sc.ctypes.data, len(sc), nxt.ctypes.data if nxt is not None else None, len(nxt) if nxt is not None else 0)
         assert np.array_equal(a.getCurrentPose(), b.getCurrentPose()), k
+
+
+def test_submit_wait_pipeline_equals_process(ctx, stream12):
+    """lo_odometry_submit / lo_odometry_wait with two scans in flight: the poses, counts and key frame of the one-call
+    lo_odometry_process, scan by scan (an empty scan first, so the bootstrap decision is taken on the device twice)."""
+    scans = [np.zeros(0, stream12[0][0].dtype)] + [np.ascontiguousarray(s) for s in stream12[0][:9]]
+    a, b = lo.LidarOdometry(ctx), lo.LidarOdometry(ctx)
+    ref = []
+    for sc in scans:
+        a.processCloud(sc)
+        st = a.stats()
+        ref.append((a.getCurrentPose().copy(), st.n_planar, st.n_update, st.n_query, st.outer_iterations, st.keyframe_voxels))
+    got = []
+
+    def collect():
+        b.wait()
+        st = b.stats()
+        got.append((b.getCurrentPose().copy(), st.n_planar, st.n_update, st.n_query, st.outer_iterations, st.keyframe_voxels))
+
+    b.submit(scans[0].ctypes.data, len(scans[0]))
+    for k in range(1, len(scans)):
+        b.submit(scans[k].ctypes.data, len(scans[k]))            # scan k queued behind scan k-1
+        if k == 3:
+            with pytest.raises(lo.LoError) as e:                   # a third one is refused, nothing is lost
+                b.submit(scans[k].ctypes.data, len(scans[k]))
+            assert e.value.code == lo.LO_E_BUSY
+            with pytest.raises(lo.LoError):                        # and so is a synchronous call while scans are in flight
+                b.processCloud(scans[k])
+        collect()
+    collect()
+    assert len(got) == len(ref)
+    for k, (r, g) in enumerate(zip(ref, got)):
+        assert np.array_equal(r[0], g[0]) and r[1:] == g[1:], (k, r, g)
+    with pytest.raises(lo.LoError):
+        b.wait()                                                   # nothing in flight
+    b.processCloud(scans[1])                                       # the synchronous call works again
