@@ -107,28 +107,49 @@ def cpu_oracle(kind=None):
     return oracle.load(kind), kind
 
 
+def _reference_stream(job):
+    """One stream through the reference's CPU path (own process); returns the wall time of the timed scans."""
+    stream_id, warmup, steps = job
+    orc, kind = cpu_oracle()
+    scans = make_stream(warmup + steps, stream_id)
+    od = orc.odometry()
+    for k in range(warmup):
+        od.process(scans[k])
+    t0 = time.perf_counter()
+    for k in range(warmup, warmup + steps):
+        od.process(scans[k])
+    return time.perf_counter() - t0, kind
+
+
 def run_reference(args):
-    """The reference's own CPU implementation of the path on this box's host cores (rank 0 only)."""
+    """The reference's own CPU implementation of the path on this box's host cores (rank 0 only). The workload at N GPUs is
+    N independent streams, so the CPU arm runs N streams too, one process each (the reference itself is single-threaded:
+    std::execution::par is serial without TBB, Ceres num_threads = 1), as many at a time as there are cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    orc, kind = cpu_oracle()
-    scans = make_stream(args.warmup + args.steps, 0)
-    od = orc.odometry()
-    for k in range(args.warmup):
-        od.process(scans[k])
+    import concurrent.futures as cf
+    n = max(1, args.gpus)
+    cores = max(1, min(n, os.cpu_count() or 1))
+    jobs = [(g, args.warmup, args.steps) for g in range(n)]
     t0 = time.perf_counter()
-    for k in range(args.warmup, args.warmup + args.steps):
-        od.process(scans[k])
-    dt = time.perf_counter() - t0
-    value = args.steps / dt
+    if n == 1:
+        results = [_reference_stream(jobs[0])]
+        dt = results[0][0]
+    else:
+        with cf.ProcessPoolExecutor(max_workers=cores) as pool:
+            results = list(pool.map(_reference_stream, jobs))
+        dt = max(r[0] for r in results) if cores >= n else time.perf_counter() - t0
+    kind = results[0][1]
+    value = n * args.steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 points / f64 solver", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "parallelism": "1 host thread (std::execution::par is serial without TBB; Ceres default num_threads=1)"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "reference" if kind == "reference" else "port",
-                         "sample": f"{args.steps} consecutive scans after {args.warmup} warm-up scans of the same stream",
+        "config": {"workload": WORKLOAD, "parallelism": f"{n} independent stream(s), one single-threaded process each on {cores} host core(s) "
+                   "(std::execution::par is serial without TBB; Ceres default num_threads=1)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if kind == "reference" else "port",
+                         "sample": f"{args.steps} consecutive scans after {args.warmup} warm-up scans of each of the {n} stream(s)",
                          "note": "reference's own headers + vendored robin_map (oracle/_ref) with Ceres restated (mini_ceres): omits "
                                  "Ceres' per-residual allocations, so it is faster than the true reference" if kind == "reference"
                                  else "oracle port (oracle/_ref not built on this box)"},

@@ -417,6 +417,11 @@ public:
                                            next_cloud.points.size()));
     }
 
+    // Extension for recorded streams: queue a scan (at most two in flight; its buffer must stay untouched until the matching
+    // wait) and collect the results in order. submit + wait == processCloud.
+    void submit(const CloudType& input_cloud) { lo::check(lo_odometry_submit(h_, input_cloud.points.data(), input_cloud.points.size())); }
+    void wait() { lo::check(lo_odometry_wait(h_)); }
+
     pcl::PointCloud<pcl::PointXYZ>::Ptr getKeyFrameCloud() const { return keyframe(0); }
     pcl::PointCloud<pcl::PointXYZ>::Ptr getFullKeyFrameCloud() const { return keyframe(1); }
     Pose3D getCurrentPose() const {

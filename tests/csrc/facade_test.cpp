@@ -116,14 +116,65 @@ static void matching_test(const char* xyz_path, size_t n, const char* normals_pa
     }
 }
 
+// A small VLP16-like sweep of a street canyon (ground z = -1.8, walls y = +-8) seen from x = shift: enough structure for
+// LidarOdometry::processCloud; used to check that the facade's one-call and queued entry points agree.
+static LidarOdometry::CloudType street_scan(float shift) {
+    LidarOdometry::CloudType cloud;
+    for (int ring = 0; ring < 16; ring++) {
+        const float el = (-15.0f + 2.0f * ring) * static_cast<float>(std::numbers::pi / 180.0);
+        for (int k = 0; k < 1800; k++) {
+            const float az = k * static_cast<float>(2.0 * std::numbers::pi / 1800.0);
+            const float dx = std::cos(el) * std::cos(az), dy = std::cos(el) * std::sin(az), dz = std::sin(el);
+            float range = 1e9f;
+            if (dz < -1e-3f) range = std::min(range, -1.8f / dz);
+            if (std::abs(dy) > 1e-3f) range = std::min(range, 8.0f / std::abs(dy));
+            if (range > 100.f) continue;
+            lidar_point::PointXYZIRT p;
+            p.x = range * dx - shift; p.y = range * dy; p.z = range * dz;
+            p.intensity = 10.f; p.ring = static_cast<uint16_t>(ring); p.time = 0.1f * k / 1800.0f;
+            cloud.points.push_back(p);
+        }
+    }
+    cloud.width = static_cast<uint32_t>(cloud.points.size());
+    cloud.height = 1;
+    return cloud;
+}
+
+static void odometry_one_call_and_queued() {
+    std::vector<LidarOdometry::CloudType> scans;
+    for (int k = 0; k < 5; k++) scans.push_back(street_scan(0.1f * k));
+    LidarOdometry one(LidarOdometry::Params{}), queued(LidarOdometry::Params{});
+    std::vector<Pose3D> ref;
+    for (const auto& sc : scans) {
+        one.processCloud(sc);
+        ref.push_back(one.getCurrentPose());
+    }
+    CHECK(one.getKeyFrameCloud()->size() > 0);
+    CHECK(std::abs(ref.back().translation.y()) < 0.05f);    // the sensor moved along x only
+    size_t done = 0;
+    queued.submit(scans[0]);
+    for (size_t k = 1; k < scans.size(); k++) {
+        queued.submit(scans[k]);                              // scan k queued behind scan k-1
+        queued.wait();
+        const Pose3D p = queued.getCurrentPose();
+        CHECK(p.translation.x() == ref[done].translation.x() && p.rotation.w() == ref[done].rotation.w());
+        done++;
+    }
+    queued.wait();
+    CHECK(queued.getCurrentPose().translation.x() == ref[done].translation.x());
+    std::printf("odometry: %zu scans, final x = %g (one call) / %g (queued)\n", scans.size(), ref.back().translation.x(),
+                queued.getCurrentPose().translation.x());
+}
+
 int main(int argc, char** argv) {
     try {
         voxel_grid_unique_points();
         voxel_grid_duplicate_points();
         rigid_transform();
         if (argc >= 4) matching_test(argv[1], std::strtoul(argv[2], nullptr, 10), argv[3]);
-        LidarOdometry odom(LidarOdometry::Params{});   // constructs the pipeline object; scans are fed by the Python tests
+        LidarOdometry odom(LidarOdometry::Params{});
         CHECK(odom.getKeyFrameCloud()->size() == 0);
+        odometry_one_call_and_queued();
     } catch (const lo::Error& e) {
         std::printf("lo::Error %d: %s\n", e.code, e.what());
         return 2;
