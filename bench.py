@@ -54,6 +54,8 @@ class ClockSampler:
     def __init__(self, device, period_s=0.02):
         self.device, self.period, self.sm, self.mx, self.reasons = device, period_s, [], None, set()
         self.stop_flag, self.thread, self.nv, self.handle = threading.Event(), None, None, None
+        if os.environ.get("LO_BENCH_NO_CLOCKS"):   # diagnosis only: no NVML polling at all
+            return
         try:
             import pynvml
             pynvml.nvmlInit()
