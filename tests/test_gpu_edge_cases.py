@@ -152,3 +152,24 @@ def test_submit_wait_pipeline_equals_process(ctx, stream12):
     with pytest.raises(lo.LoError):
         b.wait()                                                   # nothing in flight
     b.processCloud(scans[1])                                       # the synchronous call works again
+
+
+def test_config3_scan_size(ctx, port):
+    """BASELINE.json config 3: 128 beams x 2048 columns (~245 k returns per scan), voxels 0.1 / 0.05 / 0.05 — the largest scans
+    of the contract (they take the stage-by-stage pipeline and the tile search in align): counts and poses as the oracle."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from bench_c3 import c3_params, c3_stream
+    scans = c3_stream(3)
+    assert len(scans[0]) > 200_000
+    od = lo.LidarOdometry(ctx, c3_params(lo))
+    op = port.default_params()
+    op.keyframe_voxel_size, op.keyframe_update_voxel_size, op.keyframe_matching_voxel_size = 0.1, 0.05, 0.05
+    oc = port.odometry(op)
+    for k, sc in enumerate(scans):
+        od.processCloud(sc)
+        counts, _ = oc.process(sc)
+        st = od.stats()
+        assert (st.n_planar, st.n_update, st.n_query) == (counts[1], counts[2], counts[3]), k
+        dt, dr = pose_error(od.getCurrentPose(), oc.pose())
+        assert dt < 1e-4 and dr < 1e-4, (k, dt, dr)
