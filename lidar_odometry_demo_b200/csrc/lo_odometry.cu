@@ -76,12 +76,6 @@ __global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counte
 
 using namespace lo;
 
-int lo::odom_gate_enqueue(lo_odometry* h) {
-    odom_gate_kernel<<<1, 1, 0, h->ctx->stream>>>(h->d_state, h->params.angular_divergence_threshold);
-    LO_LAUNCHED(h->ctx);
-    return LO_OK;
-}
-
 static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P) {
     lo_ctx* ctx = h->ctx;
     OdomDev* s = h->d_state;

@@ -90,5 +90,4 @@ constexpr uint32_t kFusedMaxPoints = 32768;
 int fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n);
 void fused_release(lo_odometry* h);
 void fused_trace_dump(lo_odometry* h);
-int odom_gate_enqueue(lo_odometry* h);   // lo_odometry.cu: the divergence gate of lidar_odometry.cpp:53-65
 }  // namespace lo

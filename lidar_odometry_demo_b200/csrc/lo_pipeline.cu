@@ -1,7 +1,8 @@
 // LidarOdometry::processCloud (src/lidar_odometry.cpp:22-76) as ONE persistent cooperative kernel per scan, for scans
 // of up to kFusedMaxPoints points (a VLP16 revolution is ~30 k). One block per SM; the stages below are separated by
-// grid-wide barriers instead of kernel launches, poses and counts never leave the device, and the host reads back
-// 96 bytes when the kernel is done.
+// grid-wide barriers instead of kernel launches, poses and counts never leave the device (not even the decision whether
+// this is the bootstrap scan, so the host can queue a scan behind the one in flight), and the kernel ends by writing
+// an 88-byte result block straight into pinned host memory.
 //
 //   P1 prep        constant-velocity prediction (cpp:27-28,51) | min/max of `time` | clear scratch and the two
 //                  down-sampler tables
@@ -11,14 +12,17 @@
 //   P5 planar      planar test + normals (cloud_classifier.h:107-165) fused with rangeFilter (cpp:35) -> flags, block counts
 //   P6 scatter     ordered compaction into the filtered planar cloud | insert every point into both
 //                  VoxelGrid(vs,1) down-samplers (cpp:37-38,46-47): find-or-create voxel, atomicMin of the arrival index
-//   P7 select      which points are the first of their voxel (winners), block counts
-//   P8 emit        query cloud M (arrival order) | update winners U with their robin_map bucket, bucket histogram
-//   P9 a-d         the update set in the reference's tsl::robin_map iteration order: counting sort
+//                  (the voxels created = the sizes of the update set U and the query set M)
+//   P7 select      which points are the first of their voxel (winners): U winners get their tsl::robin_map bucket
+//                  (histogram), M winners are counted per block
+//   P8 emit        query cloud M (arrival order) | start of every robin_map bucket
+//   P9 place       the update set in the reference's robin_map iteration order: counting sort by bucket,
+//                  tie groups ordered by arrival; the insert below reads U through the wrap rotation
 //   align          CloudMatcher::align (lo_align.cuh), cpp:49-51
-//   gate           Euler-angle divergence gate (cpp:53-65)
+//   gate           Euler-angle divergence gate (cpp:53-65), evaluated by every block on the identical result
 //   clean-up       keyframe_.radiusCleanup (cpp:67)
 //   insert         transformWithNormals + keyframe_.addCloud (cpp:69-70): locate, ticket chain, write (lo_grid.cuh)
-//   read-back      pose + counters for the host
+//   read-back      pose + counters into pinned host memory, sequence word last
 //
 // Every per-point formula is the shared code of lo_stages.cuh / lo_grid.cuh / lo_align.cuh, so this kernel and the
 // stage-by-stage entry points (lo_points.cu, lo_grid.cu, lo_match.cu) produce identical bits; the GPU tests run both
@@ -570,7 +574,6 @@ struct ScanArgs {
     const PointXYZIRT* scan;
     PointXYZIRT* desk;
     PointNormal* filtered;
-    PointNormal* update;
     PointXYZ* query;
     uint32_t* minmax;
     PipeBufs b;
@@ -729,7 +732,6 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     carve(b, h->fused.as<char>(), std::max<uint32_t>(n, 1));
     LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
     LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
-    LO_TRY(h->update.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     LO_TRY(h->query.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZ)));
     static int blocks_per_sm = 0;
     if (blocks_per_sm == 0) {
@@ -748,7 +750,6 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.scan = d_scan;
     p.desk = h->deskewed.as<PointXYZIRT>();
     p.filtered = h->filtered.as<PointNormal>();
-    p.update = h->update.as<PointNormal>();
     p.query = h->query.as<PointXYZ>();
     p.minmax = h->d_minmax;
     p.b = b;
