@@ -81,6 +81,14 @@ int lo_grid_get_cloud(lo_grid* g, int mode, int order, void* out, size_t cap, si
 /* radiusCleanup (:236-246): erase voxels whose FIRST stored point is farther than radius from center */
 int lo_grid_radius_cleanup(lo_grid* g, const float center[3], float radius);
 
+/* Snapshot / restore (the reference's VoxelGrid is an implicitly copyable value,
+ * src/lidar_odometry.h:82, and has no serialisation). The blob is the table as it lies in HBM (slots, slabs, free
+ * list, counters) behind a small header; a restored grid answers every call exactly like the original. `out` may be
+ * NULL to query *bytes; LO_E_CAPACITY if cap is too small; restore wants a grid created with the same max_points and
+ * returns LO_E_IO for a blob it does not recognise. */
+int lo_grid_snapshot(lo_grid* g, void* out, size_t cap, size_t* bytes);
+int lo_grid_restore(lo_grid* g, const void* blob, size_t bytes);
+
 typedef struct lo_pair {   /* VoxelGrid::Correspondence (:40-46) */
     double source_point_local[3];
     double plane_origin[3];
@@ -216,6 +224,12 @@ int lo_odometry_stats(lo_odometry* h, lo_scan_stats* out);
 int lo_odometry_keyframe(lo_odometry* h, int full, float* xyz16_out, size_t cap, size_t* n);
 int lo_odometry_keyframe_pn(lo_odometry* h, float* pn48_out, size_t cap, size_t* n);
 int lo_odometry_deskewed(lo_odometry* h, void* xyzirt32_out, size_t cap, size_t* n);  /* getTempCloud */
+
+/* Checkpoint of a running LidarOdometry: previous_transform_ / current_transform_ / keyframe_
+ * (src/lidar_odometry.h:82-85) + the last scan's stats. A fresh lo_odometry created with the same Params and restored
+ * from the blob continues with bit-identical poses. No scan may be in flight (LO_E_BUSY). */
+int lo_odometry_snapshot(lo_odometry* h, void* out, size_t cap, size_t* bytes);
+int lo_odometry_restore(lo_odometry* h, const void* blob, size_t bytes);
 
 #ifdef __cplusplus
 }

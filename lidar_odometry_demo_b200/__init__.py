@@ -64,6 +64,8 @@ SIGNATURES = {
     "lo_grid_add_cloud": (_i, [_vp, _vp, _sz, _i]), "lo_grid_add_cloud_dev": (_i, [_vp, _vp, _sz, _i]),
     "lo_grid_get_cloud": (_i, [_vp, _i, _i, _vp, _sz, C.POINTER(_sz)]),
     "lo_grid_radius_cleanup": (_i, [_vp, _vp, _fl]),
+    "lo_grid_snapshot": (_i, [_vp, _vp, _sz, C.POINTER(_sz)]), "lo_grid_restore": (_i, [_vp, _vp, _sz]),
+    "lo_odometry_snapshot": (_i, [_vp, _vp, _sz, C.POINTER(_sz)]), "lo_odometry_restore": (_i, [_vp, _vp, _sz]),
     "lo_grid_find_matching_pairs": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp, C.POINTER(_sz)]),
     "lo_nn_residual": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
     "lo_nn_residual_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
@@ -253,6 +255,18 @@ class VoxelGrid:
     def getSparseCloudWithoutNormals(self, reference_order=False):
         return self._get(2, int(reference_order), XYZ)
 
+    def snapshot(self):
+        """The table as it lies in HBM (lo_grid_snapshot) as a uint8 array."""
+        n = C.c_size_t(0)
+        _check(self.lib.lo_grid_snapshot(self.h, None, 0, C.byref(n)))
+        out = np.empty(n.value, np.uint8)
+        _check(self.lib.lo_grid_snapshot(self.h, _p(out), len(out), C.byref(n)))
+        return out
+
+    def restore(self, blob):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        _check(self.lib.lo_grid_restore(self.h, _p(blob), len(blob)))
+
     def radiusCleanup(self, center, radius):
         c = np.ascontiguousarray(center, dtype=np.float32)
         _check(self.lib.lo_grid_radius_cleanup(self.h, _p(c), radius))
@@ -336,6 +350,18 @@ class LidarOdometry:
     def processPlanar(self, planar):
         planar = np.ascontiguousarray(planar, dtype=PN)
         _check(self.lib.lo_odometry_process_planar(self.h, _p(planar), len(planar)))
+
+    def snapshot(self):
+        """Checkpoint (poses + key-frame table) as a uint8 array: lo_odometry_snapshot."""
+        n = C.c_size_t(0)
+        _check(self.lib.lo_odometry_snapshot(self.h, None, 0, C.byref(n)))
+        out = np.empty(n.value, np.uint8)
+        _check(self.lib.lo_odometry_snapshot(self.h, _p(out), len(out), C.byref(n)))
+        return out
+
+    def restore(self, blob):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        _check(self.lib.lo_odometry_restore(self.h, _p(blob), len(blob)))
 
     def getCurrentPose(self):
         out = np.empty(7, np.float32)

@@ -6,6 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "liblo_b200.so")
+REPLAY = os.path.join(HERE, "lo_replay")   # headless driver (apps/lo_replay.cpp): host C++ over the C ABI
 SOURCES = ["lo_api.cu", "lo_grid.cu", "lo_robin.cu", "lo_match.cu", "lo_points.cu", "lo_planefit.cu", "lo_odometry.cu", "lo_pipeline.cu"]
 # -fmad=false: no FMA contraction, the reference is unfused x86-64 arithmetic (DESIGN.md "numerics")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
@@ -20,8 +21,22 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_apps(force=False):
+    """g++ only: the driver sees nothing but include/lo_b200.h and the header-only host facade."""
+    deps = [os.path.join(HERE, "apps", "lo_replay.cpp"), os.path.join(HERE, "host", "lo_io.hpp"), os.path.join(HERE, "host", "lo_b200.hpp"), OUT]
+    if not force and os.path.exists(REPLAY) and all(os.path.getmtime(d) <= os.path.getmtime(REPLAY) for d in deps):
+        return REPLAY
+    cmd = ["g++", "-std=c++20", "-O2", "-Wall", "-o", REPLAY, deps[0], f"-L{HERE}", "-l:liblo_b200.so", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("g++ failed on lo_replay")
+    return REPLAY
+
+
 def build(force=False, verbose=False):
     if not force and not needs_build():
+        build_apps()
         return OUT
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     extra = os.environ.get("LO_B200_NVCC_EXTRA", "").split()   # developer builds, e.g. -DLO_TILE_DEBUG
@@ -32,6 +47,7 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed")
     if verbose:
         sys.stderr.write(r.stderr)
+    build_apps(force=True)
     return OUT
 
 

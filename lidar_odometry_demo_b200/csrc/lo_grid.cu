@@ -9,6 +9,7 @@
 // sequence) and is pushed through the free entries of its voxel's slab with a chain of atomicMin on the
 // w lane; entry k ends up holding the k-th smallest ticket, whatever the thread interleaving.
 #include <algorithm>
+#include <cstring>
 
 #include "lo_grid.cuh"
 
@@ -132,9 +133,21 @@ static int rebuild_table(lo_grid* g, uint32_t new_capacity) {
 }
 
 int grid_refresh_counters(lo_grid* g) {
+    const uint32_t ticket = g->h_counters[GC_TICKET];   // arrival tickets are handed out by the host only
     LO_CUDA(cudaMemcpyAsync(g->h_counters, g->counters, sizeof(g->h_counters), cudaMemcpyDeviceToHost, g->ctx->stream));
     LO_CUDA(cudaStreamSynchronize(g->ctx->stream));
+    g->h_counters[GC_TICKET] = ticket;
     return LO_OK;
+}
+
+// Tickets only order the points of ONE add_cloud batch inside a voxel (entries below the voxel's count are never
+// touched again) and the voxels of a never-cleared grid for the reference-order export; 0xFFFFFFFF marks a free
+// entry. Restart the sequence before it could reach that value (after ~4e9 offered points).
+uint32_t grid_take_tickets(lo_grid* g, uint32_t n) {
+    if (g->h_counters[GC_TICKET] > 0xF0000000u - n) g->h_counters[GC_TICKET] = 0;
+    const uint32_t base = g->h_counters[GC_TICKET];
+    g->h_counters[GC_TICKET] = base + n;
+    return base;
 }
 
 // Make room for `incoming` more points (each may open a new voxel). Uses the host mirror of the counters,
@@ -165,7 +178,7 @@ int grid_add_dev(lo_grid* g, const void* d_points, size_t n, int has_normals, co
     LO_TRY(ctx->tmp_b.ensure(n * sizeof(uint32_t)));
     PointSource src{static_cast<const float*>(d_points), has_normals ? 12u : 4u, has_normals};
     const uint32_t nn = static_cast<uint32_t>(n);
-    const uint32_t ticket_base = g->h_counters[GC_TICKET];
+    const uint32_t ticket_base = grid_take_tickets(g, nn);
     const GridView v = g->view();
     const unsigned blocks = blocks_for(n, 256);
     grid_locate_kernel<<<blocks, 256, 0, ctx->stream>>>(src, nn, d_n, d_pose, v, g->counters, g->free_list, ctx->tmp_a.as<uint32_t>());
@@ -177,7 +190,6 @@ int grid_add_dev(lo_grid* g, const void* d_points, size_t n, int has_normals, co
     LO_LAUNCHED(ctx);
     grid_fix_counters_kernel<<<1, 1, 0, ctx->stream>>>(g->counters);
     LO_LAUNCHED(ctx);
-    g->h_counters[GC_TICKET] = ticket_base + nn;
     // conservative host-side bounds until the next refresh
     g->h_counters[GC_VOXELS] += nn;
     g->h_counters[GC_BUMP] += nn;
@@ -215,9 +227,126 @@ int grid_export_dev(lo_grid* g, int mode, void* d_out, uint32_t* d_count) {
     return LO_OK;
 }
 
+
+// ---- snapshot / restore: the table is dumped as it lies in HBM (slots, the slabs handed out so far, the free list,
+// the counters), so a restored grid behaves bit for bit like the original: same probe positions, same slab order.
+struct GridSnapHeader {
+    uint64_t magic;
+    uint32_t header_bytes, width;
+    float voxel_size;
+    uint32_t capacity;
+    uint64_t max_points;
+    uint32_t payload_used, free_n;
+    uint32_t shard_rank, shard_world;
+    uint32_t cleaned, reserved;
+    uint32_t counters[GC_COUNT];
+};
+constexpr uint64_t kGridMagic = 0x0001444952474F4CULL;   // "LOGRID\1\0"
+
+static size_t grid_snapshot_payload(const GridSnapHeader& h) {
+    return static_cast<size_t>(h.capacity) * sizeof(Slot) + 2 * static_cast<size_t>(h.payload_used) * h.width * sizeof(float4) +
+           static_cast<size_t>(h.free_n) * sizeof(uint32_t);
+}
+
+int grid_snapshot(lo_grid* g, void* out, size_t cap, size_t* bytes) {
+    lo_ctx* ctx = g->ctx;
+    LO_TRY(grid_refresh_counters(g));
+    GridSnapHeader h{};
+    h.magic = kGridMagic;
+    h.header_bytes = sizeof(GridSnapHeader);
+    h.width = g->width;
+    h.voxel_size = g->voxel_size;
+    h.capacity = g->capacity;
+    h.max_points = g->max_points;
+    h.payload_used = std::min<uint32_t>(g->h_counters[GC_BUMP], g->payload_cap);
+    h.free_n = static_cast<uint32_t>(std::max<int32_t>(static_cast<int32_t>(g->h_counters[GC_FREE_TOP]), 0));
+    h.shard_rank = g->shard_rank;
+    h.shard_world = g->shard_world;
+    h.cleaned = g->cleaned ? 1u : 0u;
+    for (int k = 0; k < GC_COUNT; k++) h.counters[k] = g->h_counters[k];
+    const size_t total = sizeof(h) + grid_snapshot_payload(h);
+    *bytes = total;
+    if (!out) return LO_OK;
+    if (cap < total) return LO_E_CAPACITY;
+    char* o = static_cast<char*>(out);
+    std::memcpy(o, &h, sizeof(h));
+    o += sizeof(h);
+    const size_t slab = static_cast<size_t>(h.payload_used) * h.width * sizeof(float4);
+    LO_CUDA(cudaMemcpyAsync(o, g->slots, static_cast<size_t>(h.capacity) * sizeof(Slot), cudaMemcpyDeviceToHost, ctx->stream));
+    o += static_cast<size_t>(h.capacity) * sizeof(Slot);
+    if (slab) {
+        LO_CUDA(cudaMemcpyAsync(o, g->points, slab, cudaMemcpyDeviceToHost, ctx->stream));
+        LO_CUDA(cudaMemcpyAsync(o + slab, g->normals, slab, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    o += 2 * slab;
+    if (h.free_n) LO_CUDA(cudaMemcpyAsync(o, g->free_list, static_cast<size_t>(h.free_n) * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return LO_OK;
+}
+
+int grid_restore(lo_grid* g, const void* blob, size_t bytes) {
+    lo_ctx* ctx = g->ctx;
+    GridSnapHeader h;
+    if (bytes < sizeof(h)) {
+        set_error("grid snapshot: %zu bytes is shorter than the header", bytes);
+        return LO_E_IO;
+    }
+    std::memcpy(&h, blob, sizeof(h));
+    if (h.magic != kGridMagic || h.header_bytes != sizeof(h) || h.capacity == 0 || (h.capacity & (h.capacity - 1)) != 0 ||
+        h.free_n > h.payload_used || bytes != sizeof(h) + grid_snapshot_payload(h)) {
+        set_error("grid snapshot: bad magic, version or size");
+        return LO_E_IO;
+    }
+    if (h.width != g->width || h.max_points != g->max_points) {
+        set_error("grid snapshot was taken with max_points %llu, this grid has %zu", static_cast<unsigned long long>(h.max_points), g->max_points);
+        return LO_E_ARG;
+    }
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (h.capacity != g->capacity) {
+        Slot* fresh = nullptr;
+        LO_CUDA(cudaMalloc(&fresh, static_cast<size_t>(h.capacity) * sizeof(Slot)));
+        if (g->slots) cudaFree(g->slots);
+        g->slots = fresh;
+        g->capacity = h.capacity;
+    }
+    if (h.payload_used > g->payload_cap) LO_TRY(grow_payload(g, next_pow2(std::max<uint64_t>(h.payload_used, 1024))));
+    const char* in = static_cast<const char*>(blob) + sizeof(h);
+    const size_t slab = static_cast<size_t>(h.payload_used) * h.width * sizeof(float4);
+    LO_CUDA(cudaMemcpyAsync(g->slots, in, static_cast<size_t>(h.capacity) * sizeof(Slot), cudaMemcpyHostToDevice, ctx->stream));
+    in += static_cast<size_t>(h.capacity) * sizeof(Slot);
+    // entries never handed out must read as free (ticket lane 0xFFFFFFFF)
+    LO_CUDA(cudaMemsetAsync(g->points, 0xFF, static_cast<size_t>(g->payload_cap) * g->width * sizeof(float4), ctx->stream));
+    if (slab) {
+        LO_CUDA(cudaMemcpyAsync(g->points, in, slab, cudaMemcpyHostToDevice, ctx->stream));
+        LO_CUDA(cudaMemcpyAsync(g->normals, in + slab, slab, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    in += 2 * slab;
+    if (h.free_n) LO_CUDA(cudaMemcpyAsync(g->free_list, in, static_cast<size_t>(h.free_n) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(g->counters, h.counters, sizeof(h.counters), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < GC_COUNT; k++) g->h_counters[k] = h.counters[k];
+    g->voxel_size = h.voxel_size;
+    g->shard_rank = h.shard_rank;
+    g->shard_world = h.shard_world;
+    g->cleaned = h.cleaned != 0;
+    return LO_OK;
+}
+
 }  // namespace lo
 
 using namespace lo;
+
+extern "C" int lo_grid_snapshot(lo_grid* g, void* out, size_t cap, size_t* bytes) {
+    if (!g || !bytes) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(g->ctx->device));
+    return grid_snapshot(g, out, cap, bytes);
+}
+
+extern "C" int lo_grid_restore(lo_grid* g, const void* blob, size_t bytes) {
+    if (!g || !blob) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(g->ctx->device));
+    return grid_restore(g, blob, bytes);
+}
 
 extern "C" int lo_grid_create(lo_ctx* ctx, float voxel_size, size_t max_points, size_t capacity_hint, lo_grid** out) {
     if (!ctx || !out || !(voxel_size > 0.f)) return LO_E_ARG;

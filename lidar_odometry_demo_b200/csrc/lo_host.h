@@ -121,6 +121,9 @@ int grid_reserve(lo_grid* g, size_t incoming_points);             // make room f
 // n = host-side upper bound of the point count; d_n (nullable) = device-side actual count
 int grid_add_dev(lo_grid* g, const void* d_points, size_t n, int has_normals, const Pose* d_pose_or_null, const uint32_t* d_n);
 int grid_refresh_counters(lo_grid* g);                            // D2H of the counter block (synchronises)
+uint32_t grid_take_tickets(lo_grid* g, uint32_t n);               // arrival tickets of the next n offered points
+int grid_snapshot(lo_grid* g, void* out, size_t cap, size_t* bytes);
+int grid_restore(lo_grid* g, const void* blob, size_t bytes);
 int grid_clear(lo_grid* g);
 int grid_cleanup_dev(lo_grid* g, const float* d_center3, float radius);
 int grid_export_dev(lo_grid* g, int mode, void* d_out, uint32_t* d_count);

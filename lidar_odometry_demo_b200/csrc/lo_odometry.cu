@@ -409,3 +409,88 @@ extern "C" int lo_odometry_deskewed(lo_odometry* h, void* xyzirt32_out, size_t c
     LO_CUDA(cudaStreamSynchronize(h->ctx->stream));
     return LO_OK;
 }
+
+// ---- snapshot / restore of a running odometry. The reference keeps this state in plain value
+// members (keyframe_, previous_transform_, current_transform_: src/lidar_odometry.h:82-85) and has no checkpoint;
+// here it is the device-resident pose block plus the key-frame table as it lies in HBM, so a restored object
+// continues with bit-identical poses. The two per-scan down-samplers are rebuilt by every scan and are not saved;
+// getTempCloud is empty until the next scan.
+namespace {
+struct OdomSnapHeader {
+    uint64_t magic;
+    uint32_t header_bytes, state_bytes;
+    lo_params params;
+    lo_scan_stats stats;
+    float pose[7];
+    uint32_t reserved;
+};
+constexpr uint64_t kOdomMagic = 0x00014D4F444F4F4CULL;   // "LOODOM\1\0"
+bool same_params(const lo_params& a, const lo_params& b) {
+    return a.lidar_min_range == b.lidar_min_range && a.lidar_max_range == b.lidar_max_range && a.keyframe_voxel_size == b.keyframe_voxel_size &&
+           a.keyframe_max_points_cnt == b.keyframe_max_points_cnt && a.keyframe_matching_voxel_size == b.keyframe_matching_voxel_size &&
+           a.keyframe_update_voxel_size == b.keyframe_update_voxel_size && a.keyframe_cleanup_range == b.keyframe_cleanup_range &&
+           a.angular_divergence_threshold == b.angular_divergence_threshold;
+}
+}  // namespace
+
+extern "C" int lo_odometry_snapshot(lo_odometry* h, void* out, size_t cap, size_t* bytes) {
+    if (!h || !bytes) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    if (h->scan_seq != h->wait_seq) {
+        set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
+    size_t grid_bytes = 0;
+    LO_TRY(grid_snapshot(h->keyframe, nullptr, 0, &grid_bytes));
+    const size_t fixed = sizeof(OdomSnapHeader) + sizeof(OdomDev);
+    *bytes = fixed + grid_bytes;
+    if (!out) return LO_OK;
+    if (cap < *bytes) return LO_E_CAPACITY;
+    OdomSnapHeader hd{};
+    hd.magic = kOdomMagic;
+    hd.header_bytes = sizeof(OdomSnapHeader);
+    hd.state_bytes = sizeof(OdomDev);
+    hd.params = h->params;
+    hd.stats = h->stats;
+    std::memcpy(hd.pose, h->pose, sizeof(hd.pose));
+    char* o = static_cast<char*>(out);
+    std::memcpy(o, &hd, sizeof(hd));
+    LO_CUDA(cudaMemcpyAsync(o + sizeof(hd), h->d_state, sizeof(OdomDev), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return grid_snapshot(h->keyframe, o + fixed, cap - fixed, &grid_bytes);
+}
+
+extern "C" int lo_odometry_restore(lo_odometry* h, const void* blob, size_t bytes) {
+    if (!h || !blob) return LO_E_ARG;
+    lo_ctx* ctx = h->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    if (h->scan_seq != h->wait_seq) {
+        set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
+    OdomSnapHeader hd;
+    const size_t fixed = sizeof(OdomSnapHeader) + sizeof(OdomDev);
+    if (bytes < fixed) {
+        set_error("odometry snapshot: %zu bytes is shorter than the header", bytes);
+        return LO_E_IO;
+    }
+    std::memcpy(&hd, blob, sizeof(hd));
+    if (hd.magic != kOdomMagic || hd.header_bytes != sizeof(OdomSnapHeader) || hd.state_bytes != sizeof(OdomDev)) {
+        set_error("odometry snapshot: bad magic or version");
+        return LO_E_IO;
+    }
+    if (!same_params(hd.params, h->params)) {
+        set_error("odometry snapshot was taken with different LidarOdometry::Params");
+        return LO_E_ARG;
+    }
+    const char* in = static_cast<const char*>(blob);
+    LO_TRY(grid_restore(h->keyframe, in + fixed, bytes - fixed));
+    LO_CUDA(cudaMemcpyAsync(h->d_state, in + sizeof(hd), sizeof(OdomDev), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    h->stats = hd.stats;
+    std::memcpy(h->pose, hd.pose, sizeof(h->pose));
+    h->n_last = 0;
+    h->next_ptr = nullptr;
+    return LO_OK;
+}

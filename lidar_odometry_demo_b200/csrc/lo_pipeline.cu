@@ -757,7 +757,7 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.kf_capacity = kf->capacity;
     p.kf_counters = kf->counters;
     p.kf_free_list = kf->free_list;
-    p.ticket_base = kf->h_counters[GC_TICKET];
+    p.ticket_base = grid_take_tickets(kf, n);
     p.seq = ++h->scan_seq;
     p.readback = h->h_readback + (p.seq & 1u);   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
     p.n = n;
@@ -776,7 +776,6 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     void* kargs[] = {&p};
     LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream));
     ctx->launches++;
-    kf->h_counters[GC_TICKET] = p.ticket_base + n;
     return LO_OK;
 }
 

@@ -15,6 +15,7 @@
 
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -228,8 +229,19 @@ public:
         if (this != &o) { lo_grid_destroy(h_); ctx_ = o.ctx_; h_ = o.h_; voxel_size_ = o.voxel_size_; max_points_ = o.max_points_; o.h_ = nullptr; }
         return *this;
     }
-    VoxelGrid(const VoxelGrid& o) : VoxelGrid(o.voxel_size_, o.max_points_, *o.ctx_) { addCloud(*o.getCloud()); }  // deep copy via the host
+    // deep copy through a snapshot of the table (lo_grid_snapshot): the copy is in the same state as the original, clean-up
+    // history included, which re-inserting getCloud() would not give
+    VoxelGrid(const VoxelGrid& o) : VoxelGrid(o.voxel_size_, o.max_points_, *o.ctx_) { restore(o.snapshot()); }
     VoxelGrid& operator=(const VoxelGrid& o) { if (this != &o) { VoxelGrid t(o); *this = std::move(t); } return *this; }
+
+    std::vector<uint8_t> snapshot() const {
+        size_t n = 0;
+        lo::check(lo_grid_snapshot(h_, nullptr, 0, &n));
+        std::vector<uint8_t> blob(n);
+        lo::check(lo_grid_snapshot(h_, blob.data(), blob.size(), &n));
+        return blob;
+    }
+    void restore(const std::vector<uint8_t>& blob) { lo::check(lo_grid_restore(h_, blob.data(), blob.size())); }
 
     void setVoxelSize(float voxel_size) { voxel_size_ = voxel_size; lo::check(lo_grid_set_voxel_size(h_, voxel_size)); }
     Indices getIndices(float x, float y, float z) const {
@@ -442,6 +454,35 @@ public:
         lo_scan_stats s;
         lo::check(lo_odometry_stats(h_, &s));
         return s;
+    }
+
+    // Extension: checkpoint of previous_transform_ / current_transform_ / keyframe_ (src/lidar_odometry.h:82-85); an object
+    // built with the same Params and restored from it continues with bit-identical poses.
+    std::vector<uint8_t> snapshot() const {
+        size_t n = 0;
+        lo::check(lo_odometry_snapshot(h_, nullptr, 0, &n));
+        std::vector<uint8_t> blob(n);
+        lo::check(lo_odometry_snapshot(h_, blob.data(), blob.size(), &n));
+        return blob;
+    }
+    void restore(const std::vector<uint8_t>& blob) { lo::check(lo_odometry_restore(h_, blob.data(), blob.size())); }
+    void saveCheckpoint(const std::string& path) const {
+        const std::vector<uint8_t> blob = snapshot();
+        std::FILE* f = std::fopen(path.c_str(), "wb");
+        if (!f || std::fwrite(blob.data(), 1, blob.size(), f) != blob.size()) {
+            if (f) std::fclose(f);
+            throw lo::Error(LO_E_IO, "cannot write checkpoint " + path);
+        }
+        std::fclose(f);
+    }
+    void loadCheckpoint(const std::string& path) {
+        std::FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) throw lo::Error(LO_E_IO, "cannot open checkpoint " + path);
+        std::vector<uint8_t> blob;
+        uint8_t chunk[1 << 16];
+        for (size_t got; (got = std::fread(chunk, 1, sizeof(chunk), f)) > 0;) blob.insert(blob.end(), chunk, chunk + got);
+        std::fclose(f);
+        restore(blob);
     }
 
 private:
