@@ -157,6 +157,37 @@ int lo_lm_propose(lo_lm* h, double cand7[7]);                                   
 int lo_lm_update(lo_lm* h, const double acc32[32]);                                                /* 1: continue */
 int lo_lm_result(const lo_lm* h, double x7[7], double* last_step_norm, double* cost, int32_t* termination, int32_t* recorded);
 
+/* ---- the same, device-resident and with the collectives inside the library (C++ / C callers; one process per GPU) ----
+ * lo_sharded holds this rank's shard (a lo_grid with lo_grid_set_shard applied), an NCCL communicator and the control
+ * block of the solve. lo_sharded_align is CloudMatcher::align (src/cloud_matcher.cpp:105-178) over the union of all
+ * ranks' shards; every rank calls it with the same queries and guess and receives the same pose. Per outer iteration:
+ * search -> ncclAllReduce(MIN, u64[m]) -> evaluate -> one kernel that sums, exchanges the 32 doubles with the peers
+ * through NVLink peer memory and runs the LM step (LO_SHARDED_SUM=nccl: ncclAllReduce(SUM, f64[32]) instead); the host
+ * synchronises once per align in the usual case. NCCL is bound at run time (libnccl.so.2, LO_B200_NCCL_LIB overrides),
+ * and not at all for world = 1. */
+#define LO_SHARDED_ID_BYTES 128
+typedef struct lo_sharded lo_sharded;
+typedef struct lo_sharded_info {
+    int32_t rank, world;
+    int32_t fused_sum;        /* 1: exchange 2 runs inside the step kernel over peer memory; 0: ncclAllReduce */
+    int32_t nccl_version;     /* ncclGetVersion, 0 for world = 1 */
+    uint64_t min_allreduces, sum_allreduces, host_syncs;   /* since creation */
+    uint64_t evaluations;     /* cost / Jacobian evaluations of the last align */
+} lo_sharded_info;
+/* rank 0 makes the id (ncclGetUniqueId) and ships it to the other ranks by whatever channel the job has */
+int lo_sharded_unique_id(uint8_t id[LO_SHARDED_ID_BYTES]);
+/* collective over all ranks; id may be NULL for world = 1. VoxelGrid(voxel_size, max_points) semantics for the shard. */
+int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYTES], int rank, int world, float voxel_size, size_t max_points,
+                      size_t capacity_hint, lo_sharded** out);
+void lo_sharded_destroy(lo_sharded* s);
+/* this rank's shard: lo_grid_add_cloud(_dev) with the replicated update cloud keeps only the voxels this rank owns */
+lo_grid* lo_sharded_grid(lo_sharded* s);
+int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out);
+int lo_sharded_align(lo_sharded* s, const float* xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
+                     lo_align_stats* stats /* nullable */);
+int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
+                         lo_align_stats* stats /* nullable */);
+
 /* ---- CloudTransformer / utils (src/utils) ------------------------------------------------------ */
 /* pointTimeNormalize (point_time_normalize.h:14-39) followed by transformNonRigid
  * (cloud_transform.h:15-40) with (start7, end7); out may alias in. */

@@ -47,6 +47,11 @@ class Params(C.Structure):
                 ("angular_divergence_threshold", C.c_float)]
 
 
+class ShardedInfo(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("fused_sum", C.c_int32), ("nccl_version", C.c_int32),
+                ("min_allreduces", C.c_uint64), ("sum_allreduces", C.c_uint64), ("host_syncs", C.c_uint64), ("evaluations", C.c_uint64)]
+
+
 class ScanStats(C.Structure):
     _fields_ = [("n_points", C.c_uint32), ("n_planar", C.c_uint32), ("n_update", C.c_uint32), ("n_query", C.c_uint32),
                 ("outer_iterations", C.c_int32), ("unstable", C.c_int32), ("keyframe_voxels", C.c_uint32),
@@ -73,6 +78,10 @@ SIGNATURES = {
     "lo_grid_set_shard": (_i, [_vp, C.c_uint32, C.c_uint32]),
     "lo_shard_search_dev": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]),
     "lo_shard_evaluate_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
+    "lo_sharded_unique_id": (_i, [_vp]),
+    "lo_sharded_create": (_i, [_vp, _vp, _i, _i, _fl, _sz, _sz, C.POINTER(_vp)]), "lo_sharded_destroy": (None, [_vp]),
+    "lo_sharded_grid": (_vp, [_vp]), "lo_sharded_info_get": (_i, [_vp, _vp]),
+    "lo_sharded_align": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]), "lo_sharded_align_dev": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]),
     "lo_lm_create": (_vp, []), "lo_lm_destroy": (None, [_vp]), "lo_lm_begin": (_i, [_vp, _vp, _vp, _vp]),
     "lo_lm_propose": (_i, [_vp, _vp]), "lo_lm_update": (_i, [_vp, _vp]), "lo_lm_result": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "lo_deskew": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]),
@@ -302,6 +311,55 @@ class CloudMatcher:
         stats = AlignStats()
         _check(keyframe.lib.lo_align(keyframe.h, _p(cloud), len(cloud), _p(_pose7(position_guess7)), _p(out), C.byref(stats)))
         return (out, stats) if with_stats else out
+
+
+def sharded_unique_id():
+    """ncclGetUniqueId through the library (rank 0 calls it and ships the 128 bytes to the other ranks)."""
+    out = np.zeros(128, np.uint8)
+    _check(load_library().lo_sharded_unique_id(_p(out)))
+    return out
+
+
+class ShardedCloudMatcher:
+    """CloudMatcher::align over a key-frame map sharded by voxel-hash range, one process per GPU (lo_sharded_*): the
+    collectives and the LM run inside the library, the host only enqueues."""
+
+    def __init__(self, ctx, unique_id, rank, world, voxel_size=0.2, max_points=20, capacity_hint=0):
+        self.ctx, self.lib = ctx, ctx.lib
+        h = C.c_void_p()
+        uid = np.ascontiguousarray(unique_id, np.uint8) if unique_id is not None else None
+        _check(self.lib.lo_sharded_create(ctx.h, _p(uid), rank, world, voxel_size, max_points, capacity_hint, C.byref(h)))
+        self.h = h
+        self.grid = VoxelGrid.__new__(VoxelGrid)          # borrowed view of the rank's shard (owned by lo_sharded)
+        self.grid.ctx, self.grid.lib, self.grid.h = ctx, ctx.lib, C.c_void_p(self.lib.lo_sharded_grid(h))
+        self.grid.close = lambda: None
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.grid.h = None
+            self.lib.lo_sharded_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def info(self):
+        out = ShardedInfo()
+        _check(self.lib.lo_sharded_info_get(self.h, C.byref(out)))
+        return out
+
+    def align(self, planar_cloud, position_guess7, max_dist=0.3, with_stats=False):
+        cloud = np.ascontiguousarray(planar_cloud, dtype=XYZ)
+        out = np.empty(7, np.float32)
+        stats = AlignStats()
+        _check(self.lib.lo_sharded_align(self.h, _p(cloud), len(cloud), _p(_pose7(position_guess7)), max_dist, _p(out), C.byref(stats)))
+        return (out, stats) if with_stats else out
+
+    def alignDevice(self, device_ptr, m, position_guess7, max_dist=0.3):
+        out = np.empty(7, np.float32)
+        stats = AlignStats()
+        _check(self.lib.lo_sharded_align_dev(self.h, C.c_void_p(device_ptr), m, _p(_pose7(position_guess7)), max_dist, _p(out), C.byref(stats)))
+        return out, stats
 
 
 class LidarOdometry:

@@ -7,10 +7,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "liblo_b200.so")
 REPLAY = os.path.join(HERE, "lo_replay")   # headless driver (apps/lo_replay.cpp): host C++ over the C ABI
-SOURCES = ["lo_api.cu", "lo_grid.cu", "lo_robin.cu", "lo_match.cu", "lo_points.cu", "lo_planefit.cu", "lo_odometry.cu", "lo_pipeline.cu"]
+SOURCES = ["lo_api.cu", "lo_grid.cu", "lo_robin.cu", "lo_match.cu", "lo_points.cu", "lo_planefit.cu", "lo_odometry.cu", "lo_pipeline.cu", "lo_sharded.cu"]
 # -fmad=false: no FMA contraction, the reference is unfused x86-64 arithmetic (DESIGN.md "numerics")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
-              "--shared", "-Xcompiler", "-fPIC,-O3,-ffp-contract=off", "-cudart", "shared"]
+              "--shared", "-Xcompiler", "-fPIC,-O3,-ffp-contract=off", "-cudart", "shared", "-ldl"]
 
 
 def needs_build():

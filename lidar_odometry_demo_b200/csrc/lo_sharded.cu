@@ -1,0 +1,516 @@
+// CloudMatcher::align (src/cloud_matcher.cpp:105-178) against a key-frame map sharded by voxel-hash range over several
+// GPUs (BASELINE.json config 4), with the whole solve resident on the devices: one process per GPU, the
+// host only enqueues.
+//
+// Per outer iteration every rank runs, on its context's stream:
+//   search      27-neighbour search of the replicated queries in ITS voxels at the current pose -> packed (d2, probe, slot)
+//   exchange 1  ncclAllReduce(MIN, u64[m]) over NVLink: the globally nearest stored point of every query, with
+//               VoxelGrid::getCorrespondence's first-strict-minimum tie-break (voxel_grid.h:175-190) in the low word
+//   evaluate    the owner of each winner adds its residual / Jacobian terms (PointToPlaneErrorAnalytic + Huber corrector)
+//   step        ONE single-block kernel: fixed-order sum of the per-block partials -> 32 doubles, exchange 2 (all-to-all
+//               of those 32 doubles through peer memory: every rank stores its sums and then a sequence flag into a
+//               mailbox on each peer, waits for the peers' flags in its own mailbox and adds the contributions in rank
+//               order, so all ranks hold bit-identical normal equations), then ceres::Solve's trust-region step logic
+//               (lo_lm.cuh) redundantly on every rank: next candidate, or the end of the solve with the float round trip
+//               of the pose and the outer stop rule (cloud_matcher.cpp:161-172).
+//   up to 4 x (evaluate at the candidate -> step), predicated on the control block: once the solve or the align has
+//   ended the remaining kernels of the fixed schedule return at once, on every rank alike.
+// The host enqueues five outer iterations (the stop rule needs outer > 3) and then reads the `done` word once per
+// further iteration: one synchronisation per align in the usual case, against 18 with a host-side LM.
+// LO_SHARDED_SUM=nccl (or peer memory that cannot be mapped) replaces the mailbox exchange by ncclAllReduce(SUM, f64[32]).
+//
+// NCCL is bound at run time (dlopen of libnccl.so.2: the copy already loaded by the process, e.g. torch's, else the
+// system's), so liblo_b200.so itself has no NCCL dependency and single-GPU users never load it.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "lo_shard.cuh"
+
+namespace lo {
+
+constexpr int kMaxShardWorld = 16;
+
+struct ShardMail {          // one sender's contribution to one exchange
+    double v[32];
+    uint32_t flag;          // sequence number of the exchange the values belong to
+    uint32_t pad[15];
+};
+struct ShardMailbox {       // lives on every rank; peers write into it through their mapping of this allocation
+    ShardMail slot[2][kMaxShardWorld];
+};
+
+struct ShardPeers {
+    ShardMailbox* box[kMaxShardWorld];   // box[r] = rank r's mailbox as seen from this device (own one included)
+    uint32_t rank, world;
+};
+
+struct ShardCtl {
+    LmState lm;
+    EvalPoint ep;           // evaluation point of the next evaluate pass
+    QueryTransform tf;      // of the current float pose
+    double prior_b[3];
+    double x0[7];
+    float pose[7];
+    float out_pose[7];
+    uint32_t done, active, outer, lm_total;
+    uint32_t seq;           // exchanges performed so far
+    uint32_t error;         // 1: a peer did not arrive
+    uint32_t evaluations;
+    uint32_t pad;
+    lo_align_stats stats;
+};
+
+__device__ inline void shard_prepare_outer(ShardCtl* c) {
+    Pose pf;
+    pf.t[0] = c->pose[0]; pf.t[1] = c->pose[1]; pf.t[2] = c->pose[2];
+    pf.w = c->pose[3]; pf.x = c->pose[4]; pf.y = c->pose[5]; pf.z = c->pose[6];
+    c->tf = make_query_transform(pf);
+    const double x0[7] = {pf.w, pf.x, pf.y, pf.z, pf.t[0], pf.t[1], pf.t[2]};   // cloud_matcher.cpp:122-131
+    for (int k = 0; k < 7; k++) c->x0[k] = x0[k];
+    c->ep = make_eval_point(x0);
+}
+
+__global__ void shard_ctl_init_kernel(ShardCtl* c, const float* __restrict__ guess7) {
+    for (int k = 0; k < 7; k++) c->pose[k] = guess7[k];
+    for (int k = 0; k < 3; k++) c->prior_b[k] = static_cast<double>(guess7[k]);   // NormalPrior mean, cloud_matcher.cpp:153
+    c->done = 0;
+    c->active = 0;
+    c->outer = 0;
+    c->lm_total = 0;
+    c->evaluations = 0;
+    memset(&c->stats, 0, sizeof(c->stats));
+    shard_prepare_outer(c);
+}
+
+__global__ void __launch_bounds__(kShardThreads) shard_search_ctl_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+                                                                          const ShardCtl* __restrict__ c, float max_d2, int tiled,
+                                                                          unsigned long long* __restrict__ packed, float4* __restrict__ hit) {
+    if (c->done) return;
+    const QueryTransform tf = c->tf;
+    if (tiled) shard_search_tile_body(g, queries, m, tf, max_d2, packed, hit);
+    else shard_search_body(g, queries, m, tf, max_d2, packed, hit);
+}
+
+// phase 0: evaluation at x0 right after the search; phase 1: evaluation at an LM candidate (only while the solve is active)
+__global__ void __launch_bounds__(kShardThreads) shard_evaluate_ctl_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+                                                                            const ShardCtl* __restrict__ c, int phase,
+                                                                            const unsigned long long* __restrict__ local,
+                                                                            const unsigned long long* __restrict__ global,
+                                                                            const float4* __restrict__ hit, double* __restrict__ partials) {
+    if (c->done || (phase == 1 && !c->active)) return;
+    const EvalPoint ep = c->ep;
+    shard_evaluate_body(g, queries, m, ep, local, global, hit, partials);
+}
+
+// end of one ceres::Solve: float round trip of the pose (cloud_matcher.cpp:161-167), outer stop rule (:169), and either
+// the final normalisation (:175) or the set-up of the next outer iteration
+__device__ inline void shard_finish_outer(ShardCtl* c) {
+    const LmState& lm = c->lm;
+    c->pose[3] = static_cast<float>(lm.x[0]); c->pose[4] = static_cast<float>(lm.x[1]);
+    c->pose[5] = static_cast<float>(lm.x[2]); c->pose[6] = static_cast<float>(lm.x[3]);
+    c->pose[0] = static_cast<float>(lm.x[4]); c->pose[1] = static_cast<float>(lm.x[5]); c->pose[2] = static_cast<float>(lm.x[6]);
+    c->lm_total += lm.recorded;
+    const uint32_t outer = c->outer;
+    for (int k = 0; k < 7; k++) c->stats.pose_log[outer][k] = c->pose[k];
+    c->stats.outer_iterations = static_cast<int32_t>(outer + 1);
+    c->stats.lm_iterations = static_cast<int32_t>(c->lm_total);
+    c->stats.termination = lm.termination;
+    c->stats.final_cost = lm.x_cost;
+    c->stats.last_step_norm = lm.last_step_norm;
+    c->outer = outer + 1;
+    if ((lm.last_step_norm < 1e-4 && outer > 3) || outer + 1 >= 35) {
+        const float w = c->pose[3], x = c->pose[4], y = c->pose[5], z = c->pose[6];
+        const float nrm = sqrtf((x * x + z * z) + (y * y + w * w));
+        c->out_pose[0] = c->pose[0]; c->out_pose[1] = c->pose[1]; c->out_pose[2] = c->pose[2];
+        c->out_pose[3] = w / nrm; c->out_pose[4] = x / nrm; c->out_pose[5] = y / nrm; c->out_pose[6] = z / nrm;
+        c->done = 1;
+    } else {
+        shard_prepare_outer(c);
+    }
+}
+
+// sum of the partials + exchange 2 + LM step logic, one block. kStepLocal: the sums in `partials` are already global
+// (one shard, or ncclAllReduce ran before this kernel).
+enum { kStepLocal = 0, kStepExchange = 1, kStepSumOnly = 2 };
+__global__ void __launch_bounds__(256) shard_step_kernel(const double* __restrict__ partials, int nblocks, ShardCtl* c, ShardPeers peers, int exchange,
+                                                         int phase, long long timeout_cycles, double* __restrict__ sums_out) {
+    __shared__ double total[32];
+    __shared__ double scratch[(256 / 32) * kRow];
+    __shared__ uint32_t seq_s;
+    __shared__ int late_s;
+    if (c->done || (phase == 1 && !c->active)) return;   // identical on every rank: nobody waits for a rank that skips
+    reduce_partials(partials, nblocks, scratch, total);
+    if (threadIdx.x >= kAcc && threadIdx.x < 32) total[threadIdx.x] = 0.0;
+    __syncthreads();
+    if (exchange == kStepSumOnly) {   // first half of the NCCL variant: this rank's sums for ncclAllReduce
+        if (threadIdx.x < 32) sums_out[threadIdx.x] = total[threadIdx.x];
+        return;
+    }
+    if (exchange == kStepExchange && peers.world > 1) {
+        if (threadIdx.x == 0) {
+            seq_s = c->seq + 1;
+            c->seq = seq_s;
+            late_s = 0;
+        }
+        __syncthreads();
+        const uint32_t seq = seq_s, slot = seq & 1u, me = peers.rank;
+        // my 32 sums into every peer's mailbox (one thread per value and peer), then the flags
+        for (uint32_t e = threadIdx.x; e < 32 * peers.world; e += blockDim.x) {
+            const uint32_t r = e >> 5, k = e & 31u;
+            if (r != me) peers.box[r]->slot[slot][me].v[k] = total[k];
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x < peers.world && threadIdx.x != me) {
+            *reinterpret_cast<volatile uint32_t*>(&peers.box[threadIdx.x]->slot[slot][me].flag) = seq;
+            // wait for that peer's contribution to arrive in MY mailbox
+            const volatile uint32_t* flag = &peers.box[me]->slot[slot][threadIdx.x].flag;
+            const long long t0 = clock64();
+            while (*flag != seq) {
+                if (clock64() - t0 > timeout_cycles) {
+                    late_s = 1;
+                    break;
+                }
+            }
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (late_s) {   // a peer is gone: stop this rank's schedule instead of hanging the stream
+            if (threadIdx.x == 0) {
+                c->error = 1;
+                c->done = 1;
+            }
+            return;
+        }
+        if (threadIdx.x < 32) {   // contributions in rank order: the same sum, bit for bit, on every rank
+            double v = 0.0;
+            for (uint32_t r = 0; r < peers.world; r++)
+                v += (r == me) ? total[threadIdx.x] : *reinterpret_cast<const volatile double*>(&peers.box[me]->slot[slot][r].v[threadIdx.x]);
+            total[threadIdx.x] = v;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x != 0) return;
+    c->evaluations++;
+    bool cont;
+    if (phase == 0) {
+        add_prior(total, c->x0 + 4, c->prior_b);
+        cont = lm_begin(c->lm, c->x0, total);
+        c->stats.pairs_log[c->outer] = static_cast<int32_t>(total[28] + 0.5);
+        c->stats.valid_pairs = static_cast<int32_t>(total[28] + 0.5);
+    } else {
+        add_prior(total, c->lm.cand + 4, c->prior_b);
+        cont = lm_update(c->lm, total);
+    }
+    const bool need_eval = cont && lm_propose(c->lm);
+    if (need_eval) {
+        c->ep = make_eval_point(c->lm.cand);
+        c->active = 1;
+    } else {
+        c->active = 0;
+        shard_finish_outer(c);
+    }
+}
+
+// ---- NCCL, bound at run time ---------------------------------------------------------------------------------
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetVersion)(int*) = nullptr;
+};
+
+static NcclApi* nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api.lib ? &api : nullptr;
+    tried = true;
+    const char* names[] = {getenv("LO_B200_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+        if (!n || !*n) continue;
+        api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (api.lib) break;
+    }
+    if (!api.lib) {
+        set_error("NCCL could not be loaded (libnccl.so.2): %s", dlerror());
+        return nullptr;
+    }
+    bool ok = true;
+    auto sym = [&](const char* name) {
+        void* p = dlsym(api.lib, name);
+        if (!p) ok = false;
+        return p;
+    };
+    api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+    api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+    api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+    api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+    api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+    api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+    api.GetVersion = reinterpret_cast<decltype(api.GetVersion)>(sym("ncclGetVersion"));
+    if (!ok) {
+        set_error("libnccl.so.2 lacks an expected symbol");
+        dlclose(api.lib);
+        api.lib = nullptr;
+        return nullptr;
+    }
+    return &api;
+}
+
+#define LO_NCCL(api, expr)                                                                              \
+    do {                                                                                                \
+        ncclResult_t _r = (expr);                                                                       \
+        if (_r != ncclSuccess) {                                                                        \
+            lo::set_error("%s failed: %s (%s:%d)", #expr, (api)->GetErrorString(_r), __FILE__, __LINE__); \
+            return LO_E_CUDA;                                                                           \
+        }                                                                                               \
+    } while (0)
+
+}  // namespace lo
+
+using namespace lo;
+
+struct lo_sharded {
+    lo_ctx* ctx = nullptr;
+    lo_grid* grid = nullptr;
+    int rank = 0, world = 1;
+    NcclApi* api = nullptr;
+    ncclComm_t comm = nullptr;
+    ShardCtl* d_ctl = nullptr;
+    ShardCtl* h_ctl = nullptr;          // pinned read-back copy
+    ShardMailbox* d_box = nullptr;      // this rank's mailbox
+    ShardPeers peers;
+    void* peer_mapped[kMaxShardWorld] = {nullptr};
+    bool fused_sum = false;             // exchange 2 through peer memory inside shard_step_kernel
+    DevBuf queries, local, global, hit, partials, acc32, guess;
+    long long timeout_cycles = 19000000000LL;   // ~10 s of SM clocks (LO_SHARDED_TIMEOUT_MS)
+    lo_sharded_info info;
+};
+
+static void sharded_release(lo_sharded* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    for (int r = 0; r < s->world && r < kMaxShardWorld; r++)
+        if (s->peer_mapped[r]) cudaIpcCloseMemHandle(s->peer_mapped[r]);
+    if (s->comm && s->api) s->api->CommDestroy(s->comm);
+    if (s->grid) lo_grid_destroy(s->grid);
+    if (s->d_ctl) cudaFree(s->d_ctl);
+    if (s->h_ctl) cudaFreeHost(s->h_ctl);
+    if (s->d_box) cudaFree(s->d_box);
+    for (DevBuf* b : {&s->queries, &s->local, &s->global, &s->hit, &s->partials, &s->acc32, &s->guess}) b->release();
+    delete s;
+}
+
+extern "C" int lo_sharded_unique_id(uint8_t id[LO_SHARDED_ID_BYTES]) {
+    if (!id) return LO_E_ARG;
+    static_assert(sizeof(ncclUniqueId) == LO_SHARDED_ID_BYTES, "ncclUniqueId is 128 bytes");
+    NcclApi* api = nccl_api();
+    if (!api) return LO_E_CUDA;
+    ncclUniqueId u;
+    LO_NCCL(api, api->GetUniqueId(&u));
+    std::memcpy(id, &u, sizeof(u));
+    return LO_OK;
+}
+
+// map every peer's mailbox; any failure (no peer access, IPC not permitted) leaves the NCCL sum in place
+static bool sharded_map_peers(lo_sharded* s) {
+    lo_ctx* ctx = s->ctx;
+    cudaIpcMemHandle_t mine;
+    if (cudaIpcGetMemHandle(&mine, s->d_box) != cudaSuccess) return false;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    DevBuf hs;
+    if (hs.ensure(64 * (s->world + 1)) != LO_OK) return false;
+    char* d_all = hs.as<char>();
+    char* d_mine = d_all + 64 * s->world;
+    bool ok = cudaMemcpyAsync(d_mine, &mine, 64, cudaMemcpyHostToDevice, ctx->stream) == cudaSuccess &&
+              s->api->AllGather(d_mine, d_all, 64, ncclChar, s->comm, ctx->stream) == ncclSuccess;
+    std::vector<cudaIpcMemHandle_t> all(s->world);
+    ok = ok && cudaMemcpyAsync(all.data(), d_all, 64 * s->world, cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess &&
+         cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+    hs.release();
+    int mapped_ok = ok ? 1 : 0;
+    for (int r = 0; r < s->world && mapped_ok; r++) {
+        if (r == s->rank) {
+            s->peers.box[r] = s->d_box;
+            continue;
+        }
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            mapped_ok = 0;
+            break;
+        }
+        s->peer_mapped[r] = p;
+        s->peers.box[r] = static_cast<ShardMailbox*>(p);
+    }
+    cudaGetLastError();   // a failed IPC call must not poison later launches
+    return mapped_ok == 1;
+}
+
+extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYTES], int rank, int world, float voxel_size, size_t max_points,
+                                 size_t capacity_hint, lo_sharded** out) {
+    if (!ctx || !out || world < 1 || world > kMaxShardWorld || rank < 0 || rank >= world || (world > 1 && !id)) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    lo_sharded* s = new lo_sharded();
+    s->ctx = ctx;
+    s->rank = rank;
+    s->world = world;
+    std::memset(&s->peers, 0, sizeof(s->peers));
+    s->peers.rank = static_cast<uint32_t>(rank);
+    s->peers.world = static_cast<uint32_t>(world);
+    std::memset(&s->info, 0, sizeof(s->info));
+    auto fail = [&](int code) {
+        sharded_release(s);
+        return code;
+    };
+    int st = lo_grid_create(ctx, voxel_size, max_points, capacity_hint, &s->grid);
+    if (st == LO_OK) st = lo_grid_set_shard(s->grid, static_cast<uint32_t>(rank), static_cast<uint32_t>(world));
+    if (st != LO_OK) return fail(st);
+    if (cudaMalloc(&s->d_ctl, sizeof(ShardCtl)) != cudaSuccess || cudaMallocHost(&s->h_ctl, sizeof(ShardCtl)) != cudaSuccess ||
+        cudaMalloc(&s->d_box, sizeof(ShardMailbox)) != cudaSuccess || cudaMemsetAsync(s->d_ctl, 0, sizeof(ShardCtl), ctx->stream) != cudaSuccess ||
+        cudaMemsetAsync(s->d_box, 0, sizeof(ShardMailbox), ctx->stream) != cudaSuccess || s->acc32.ensure(32 * sizeof(double)) != LO_OK ||
+        s->guess.ensure(8 * sizeof(float)) != LO_OK || cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+        set_error("lo_sharded_create: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return fail(LO_E_CUDA);
+    }
+    s->peers.box[rank] = s->d_box;
+    if (world > 1) {
+        s->api = nccl_api();
+        if (!s->api) return fail(LO_E_CUDA);
+        ncclUniqueId u;
+        std::memcpy(&u, id, sizeof(u));
+        ncclResult_t r = s->api->CommInitRank(&s->comm, world, u, rank);
+        if (r != ncclSuccess) {
+            set_error("ncclCommInitRank failed: %s", s->api->GetErrorString(r));
+            s->comm = nullptr;
+            return fail(LO_E_CUDA);
+        }
+        const char* mode = getenv("LO_SHARDED_SUM");
+        const bool want_fused = !(mode && mode[0] == 'n');
+        // every rank maps (the all-gather of the handles is a collective), then all must agree, or the ranks would mix
+        // the two exchange protocols: MIN over "I can and want to"
+        const bool mapped = sharded_map_peers(s);
+        int both = (want_fused && mapped) ? 1 : 0;
+        int* d_flag = s->acc32.as<int>();
+        if (cudaMemcpyAsync(d_flag, &both, sizeof(int), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+            s->api->AllReduce(d_flag, d_flag, 1, ncclInt, ncclMin, s->comm, ctx->stream) != ncclSuccess ||
+            cudaMemcpyAsync(&both, d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+            cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+            set_error("lo_sharded_create: the ranks could not agree on the exchange protocol");
+            return fail(LO_E_CUDA);
+        }
+        s->fused_sum = both == 1;
+        int version = 0;
+        s->api->GetVersion(&version);
+        s->info.nccl_version = version;
+    }
+    const char* to = getenv("LO_SHARDED_TIMEOUT_MS");
+    if (to && atof(to) > 0) s->timeout_cycles = static_cast<long long>(atof(to) * 1.9e6);
+    s->info.rank = rank;
+    s->info.world = world;
+    s->info.fused_sum = s->fused_sum ? 1 : 0;
+    *out = s;
+    return LO_OK;
+}
+
+extern "C" void lo_sharded_destroy(lo_sharded* s) { sharded_release(s); }
+
+extern "C" lo_grid* lo_sharded_grid(lo_sharded* s) { return s ? s->grid : nullptr; }
+
+extern "C" int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out) {
+    if (!s || !out) return LO_E_ARG;
+    *out = s->info;
+    return LO_OK;
+}
+
+static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max_d2) {
+    lo_ctx* ctx = s->ctx;
+    lo_grid* g = s->grid;
+    const GridView v = g->view();
+    unsigned long long* local = s->local.as<unsigned long long>();
+    unsigned long long* global = s->world > 1 ? s->global.as<unsigned long long>() : local;
+    float4* hit = s->hit.as<float4>();
+    const int tiled = g->width <= kTileMaxWidth ? 1 : 0;
+    const int sblocks = tiled ? std::max(1, std::min<int>(ctx->sm_count * 4, static_cast<int>((m + kShardThreads - 1) / kShardThreads)))
+                              : std::max(1, std::min<int>(ctx->sm_count * 8, static_cast<int>((static_cast<size_t>(m) * 32 + kShardThreads - 1) / kShardThreads)));
+    const int eblocks = std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
+    double* partials = s->partials.as<double>();
+    double* acc32 = s->acc32.as<double>();
+    shard_search_ctl_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit);
+    LO_LAUNCHED(ctx);
+    if (s->world > 1 && m) {
+        LO_NCCL(s->api, s->api->AllReduce(local, global, m, ncclUint64, ncclMin, s->comm, ctx->stream));   // exchange 1
+        s->info.min_allreduces++;
+    }
+    const int exchange = (s->world > 1 && m) ? kStepExchange : kStepLocal;   // without queries every rank's sums are zero
+    for (int phase = 0; phase < 5; phase++) {   // x0, then at most 4 LM candidates (max_num_iterations = 4, cloud_matcher.cpp:111)
+        const int ph = phase ? 1 : 0;
+        shard_evaluate_ctl_kernel<<<eblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, ph, local, global, hit, partials);
+        LO_LAUNCHED(ctx);
+        if (exchange == kStepExchange && !s->fused_sum) {
+            // NCCL variant: local sums -> acc32, all-reduce in place, then the step logic on the global sums
+            shard_step_kernel<<<1, 256, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, kStepSumOnly, ph, s->timeout_cycles, acc32);
+            LO_LAUNCHED(ctx);
+            LO_NCCL(s->api, s->api->AllReduce(acc32, acc32, 32, ncclDouble, ncclSum, s->comm, ctx->stream));   // exchange 2
+            s->info.sum_allreduces++;
+            shard_step_kernel<<<1, 256, 0, ctx->stream>>>(acc32, 1, s->d_ctl, s->peers, kStepLocal, ph, s->timeout_cycles, nullptr);
+        } else {
+            shard_step_kernel<<<1, 256, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, exchange, ph, s->timeout_cycles, nullptr);
+        }
+        LO_LAUNCHED(ctx);
+    }
+    return LO_OK;
+}
+
+extern "C" int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
+                                    lo_align_stats* stats) {
+    if (!s || !guess7 || !out7 || (!d_xyz16 && m) || m > 0x7FFFFFFFu) return LO_E_ARG;
+    lo_ctx* ctx = s->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const uint32_t mm = static_cast<uint32_t>(m);
+    const size_t mr = std::max<size_t>(m, 1);
+    LO_TRY(s->local.ensure(mr * 8));
+    if (s->world > 1) LO_TRY(s->global.ensure(mr * 8));
+    LO_TRY(s->hit.ensure(mr * 16));
+    LO_TRY(s->partials.ensure(static_cast<size_t>(ctx->sm_count) * 2 * 32 * sizeof(double)));
+    LO_CUDA(cudaMemcpyAsync(s->guess.p, guess7, 7 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    shard_ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(s->d_ctl, s->guess.as<float>());
+    LO_LAUNCHED(ctx);
+    const PointXYZ* q = static_cast<const PointXYZ*>(d_xyz16);
+    const float max_d2 = max_dist * max_dist;   // voxel_grid.h:215
+    for (int outer = 0; outer < 35; outer++) {
+        LO_TRY(enqueue_outer(s, q, mm, max_d2));
+        if (outer >= 4) {   // the stop rule can first hold after the fifth solve (cloud_matcher.cpp:169)
+            LO_CUDA(cudaMemcpyAsync(s->h_ctl, s->d_ctl, sizeof(ShardCtl), cudaMemcpyDeviceToHost, ctx->stream));
+            LO_CUDA(cudaStreamSynchronize(ctx->stream));
+            s->info.host_syncs++;
+            if (s->h_ctl->done) break;
+        }
+    }
+    if (s->h_ctl->error) {
+        set_error("sharded align: a peer rank did not deliver its sums within the time limit");
+        return LO_E_CUDA;
+    }
+    std::memcpy(out7, s->h_ctl->out_pose, 7 * sizeof(float));
+    if (stats) *stats = s->h_ctl->stats;
+    s->info.evaluations = s->h_ctl->evaluations;
+    return LO_OK;
+}
+
+extern "C" int lo_sharded_align(lo_sharded* s, const float* xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
+                                lo_align_stats* stats) {
+    if (!s || (!xyz16 && m)) return LO_E_ARG;
+    lo_ctx* ctx = s->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    LO_TRY(s->queries.ensure(std::max<size_t>(m, 1) * sizeof(PointXYZ)));
+    if (m) LO_CUDA(cudaMemcpyAsync(s->queries.p, xyz16, m * sizeof(PointXYZ), cudaMemcpyHostToDevice, ctx->stream));
+    return lo_sharded_align_dev(s, s->queries.p, m, guess7, max_dist, out7, stats);
+}

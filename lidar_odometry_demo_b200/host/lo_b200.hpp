@@ -316,6 +316,45 @@ public:
     }
 };
 
+// ---- CloudMatcher over a key-frame map sharded by voxel-hash range, one process per GPU (BASELINE.json config 4) ------
+// Extension (the reference is single-process): every rank constructs one with the same NCCL id (ShardedCloudMatcher::
+// UniqueId() on rank 0, shipped by the job's own channel), adds the replicated key-frame cloud to keyframe() (only the
+// voxels the rank owns are kept) and calls align() with the same queries and guess; every rank receives the same pose.
+class ShardedCloudMatcher {
+public:
+    using UniqueIdBytes = std::vector<uint8_t>;
+    static UniqueIdBytes UniqueId() {
+        UniqueIdBytes id(LO_SHARDED_ID_BYTES);
+        lo::check(lo_sharded_unique_id(id.data()));
+        return id;
+    }
+    ShardedCloudMatcher(const UniqueIdBytes& id, int rank, int world, float voxel_size, size_t max_points, lo::Context& ctx = lo::Context::instance()) {
+        lo::check(lo_sharded_create(ctx.handle(), id.empty() ? nullptr : id.data(), rank, world, voxel_size, max_points, 0, &h_));
+    }
+    ~ShardedCloudMatcher() { lo_sharded_destroy(h_); }
+    ShardedCloudMatcher(const ShardedCloudMatcher&) = delete;
+    ShardedCloudMatcher& operator=(const ShardedCloudMatcher&) = delete;
+
+    // VoxelGrid::addCloud on this rank's shard
+    void addCloud(const pcl::PointCloud<pcl::PointNormal>& cloud) { lo::check(lo_grid_add_cloud(lo_sharded_grid(h_), cloud.points.data(), cloud.points.size(), 1)); }
+    size_t size() const { size_t v = 0, p = 0; lo::check(lo_grid_size(lo_sharded_grid(h_), &v, &p)); return v; }
+    // CloudMatcher::align (src/cloud_matcher.h:13-17) against the union of all shards; findMatchingPairs' 0.3 m gate
+    Pose3D align(const pcl::PointCloud<pcl::PointXYZ>& planar_cloud, const Pose3D& position_guess, float max_distance = 0.3f) const {
+        float guess[7], out[7];
+        position_guess.to7(guess);
+        lo::check(lo_sharded_align(h_, reinterpret_cast<const float*>(planar_cloud.points.data()), planar_cloud.points.size(), guess, max_distance, out, nullptr));
+        return Pose3D::from7(out);
+    }
+    lo_sharded_info info() const {
+        lo_sharded_info i;
+        lo::check(lo_sharded_info_get(h_, &i));
+        return i;
+    }
+
+private:
+    lo_sharded* h_ = nullptr;
+};
+
 // ---- CloudTransformer (src/utils/cloud_transform.h:13-98) and utils:: (point_time_normalize.h, range_filter.h) ---
 class CloudTransformer {
 public:
