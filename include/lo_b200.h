@@ -183,6 +183,9 @@ void lo_sharded_destroy(lo_sharded* s);
 /* this rank's shard: lo_grid_add_cloud(_dev) with the replicated update cloud keeps only the voxels this rank owns */
 lo_grid* lo_sharded_grid(lo_sharded* s);
 int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out);
+/* choose exchange 2 at run time: 1 = inside the step kernel over peer memory, 0 = ncclAllReduce. Every rank must make
+ * the same choice before the same align; LO_E_ARG if the peers' memory could not be mapped at creation. */
+int lo_sharded_set_fused_sum(lo_sharded* s, int enable);
 int lo_sharded_align(lo_sharded* s, const float* xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
                      lo_align_stats* stats /* nullable */);
 int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
@@ -242,7 +245,7 @@ int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, size_t n, con
  * the scan in flight, so the GPU goes from one scan to the next without waiting for the host) and returns at once;
  * lo_odometry_wait blocks until the OLDEST queued scan is done, after which lo_odometry_pose / _stats describe that
  * scan. At most two scans in flight (LO_E_BUSY otherwise); a host buffer must stay untouched until the wait that
- * matches its submit; scans of more than 32 768 points are not accepted here. submit + wait == lo_odometry_process:
+ * matches its submit; scans of more than 524 288 points are not accepted here. submit + wait == lo_odometry_process:
  * same poses, same key frame. */
 int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n);
 int lo_odometry_submit_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);

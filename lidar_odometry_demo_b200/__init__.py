@@ -81,6 +81,7 @@ SIGNATURES = {
     "lo_sharded_unique_id": (_i, [_vp]),
     "lo_sharded_create": (_i, [_vp, _vp, _i, _i, _fl, _sz, _sz, C.POINTER(_vp)]), "lo_sharded_destroy": (None, [_vp]),
     "lo_sharded_grid": (_vp, [_vp]), "lo_sharded_info_get": (_i, [_vp, _vp]),
+    "lo_sharded_set_fused_sum": (_i, [_vp, _i]),
     "lo_sharded_align": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]), "lo_sharded_align_dev": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]),
     "lo_lm_create": (_vp, []), "lo_lm_destroy": (None, [_vp]), "lo_lm_begin": (_i, [_vp, _vp, _vp, _vp]),
     "lo_lm_propose": (_i, [_vp, _vp]), "lo_lm_update": (_i, [_vp, _vp]), "lo_lm_result": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
@@ -342,6 +343,9 @@ class ShardedCloudMatcher:
 
     def __del__(self):
         self.close()
+
+    def setFusedSum(self, enable):
+        _check(self.lib.lo_sharded_set_fused_sum(self.h, int(bool(enable))))
 
     def info(self):
         out = ShardedInfo()

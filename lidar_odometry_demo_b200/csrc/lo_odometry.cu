@@ -74,6 +74,14 @@ __global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counte
 
 }  // namespace lo
 
+uint32_t lo::fused_max_points() {
+    static const uint32_t v = [] {
+        const char* e = getenv("LO_B200_FUSED_MAX");
+        return e && atoll(e) > 0 ? static_cast<uint32_t>(atoll(e)) : kFusedMaxPoints;
+    }();
+    return v;
+}
+
 using namespace lo;
 
 static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P) {
@@ -244,7 +252,7 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
         set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
         return LO_E_BUSY;
     }
-    if (!staged && nn <= kFusedMaxPoints) {
+    if (!staged && nn <= fused_max_points()) {
         LO_TRY(submit_fused(h, static_cast<const PointXYZIRT*>(d_xyzirt32), nn));
         return wait_oldest(h);
     }
@@ -306,8 +314,8 @@ extern "C" int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, si
 extern "C" int lo_odometry_submit_dev(lo_odometry* h, const void* d_xyzirt32, size_t n) {
     if (!h || (!d_xyzirt32 && n)) return LO_E_ARG;
     LO_CUDA(cudaSetDevice(h->ctx->device));
-    if (n > kFusedMaxPoints) {
-        set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", kFusedMaxPoints);
+    if (n > fused_max_points()) {
+        set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", fused_max_points());
         return LO_E_ARG;
     }
     return submit_fused(h, static_cast<const PointXYZIRT*>(d_xyzirt32), static_cast<uint32_t>(n));
@@ -317,8 +325,8 @@ extern "C" int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n
     if (!h || (!xyzirt32 && n)) return LO_E_ARG;
     lo_ctx* ctx = h->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
-    if (n > kFusedMaxPoints) {
-        set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", kFusedMaxPoints);
+    if (n > fused_max_points()) {
+        set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", fused_max_points());
         return LO_E_ARG;
     }
     if (h->scan_seq - h->wait_seq >= 2) {

@@ -86,7 +86,8 @@ struct lo_odometry {
 namespace lo {
 // lo_pipeline.cu: LidarOdometry::processCloud as one persistent cooperative kernel. Requires n <= kFusedMaxPoints;
 // returns LO_OK after enqueueing the kernel, which also fills the device-side ScanReadback block.
-constexpr uint32_t kFusedMaxPoints = 32768;
+constexpr uint32_t kFusedMaxPoints = 1u << 19;   // 524 288: a 128-beam revolution (262 144 returns) twice over
+uint32_t fused_max_points();   // kFusedMaxPoints, or the developer override LO_B200_FUSED_MAX
 int fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n);
 void fused_release(lo_odometry* h);
 void fused_trace_dump(lo_odometry* h);

@@ -501,18 +501,23 @@ __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNorma
     const uint32_t n = s->n_update;
     if (n == 0) return;
     const uint32_t C = robin_bucket_count(n);
-    const uint32_t shift = robin_bin_shift(C), bins = C >> shift, per = 1u << shift;   // per <= kRobinBins <= blockDim.x
+    const uint32_t shift = robin_bin_shift(C), bins = C >> shift, per = 1u << shift;   // bins <= kRobinBins <= blockDim.x
     for (uint32_t bin = blockIdx.x; bin < bins; bin += gridDim.x) {
-        uint32_t base, bin_total;
-        block_exclusive_scan(threadIdx.x < bin ? b.rb_coarse[threadIdx.x] : 0u, base);
-        const uint32_t c = (bin << shift) + threadIdx.x;
-        const uint32_t v = threadIdx.x < per ? b.rb_hist[c] : 0u;
-        const uint32_t start = base + block_exclusive_scan(v, bin_total);
-        if (threadIdx.x < per) {
-            b.rb_hist[c] = start;    // exclusive start of bucket c
-            b.rb_fill[c] = start;
+        uint32_t run;
+        block_exclusive_scan(threadIdx.x < bin ? b.rb_coarse[threadIdx.x] : 0u, run);   // winners in the bins before this one
+        // the bin's buckets in chunks of blockDim.x (one chunk for a VLP16 scan; 128-beam scans have up to 2048 buckets per bin)
+        for (uint32_t off = 0; off < per; off += blockDim.x) {
+            const uint32_t k = off + threadIdx.x, c = (bin << shift) + k;
+            const uint32_t v = k < per ? b.rb_hist[c] : 0u;
+            uint32_t chunk_total;
+            const uint32_t start = run + block_exclusive_scan(v, chunk_total);
+            if (k < per) {
+                b.rb_hist[c] = start;    // exclusive start of bucket c
+                b.rb_fill[c] = start;
+            }
+            if (bin == bins - 1 && k == per - 1) b.rb_hist[C] = start + v;   // = n
+            run += chunk_total;
         }
-        if (bin == bins - 1 && threadIdx.x == per - 1) b.rb_hist[C] = start + v;   // = n
     }
 }
 
@@ -589,7 +594,10 @@ struct ScanArgs {
     long long* trace;
 };
 
-__global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
+// kTiled: align may use the tile search (scans with more than ~19 k queries); the VLP16-sized instantiation is compiled
+// without it so that its code and register allocation stay what they were tuned to.
+template <bool kTiled>
+__device__ __forceinline__ void scan_body(const ScanArgs& p) {
     cg::grid_group grid = cg::this_grid();
     OdomDev* s = p.s;
     // the key frame is empty: bootstrap scan (cpp:40-44). Read on the device, so the host can queue a scan before the
@@ -654,7 +662,14 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
         a.trace = p.trace;
         a.trace_start = trace_n;
         a.out_pose_block = next_s;
-        align_device(a, grid);
+        // large query sets (a 128-beam scan has ~10^5 queries: more than 8 per warp) take the tile search; a VLP16 scan's
+        // ~6 k queries stay on the per-query search. Same winners either way (lo_tile_search.cuh).
+        if constexpr (kTiled) {
+            extern __shared__ __align__(16) unsigned char tile_scratch[];
+            align_device(a, grid, reinterpret_cast<TileScratch*>(tile_scratch));
+        } else {
+            align_device(a, grid);
+        }
         if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_n = static_cast<int>(p.trace[1000]);
         // every block runs the gate on the (identical) result: no grid-wide hand-over; block 0 stores the state at the end
         if (threadIdx.x == 0) {
@@ -719,6 +734,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) {
 #undef LO_SCAN_TRACE
 }
 
+__global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) { scan_body<false>(p); }
+__global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel_large(ScanArgs p) { scan_body<true>(p); }
+constexpr uint32_t kSmallScanPoints = 32768;   // scans up to this size (a VLP16 revolution is ~30 k) run scan_kernel
+
 }  // namespace lo
 
 using namespace lo;
@@ -735,7 +754,11 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     LO_TRY(h->query.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZ)));
     static int blocks_per_sm = 0;
     if (blocks_per_sm == 0) {
+        int large_per_sm = 0;
+        LO_CUDA(cudaFuncSetAttribute(scan_kernel_large, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kAlignTileScratchBytes)));
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&large_per_sm, scan_kernel_large, kPipeThreads, kAlignTileScratchBytes));
         LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, 0));
+        blocks_per_sm = std::min(blocks_per_sm, large_per_sm);
         if (blocks_per_sm < 1) {
             set_error("the per-scan kernel does not fit on an SM");
             return LO_E_CUDA;
@@ -774,7 +797,11 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
         p.trace = ctx->tmp_d.as<long long>();
     }
     void* kargs[] = {&p};
-    LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream));
+    if (n <= kSmallScanPoints)
+        LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream));
+    else
+        LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel_large), dim3(blocks), dim3(kPipeThreads), kargs,
+                                            kAlignTileScratchBytes, ctx->stream));
     ctx->launches++;
     return LO_OK;
 }

@@ -290,6 +290,7 @@ struct lo_sharded {
     ShardPeers peers;
     void* peer_mapped[kMaxShardWorld] = {nullptr};
     bool fused_sum = false;             // exchange 2 through peer memory inside shard_step_kernel
+    bool peers_mapped = false;          // every rank could map every peer's mailbox
     DevBuf queries, local, global, hit, partials, acc32, guess;
     long long timeout_cycles = 19000000000LL;   // ~10 s of SM clocks (LO_SHARDED_TIMEOUT_MS)
     lo_sharded_info info;
@@ -398,7 +399,7 @@ extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYT
         // every rank maps (the all-gather of the handles is a collective), then all must agree, or the ranks would mix
         // the two exchange protocols: MIN over "I can and want to"
         const bool mapped = sharded_map_peers(s);
-        int both = (want_fused && mapped) ? 1 : 0;
+        int both = mapped ? 1 : 0;
         int* d_flag = s->acc32.as<int>();
         if (cudaMemcpyAsync(d_flag, &both, sizeof(int), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
             s->api->AllReduce(d_flag, d_flag, 1, ncclInt, ncclMin, s->comm, ctx->stream) != ncclSuccess ||
@@ -407,7 +408,8 @@ extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYT
             set_error("lo_sharded_create: the ranks could not agree on the exchange protocol");
             return fail(LO_E_CUDA);
         }
-        s->fused_sum = both == 1;
+        s->peers_mapped = both == 1;
+        s->fused_sum = s->peers_mapped && want_fused;   // LO_SHARDED_SUM is read by every rank of the job alike
         int version = 0;
         s->api->GetVersion(&version);
         s->info.nccl_version = version;
@@ -424,6 +426,17 @@ extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYT
 extern "C" void lo_sharded_destroy(lo_sharded* s) { sharded_release(s); }
 
 extern "C" lo_grid* lo_sharded_grid(lo_sharded* s) { return s ? s->grid : nullptr; }
+
+extern "C" int lo_sharded_set_fused_sum(lo_sharded* s, int enable) {
+    if (!s) return LO_E_ARG;
+    if (enable && s->world > 1 && !s->peers_mapped) {
+        set_error("the peers' mailboxes could not be mapped on this job (no peer access / IPC): the NCCL sum stays in place");
+        return LO_E_ARG;
+    }
+    s->fused_sum = enable && s->world > 1;
+    s->info.fused_sum = s->fused_sum ? 1 : 0;
+    return LO_OK;
+}
 
 extern "C" int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out) {
     if (!s || !out) return LO_E_ARG;

@@ -52,13 +52,17 @@ def test_ragged_rings_and_non_finite_returns(ctx, port, stream12):
 
 
 def test_pipeline_handover_size(ctx, port, stream12):
-    """Scans up to 32 768 points run in the per-scan kernel, larger ones stage by stage: same results on both sides."""
+    """Scans up to 524 288 points run in the per-scan kernel, larger ones stage by stage: same results on both sides. (The
+    scan is a VLP16 revolution repeated: 16 rings of ~34 k columns each.)"""
     scans = stream12[0]
-    base = np.concatenate([scans[0], scans[0][:5000]])
-    assert len(base) > 32769
-    a, b = base[:32768].copy(), base[:32769].copy()
+    base = np.tile(scans[0], 19)
+    limit = 1 << 19
+    assert len(base) > limit + 1
+    a, b = base[:limit].copy(), base[:limit + 1].copy()
+    l0 = ctx.kernel_launches
     (dt, dr), od, oc = run_both(ctx, port, [a, b, a])
     assert dt < 1e-4 and dr < 1e-4
+    assert 10 < ctx.kernel_launches - l0 < 200        # two scans = one launch each (+ table growth), one scan = many
 
 
 def test_stage_by_stage_pipeline_matches_oracle():
@@ -156,7 +160,8 @@ def test_submit_wait_pipeline_equals_process(ctx, stream12):
 
 def test_config3_scan_size(ctx, port):
     """BASELINE.json config 3: 128 beams x 2048 columns (~245 k returns per scan), voxels 0.1 / 0.05 / 0.05 — the largest scans
-    of the contract (they take the stage-by-stage pipeline and the tile search in align): counts and poses as the oracle."""
+    of the contract (per-scan kernel with the tile search in align; bucket bins of the robin order span several chunks): counts
+    and poses as the oracle."""
     import sys
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     from bench_c3 import c3_params, c3_stream

@@ -5,7 +5,9 @@ correspondence keys and an all-reduce(SUM) of the 28 normal-equation sums per ev
 
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
       tools/bench_sharded.py [--points 50000000] [--queries 262144] [--repeat 5]
-Prints one JSON line on rank 0 (device time = max over ranks)."""
+Prints one JSON line on rank 0 (device time = max over ranks): the Python-orchestrated path (per-rank phases + torch.distributed
+collectives + host LM) and, under "native", the device-resident matcher of the library (lo_sharded_*: NCCL MIN exchange, the
+32-double sum through peer memory inside the LM step kernel, and the same with ncclAllReduce for that sum)."""
 import argparse
 import json
 import os
@@ -32,6 +34,12 @@ if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ctx = lo.Context(local)
 shard = sharded.GpuShard(lo, ctx, 0.2, 20, rank, world, capacity_hint=args.points // (6 * world))
+uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+if world > 1:
+    if rank == 0:
+        uid = torch.from_numpy(lo.sharded_unique_id()).cuda()
+    dist.broadcast(uid, 0)
+native = lo.ShardedCloudMatcher(ctx, uid.cpu().numpy() if world > 1 else None, rank, world, 0.2, 20, capacity_hint=args.points // (6 * world))
 
 # the map: planar patches in a 1 km x 1 km x 40 m volume, generated in chunks, identical on every rank
 t0 = time.perf_counter()
@@ -42,6 +50,7 @@ while made < args.points:
     n = min(chunk, args.points - made)
     pn = S.planar_patch_map(n, seed=777 + k, extent=(1000.0, 1000.0, 40.0))
     shard.add_cloud(pn)
+    native.grid.addCloud(pn)
     take = rng.choice(len(pn), max(1, args.queries * n // args.points), replace=False)
     qsel.append(np.stack([pn["x"][take], pn["y"][take], pn["z"][take]], 1))
     made += len(pn)
@@ -75,6 +84,39 @@ for it in range(args.repeat + 1):
     if it > 0:
         times.append(e0.elapsed_time(e1) / 1e3)
     evals = m.evaluations
+# the same align through lo_sharded_align_dev (queries already resident in HBM: shard.q)
+native_out = {}
+modes = (("fused_peer_memory_sum", 1), ("nccl_sum", 0)) if world > 1 else (("one_shard", 0),)
+for name, fused in modes:
+    if world > 1:
+        try:
+            native.setFusedSum(fused)
+        except lo.LoError as e:
+            native_out[name] = {"unavailable": str(e)}
+            continue
+    nt = []
+    for it in range(args.repeat + 1):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        s0 = native.info().host_syncs
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        e0.record(stream)
+        npose, nstats = native.alignDevice(shard.q.data_ptr(), len(queries), guess)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        w1 = time.perf_counter()
+        if it > 0:
+            nt.append((e0.elapsed_time(e1) / 1e3, w1 - w0))
+    tt = torch.tensor([float(np.mean([a for a, _ in nt])), float(np.mean([b for _, b in nt]))], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    info = native.info()
+    native_out[name] = {"align_s": float(tt[0]), "align_wall_s": float(tt[1]), "outer_iterations": int(nstats.outer_iterations),
+                        "evaluations": int(info.evaluations), "host_syncs_per_align": int(info.host_syncs - s0), "final_cost": float(nstats.final_cost),
+                        "pose": [float(v) for v in npose], "pose_equals_python_path": bool(np.array_equal(npose, pose)),
+                        "nccl_version": int(info.nccl_version), "fused_sum": int(info.fused_sum)}
 # phase timings of one search + one evaluation (device, this rank)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
 ev[0].record(stream)
@@ -98,7 +140,7 @@ if rank == 0:
         "n_gpus": world, "align_s": t_align, "outer_iterations": outers, "evaluations": evals,
         "allreduces_per_align": outers + evals, "queries_per_s_through_align": len(queries) * outers / t_align,
         "search_ms_per_pass_max_rank": 1e3 * t_search, "evaluate_ms_per_pass_max_rank": 1e3 * t_eval,
-        "valid_pairs_last": log[-1][0], "final_cost": log[-1][3], "pose": [float(v) for v in pose], "map_build_s": build_s,
+        "native": native_out, "valid_pairs_last": log[-1][0], "final_cost": log[-1][3], "pose": [float(v) for v in pose], "map_build_s": build_s,
         "expected_pose_note": "queries were moved by t=(0.06,-0.05,0.06) + 0.01 deg about z at (500,500,20); align returns the inverse motion"}))
 if world > 1:
     dist.destroy_process_group()
