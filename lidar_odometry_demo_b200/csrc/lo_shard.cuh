@@ -48,7 +48,7 @@ __device__ __forceinline__ void shard_search_tile_body(GridView g, const PointXY
         if (have) q = queries[i];
         float wq[3];
         transform_query(tf, q.x, q.y, q.z, wq);
-        const TileBest b = nn_search_tile_best(g, wq, have, max_d2, lane, ts);
+        const TileBest b = nn_search_tile_best<true>(g, wq, have, max_d2, lane, ts);
         if (have) {
             float4 o = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
             if (b.key != ~0ull) {

@@ -33,6 +33,7 @@
 namespace lo {
 
 constexpr int kMaxShardWorld = 16;
+constexpr int kEvalBlocksPerSm = 4;   // evaluate passes are latency-bound gathers: one or two queries per thread
 
 struct ShardMail {          // one sender's contribution to one exchange
     double v[32];
@@ -454,7 +455,7 @@ static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max
     const int tiled = g->width <= kTileMaxWidth ? 1 : 0;
     const int sblocks = tiled ? std::max(1, std::min<int>(ctx->sm_count * 4, static_cast<int>((m + kShardThreads - 1) / kShardThreads)))
                               : std::max(1, std::min<int>(ctx->sm_count * 8, static_cast<int>((static_cast<size_t>(m) * 32 + kShardThreads - 1) / kShardThreads)));
-    const int eblocks = std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
+    const int eblocks = std::max(1, std::min<int>(ctx->sm_count * kEvalBlocksPerSm, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
     double* partials = s->partials.as<double>();
     double* acc32 = s->acc32.as<double>();
     shard_search_ctl_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit);
@@ -493,7 +494,7 @@ extern "C" int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m
     LO_TRY(s->local.ensure(mr * 8));
     if (s->world > 1) LO_TRY(s->global.ensure(mr * 8));
     LO_TRY(s->hit.ensure(mr * 16));
-    LO_TRY(s->partials.ensure(static_cast<size_t>(ctx->sm_count) * 2 * 32 * sizeof(double)));
+    LO_TRY(s->partials.ensure(static_cast<size_t>(ctx->sm_count) * kEvalBlocksPerSm * 32 * sizeof(double)));
     LO_CUDA(cudaMemcpyAsync(s->guess.p, guess7, 7 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     shard_ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(s->d_ctl, s->guess.as<float>());
     LO_LAUNCHED(ctx);

@@ -113,6 +113,10 @@ struct TileBest {     // per lane: the lane's own query
 };
 
 // `visited` / `occupied` (nullable): this lane's share of the stored points / occupied voxels the tile looked at.
+// kSharded: the grid holds one hash range of a sharded key frame (lo_grid_set_shard). Which rank owns a voxel follows from
+// its indices alone, so look-ups of other ranks' voxels are dropped before they cost a slot load: the look-ups a rank
+// issues shrink with the world size instead of staying at 27 per query.
+template <bool kSharded = false>
 __device__ inline TileBest nn_search_tile_best(const GridView& g, const float wq[3], bool have, float max_d2, int lane, TileScratch* ts,
                                                uint32_t* visited = nullptr, uint32_t* occupied = nullptr) {
     const float vs = g.voxel_size;
@@ -129,6 +133,7 @@ __device__ inline TileBest nn_search_tile_best(const GridView& g, const float wq
     LaneOffset centre;
     centre.dx = centre.dy = centre.dz = 0;
     centre.probing = have;
+    if constexpr (kSharded) centre.probing = have && (g.shard_world <= 1 || shard_owner(ox, oy, oz, g.shard_world) == g.shard_rank);
     uint32_t vid, count;
     probe_resolve(g, probe_issue_at(g, ox, oy, oz, centre), vid, count);
     if (visited) *visited += count;
@@ -159,7 +164,9 @@ __device__ inline TileBest nn_search_tile_best(const GridView& g, const float wq
             const int dx = l / 9 - 1, dy = (l / 3) % 3 - 1, dz = l % 3 - 1;
             const float far2 = (dx < 0 ? m2[0] : (dx > 0 ? p2[0] : 0.f)) + (dy < 0 ? m2[1] : (dy > 0 ? p2[1] : 0.f)) +
                                (dz < 0 ? m2[2] : (dz > 0 ? p2[2] : 0.f));
-            if (!(far2 > bound)) mask |= 1u << l;   // NaN: visit
+            bool visit = !(far2 > bound);   // NaN: visit
+            if constexpr (kSharded) visit = visit && (g.shard_world <= 1 || shard_owner(ox + dx, oy + dy, oz + dz, g.shard_world) == g.shard_rank);
+            if (visit) mask |= 1u << l;
         }
     }
     LO_TILE_STAGE(6);
