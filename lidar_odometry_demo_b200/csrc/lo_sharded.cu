@@ -34,6 +34,7 @@ namespace lo {
 
 constexpr int kMaxShardWorld = 16;
 constexpr int kEvalBlocksPerSm = 4;   // evaluate passes are latency-bound gathers: one or two queries per thread
+constexpr int kStepThreads = 256;     // (512 threads and half the partials measured no better: the sums are L2-resident)
 
 struct ShardMail {          // one sender's contribution to one exchange
     double v[32];
@@ -137,10 +138,10 @@ __device__ inline void shard_finish_outer(ShardCtl* c) {
 // sum of the partials + exchange 2 + LM step logic, one block. kStepLocal: the sums in `partials` are already global
 // (one shard, or ncclAllReduce ran before this kernel).
 enum { kStepLocal = 0, kStepExchange = 1, kStepSumOnly = 2 };
-__global__ void __launch_bounds__(256) shard_step_kernel(const double* __restrict__ partials, int nblocks, ShardCtl* c, ShardPeers peers, int exchange,
+__global__ void __launch_bounds__(kStepThreads) shard_step_kernel(const double* __restrict__ partials, int nblocks, ShardCtl* c, ShardPeers peers, int exchange,
                                                          int phase, long long timeout_cycles, double* __restrict__ sums_out) {
     __shared__ double total[32];
-    __shared__ double scratch[(256 / 32) * kRow];
+    __shared__ double scratch[(kStepThreads / 32) * kRow];
     __shared__ uint32_t seq_s;
     __shared__ int late_s;
     if (c->done || (phase == 1 && !c->active)) return;   // identical on every rank: nobody waits for a rank that skips
@@ -471,13 +472,13 @@ static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max
         LO_LAUNCHED(ctx);
         if (exchange == kStepExchange && !s->fused_sum) {
             // NCCL variant: local sums -> acc32, all-reduce in place, then the step logic on the global sums
-            shard_step_kernel<<<1, 256, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, kStepSumOnly, ph, s->timeout_cycles, acc32);
+            shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, kStepSumOnly, ph, s->timeout_cycles, acc32);
             LO_LAUNCHED(ctx);
             LO_NCCL(s->api, s->api->AllReduce(acc32, acc32, 32, ncclDouble, ncclSum, s->comm, ctx->stream));   // exchange 2
             s->info.sum_allreduces++;
-            shard_step_kernel<<<1, 256, 0, ctx->stream>>>(acc32, 1, s->d_ctl, s->peers, kStepLocal, ph, s->timeout_cycles, nullptr);
+            shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(acc32, 1, s->d_ctl, s->peers, kStepLocal, ph, s->timeout_cycles, nullptr);
         } else {
-            shard_step_kernel<<<1, 256, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, exchange, ph, s->timeout_cycles, nullptr);
+            shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, exchange, ph, s->timeout_cycles, nullptr);
         }
         LO_LAUNCHED(ctx);
     }

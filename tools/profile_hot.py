@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Short driver for `ncu --set full`: a few scans through the pipeline (scan_kernel), one stand-alone align
-(align_kernel) and the fused NN+residual kernels (tile search and exhaustive) on a map much larger than L2.
-Not a benchmark."""
+(align_kernel), the fused NN+residual kernels (tile search and exhaustive) on a map much larger than L2, three 128-beam
+scans of config 3 (scan_kernel_large) and one device-resident sharded align with one shard on the big map
+(shard_search_ctl / shard_evaluate_ctl / shard_step kernels). Not a benchmark."""
 import os
 import sys
 
@@ -47,3 +48,18 @@ for mode in ("tile", "exhaustive"):
     for _ in range(3):
         cost, grad, hess, nv = gb.nnResidual(qq, ident, x, np.zeros(3))
     print("nn_residual", mode, cost, nv, gb.last_candidates / len(qq))
+
+# config 3: 128 beams x 2048 columns through the per-scan kernel's large instantiation
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from bench_c3 import c3_params, c3_stream  # noqa: E402
+od3 = lo.LidarOdometry(ctx, c3_params(lo))
+for s in c3_stream(3):
+    od3.processCloud(s)
+print("config 3", len(s), od3.getCurrentPose(), od3.stats().outer_iterations)
+
+# the device-resident sharded matcher, one shard (no NCCL): same map and queries as the NN kernels above
+m = lo.ShardedCloudMatcher(ctx, None, 0, 1, 0.2, 20, capacity_hint=n_map // 8)
+for i in range(0, len(big), 2_000_000):
+    m.grid.addCloud(big[i:i + 2_000_000])
+pose, st = m.align(qq, ident, with_stats=True)
+print("sharded align (1 shard)", pose, st.outer_iterations, m.info().evaluations)
