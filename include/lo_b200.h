@@ -39,7 +39,7 @@ enum {
     LO_E_CAPACITY = -3,  /* caller buffer too small; the needed count is returned through the size out-param */
     LO_E_RANGE = -4,     /* a voxel index fell outside the supported +-2^20 range */
     LO_E_IO = -5,        /* file could not be read / parsed */
-    LO_E_BUSY = -6       /* lo_odometry_submit: two scans already in flight / scans in flight during a synchronous call */
+    LO_E_BUSY = -6       /* lo_odometry_submit: the queue is full / scans in flight during a synchronous call */
 };
 
 typedef struct lo_ctx lo_ctx;
@@ -244,9 +244,10 @@ int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, size_t n, con
 /* processCloud split in two for recorded streams: lo_odometry_submit queues a scan (its upload and its kernel run behind
  * the scan in flight, so the GPU goes from one scan to the next without waiting for the host) and returns at once;
  * lo_odometry_wait blocks until the OLDEST queued scan is done, after which lo_odometry_pose / _stats describe that
- * scan. At most two scans in flight (LO_E_BUSY otherwise); a host buffer must stay untouched until the wait that
+ * scan. At most LO_ODOMETRY_QUEUE_DEPTH scans in flight (LO_E_BUSY otherwise); a host buffer must stay untouched until the wait that
  * matches its submit; scans of more than 524 288 points are not accepted here. submit + wait == lo_odometry_process:
  * same poses, same key frame. */
+#define LO_ODOMETRY_QUEUE_DEPTH 8
 int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n);
 int lo_odometry_submit_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);
 int lo_odometry_wait(lo_odometry* h);

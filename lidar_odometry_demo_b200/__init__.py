@@ -16,6 +16,7 @@ from .synthetic import PN, XYZ, XYZIRT  # noqa: F401  (wire dtypes)
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "liblo_b200.so")
 
+QUEUE_DEPTH = 8   # LO_ODOMETRY_QUEUE_DEPTH
 LO_OK, LO_E_CUDA, LO_E_ARG, LO_E_CAPACITY, LO_E_RANGE, LO_E_IO, LO_E_BUSY = 0, -1, -2, -3, -4, -5, -6
 
 
@@ -396,7 +397,7 @@ class LidarOdometry:
         _check(self.lib.lo_odometry_process_next(self.h, C.c_void_p(cloud_ptr), n, C.c_void_p(next_ptr) if next_ptr else None, next_n))
 
     def submit(self, host_ptr, n):
-        """Queue a host scan (lo_odometry_submit); at most two in flight."""
+        """Queue a host scan (lo_odometry_submit); at most QUEUE_DEPTH in flight."""
         _check(self.lib.lo_odometry_submit(self.h, C.c_void_p(host_ptr), n))
 
     def submitDevice(self, device_ptr, n):

@@ -149,7 +149,7 @@ static int finish_scan(lo_odometry* h, uint32_t n_points) {
 // checking the stream now and then so that a failed launch cannot hang the caller.
 static int wait_oldest(lo_odometry* h) {
     lo_ctx* ctx = h->ctx;
-    const uint32_t want = h->wait_seq + 1, slot = want & 1u;
+    const uint32_t want = h->wait_seq + 1, slot = want % kQueueDepth;
     const volatile uint32_t* seq = &h->h_readback[slot].seq;
     static const char* wait_mode = getenv("LO_B200_WAIT");   // developer switch: "sync" waits on the stream first
     if (wait_mode && wait_mode[0] == 's') LO_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -168,17 +168,17 @@ static int wait_oldest(lo_odometry* h) {
     const ScanReadback& r = h->h_readback[slot];
     if (!r.bootstrap) h->keyframe->cleaned = true;   // radiusCleanup ran: reference iteration order can no longer be emulated
     const int st = adopt_readback(h, r, h->queued_n[slot]);
-    h->keyframe->h_counters[GC_TICKET] = h->queued_ticket[(h->scan_seq) & 1u];   // tickets: as of the newest scan submitted
+    h->keyframe->h_counters[GC_TICKET] = h->queued_ticket[h->scan_seq % kQueueDepth];   // tickets: as of the newest scan submitted
     return st;
 }
 
 static int submit_fused(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
-    if (h->scan_seq - h->wait_seq >= 2) {
-        set_error("two scans are already in flight: call lo_odometry_wait first");
+    if (h->scan_seq - h->wait_seq >= kQueueDepth) {
+        set_error("%u scans are already in flight: call lo_odometry_wait first", kQueueDepth);
         return LO_E_BUSY;
     }
     LO_TRY(fused_process_enqueue(h, d_scan, n));
-    const uint32_t slot = h->scan_seq & 1u;
+    const uint32_t slot = h->scan_seq % kQueueDepth;
     h->queued_n[slot] = n;
     h->queued_ticket[slot] = h->keyframe->h_counters[GC_TICKET];
     h->pending_points += n;
@@ -206,8 +206,8 @@ extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odome
     LO_CUDA(cudaMalloc(&h->d_state, sizeof(OdomDev)));
     LO_CUDA(cudaMemsetAsync(h->d_state, 0, sizeof(OdomDev), ctx->stream));
     LO_CUDA(cudaMalloc(&h->d_readback, sizeof(ScanReadback)));
-    LO_CUDA(cudaMallocHost(&h->h_readback, 2 * sizeof(ScanReadback)));
-    std::memset(h->h_readback, 0, 2 * sizeof(ScanReadback));
+    LO_CUDA(cudaMallocHost(&h->h_readback, kQueueDepth * sizeof(ScanReadback)));
+    std::memset(h->h_readback, 0, kQueueDepth * sizeof(ScanReadback));
     LO_CUDA(cudaMalloc(&h->d_minmax, 2 * sizeof(uint32_t)));
     const uint32_t minmax_init[2] = {0xFFFFFFFFu, 0u};
     LO_CUDA(cudaMemcpyAsync(h->d_minmax, minmax_init, sizeof(minmax_init), cudaMemcpyHostToDevice, ctx->stream));
@@ -235,7 +235,8 @@ extern "C" void lo_odometry_destroy(lo_odometry* h) {
         cudaStreamDestroy(h->copy_stream);
     }
     if (h->copy_done) cudaEventDestroy(h->copy_done);
-    for (DevBuf* b : {&h->scan, &h->scan_next, &h->scan_q[0], &h->scan_q[1], &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    for (DevBuf* b : {&h->scan, &h->scan_next, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    for (DevBuf& b : h->scan_q) b.release();
     for (cudaEvent_t e : h->scan_q_done)
         if (e) cudaEventDestroy(e);
     delete h;
@@ -329,8 +330,8 @@ extern "C" int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n
         set_error("lo_odometry_submit takes scans of at most %u points; larger ones go through lo_odometry_process", fused_max_points());
         return LO_E_ARG;
     }
-    if (h->scan_seq - h->wait_seq >= 2) {
-        set_error("two scans are already in flight: call lo_odometry_wait first");
+    if (h->scan_seq - h->wait_seq >= kQueueDepth) {
+        set_error("%u scans are already in flight: call lo_odometry_wait first", kQueueDepth);
         return LO_E_BUSY;
     }
     if (!h->copy_stream) {
@@ -339,7 +340,7 @@ extern "C" int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n
     }
     // the slot's device copy was last read by scan (seq - 1), which has been waited for; the upload runs on the copy
     // stream, i.e. under the kernel of the scan in flight
-    const uint32_t slot = (h->scan_seq + 1) & 1u;
+    const uint32_t slot = (h->scan_seq + 1) % kQueueDepth;
     if (!h->scan_q_done[slot]) LO_CUDA(cudaEventCreateWithFlags(&h->scan_q_done[slot], cudaEventDisableTiming));
     LO_TRY(h->scan_q[slot].ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
     if (n) LO_CUDA(cudaMemcpyAsync(h->scan_q[slot].p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, h->copy_stream));

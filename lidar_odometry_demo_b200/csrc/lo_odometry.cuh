@@ -53,6 +53,10 @@ struct ScanReadback {   // per scan, device -> host. The per-scan kernel writes 
 
 }  // namespace lo
 
+namespace lo {
+constexpr uint32_t kQueueDepth = LO_ODOMETRY_QUEUE_DEPTH;   // scans in flight through lo_odometry_submit*: rings of result blocks and staging buffers
+}
+
 struct lo_odometry {
     lo_ctx* ctx = nullptr;
     lo_params params;
@@ -61,14 +65,14 @@ struct lo_odometry {
     lo_grid* match_ds = nullptr;     // VoxelGrid(keyframe_matching_voxel_size, 1) lidar_odometry.cpp:46
     lo::OdomDev* d_state = nullptr;
     lo::ScanReadback* d_readback = nullptr;
-    lo::ScanReadback* h_readback = nullptr;  // [2] pinned, mapped: the per-scan kernel of scan s writes slot s & 1 directly
+    lo::ScanReadback* h_readback = nullptr;  // [kQueueDepth] pinned, mapped: the per-scan kernel of scan s writes slot s % kQueueDepth directly
     uint32_t scan_seq = 0;                   // scans submitted to the per-scan kernel
-    uint32_t wait_seq = 0;                   // ... and waited for (at most 2 in flight)
-    uint32_t queued_n[2] = {0, 0};           // per slot: points of the scan, key-frame ticket after it
-    uint32_t queued_ticket[2] = {0, 0};
+    uint32_t wait_seq = 0;                   // ... and waited for (at most kQueueDepth in flight)
+    uint32_t queued_n[lo::kQueueDepth] = {};      // per slot: points of the scan, key-frame ticket after it
+    uint32_t queued_ticket[lo::kQueueDepth] = {};
     size_t pending_points = 0;               // points of the scans in flight
-    lo::DevBuf scan_q[2];                    // lo_odometry_submit: device copies of the queued host scans
-    cudaEvent_t scan_q_done[2] = {nullptr, nullptr};
+    lo::DevBuf scan_q[lo::kQueueDepth];      // lo_odometry_submit: device copies of the queued host scans
+    cudaEvent_t scan_q_done[lo::kQueueDepth] = {};
     lo::DevBuf scan, deskewed, filtered, update, query;
     lo::DevBuf scan_next;                    // lo_odometry_process_next: the scan being uploaded behind the current one
     cudaStream_t copy_stream = nullptr;

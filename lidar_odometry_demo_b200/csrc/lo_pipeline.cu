@@ -782,7 +782,7 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.kf_free_list = kf->free_list;
     p.ticket_base = grid_take_tickets(kf, n);
     p.seq = ++h->scan_seq;
-    p.readback = h->h_readback + (p.seq & 1u);   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
+    p.readback = h->h_readback + (p.seq % kQueueDepth);   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
     p.n = n;
     p.lo2 = h->params.lidar_min_range * h->params.lidar_min_range;
     p.hi2 = h->params.lidar_max_range * h->params.lidar_max_range;

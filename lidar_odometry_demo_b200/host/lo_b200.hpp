@@ -468,7 +468,7 @@ public:
                                            next_cloud.points.size()));
     }
 
-    // Extension for recorded streams: queue a scan (at most two in flight; its buffer must stay untouched until the matching
+    // Extension for recorded streams: queue a scan (at most LO_ODOMETRY_QUEUE_DEPTH in flight; its buffer must stay untouched until the matching
     // wait) and collect the results in order. submit + wait == processCloud.
     void submit(const CloudType& input_cloud) { lo::check(lo_odometry_submit(h_, input_cloud.points.data(), input_cloud.points.size())); }
     void wait() { lo::check(lo_odometry_wait(h_)); }

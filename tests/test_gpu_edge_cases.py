@@ -123,8 +123,9 @@ def test_process_next_equals_process(ctx, stream12):
 
 
 def test_submit_wait_pipeline_equals_process(ctx, stream12):
-    """lo_odometry_submit / lo_odometry_wait with two scans in flight: the poses, counts and key frame of the one-call
-    lo_odometry_process, scan by scan (an empty scan first, so the bootstrap decision is taken on the device twice)."""
+    """lo_odometry_submit / lo_odometry_wait with two scans in flight, then with the queue filled to its depth: the poses,
+    counts and key frame of the one-call lo_odometry_process, scan by scan (an empty scan first, so the bootstrap decision
+    is taken on the device twice)."""
     scans = [np.zeros(0, stream12[0][0].dtype)] + [np.ascontiguousarray(s) for s in stream12[0][:9]]
     a, b = lo.LidarOdometry(ctx), lo.LidarOdometry(ctx)
     ref = []
@@ -143,14 +144,28 @@ def test_submit_wait_pipeline_equals_process(ctx, stream12):
     for k in range(1, len(scans)):
         b.submit(scans[k].ctypes.data, len(scans[k]))            # scan k queued behind scan k-1
         if k == 3:
-            with pytest.raises(lo.LoError) as e:                   # a third one is refused, nothing is lost
-                b.submit(scans[k].ctypes.data, len(scans[k]))
-            assert e.value.code == lo.LO_E_BUSY
-            with pytest.raises(lo.LoError):                        # and so is a synchronous call while scans are in flight
+            with pytest.raises(lo.LoError):                        # a synchronous call is refused while scans are in flight
                 b.processCloud(scans[k])
         collect()
     collect()
     assert len(got) == len(ref)
+    # the whole queue: QUEUE_DEPTH scans submitted before the first wait, one more is refused and nothing is lost
+    c = lo.LidarOdometry(ctx)
+    c.processCloud(scans[0])
+    c.processCloud(scans[1])
+    deep = []
+    assert lo.QUEUE_DEPTH == 8 and len(scans) >= 2 + lo.QUEUE_DEPTH
+    for k in range(2, 2 + lo.QUEUE_DEPTH):
+        c.submit(scans[k].ctypes.data, len(scans[k]))
+    with pytest.raises(lo.LoError) as e:
+        c.submit(scans[2].ctypes.data, len(scans[2]))
+    assert e.value.code == lo.LO_E_BUSY
+    for k in range(2, 2 + lo.QUEUE_DEPTH):
+        c.wait()
+        st = c.stats()
+        deep.append((c.getCurrentPose().copy(), st.n_planar, st.n_update, st.n_query, st.outer_iterations, st.keyframe_voxels))
+    for k, (r, g) in enumerate(zip(ref[2:2 + lo.QUEUE_DEPTH], deep)):
+        assert np.array_equal(r[0], g[0]) and r[1:] == g[1:], (k, r, g)
     for k, (r, g) in enumerate(zip(ref, got)):
         assert np.array_equal(r[0], g[0]) and r[1:] == g[1:], (k, r, g)
     with pytest.raises(lo.LoError):
