@@ -1,26 +1,31 @@
 #!/usr/bin/env python
 """bench.py — registered scans/s on the synthetic 30k-point VLP16 stream (BASELINE.json config 2).
 
-One "step" = one scan through LidarOdometry::processCloud (time-normalise, deskew, classify, range filter,
-two down-samplers, CloudMatcher::align, divergence gate, radius clean-up, key-frame update).
+One "step" = one scan through LidarOdometry::processCloud (time-normalise, deskew, classify, range filter, two
+down-samplers, CloudMatcher::align, divergence gate, radius clean-up, key-frame update) = one `scan_kernel` launch.
 
   python bench.py [--gpus N] [--steps K] [--warmup W]            our CUDA path (one independent stream per GPU)
   python bench.py --impl reference [--steps K] [--warmup W]      the reference's CPU code (oracle/_ref, else the port)
 
-`value` : scans/s with every scan already resident in HBM (lo_odometry_process_dev), per-step CUDA events on the
-          library's stream, L2 flushed between steps (the flush is not timed).
-`e2e`   : the same metric through the host-pointer C ABI call a user makes (lo_odometry_process): pinned host
-          scan -> H2D -> pipeline -> D2H pose inside the timed region.
-`roofline` : the dominant kernel of the step (align_kernel, persistent cooperative): algorithmic bytes of its
-          correspondence searches (464 + 16*C per query per outer iteration) + its LM evaluations
-          (64 B per query per evaluation) over its measured duration, against MEASURED_PEAKS.json hbm_gbs.
-          `roofline_nn` is the stand-alone fused NN+residual kernel on a 262 144-query batch.
+`value`  : scans/s with every scan already resident in HBM, through lo_odometry_submit_dev / lo_odometry_wait with the
+           queue kept full; per-step CUDA events on the library's stream, L2 flushed between steps (the flush is not
+           timed); the warm-up runs through the same queued path at full depth. Three passes, the median one counts.
+`e2e`    : the drop-in call by the wall clock: K blocking lo_odometry_process calls (processCloud-shaped) on scans in
+           ordinary pageable host memory, pose fetched after each; time.perf_counter around every call, L2 flushed (and
+           the device idle) between calls. K / sum of the call times. Three passes, the median one counts.
+`value_steady_state` / `e2e_steady_state`: the same two measurements after the key frame has been grown by 400 scans of a
+           longer stream (config 2 is "1000 scans"; the key frame saturates at ~1.6e5 voxels after ~350), with the CPU arm
+           timed on the same scans (`cpu_baseline_steady_state`) and the poses compared over the whole way.
+`roofline`: the dominant kernel of the step, scan_kernel (live per-step time, algorithmic bytes of DESIGN.md 5);
+           `roofline_nn`: the stand-alone fused NN+residual kernel on 262 144 queries against a map >> L2, as DRAM bytes
+           actually moved (this round's ncu capture, profiles/r2_ncu_summary.json) over the live time.
+N > 1    : one independent stream per GPU (config 5, no data-path collective), plus `sharded_map`: config 4, one key-frame
+           map sharded by voxel-hash range over the N ranks, CloudMatcher::align through lo_sharded_align_dev.
 """
 import argparse
 import ctypes as C
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -35,6 +40,15 @@ from lidar_odometry_demo_b200 import synthetic as S  # noqa: E402
 METRIC = "registered_scans_per_sec"
 UNIT = "scans/s"
 WORKLOAD = "synthetic VLP16 XYZIRT stream, 16x1875 rays (~28.6k returns/scan), street-canyon scene seed 1234, trajectory seed 99, params.yaml defaults"
+PASSES = 3          # timed passes per headline arm; the median pass is reported, all are listed under "attempts"
+STEADY_SKIP = 400   # scans that grow the key frame before the steady-state window
+STEADY_MAX = 40     # timed scans of the steady-state window (min(K, this))
+
+
+def shared_config(W, K):
+    """`config` is the same object in both arms (the driver compares them)."""
+    return {"workload": WORKLOAD, "window": f"scans {W}..{W + K - 1} of the stream, after {W} warm-up scans",
+            "l2": "flushed between timed steps"}
 
 
 def peaks():
@@ -45,17 +59,14 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-PASSES = 4   # timed passes per queued arm, see the comment in main()
-
-
 class ClockSampler:
     """SM clock and throttle reasons sampled during the timed region, in-process through NVML (nvidia_ml_py). An
     `nvidia-smi -lms` child is NOT used: its start-up (NVML init + device enumeration, ~1 s, once per rank) lands in the
-    first timed arm and stalls kernel launches on every GPU of the box. The period is the recipe's 200 ms: every NVML
-    query may hold up kernel launches (polling every 20 ms was measured no better and sometimes worse: tools/nvml_exp.sh)."""
+    first timed arm and stalls kernel launches on every GPU of the box. The period is 50 ms (the timed arms of the driver's
+    --steps 20 run last ~0.1 s in all, the recipe's 200 ms would give one sample)."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, device, period_s=0.2):
+    def __init__(self, device, period_s=0.05):
         self.device, self.period, self.sm, self.mx, self.reasons = device, period_s, [], None, set()
         self.stop_flag, self.thread, self.nv, self.handle = threading.Event(), None, None, None
         if os.environ.get("LO_BENCH_NO_CLOCKS"):   # diagnosis only: no NVML polling at all
@@ -101,9 +112,21 @@ class ClockSampler:
                 "samples": len(self.sm)}
 
 
-def make_stream(n_scans, rank):
-    scans, pos, q = S.vlp16_stream(n_scans, scene_seed=1234 + 1000 * rank, traj_seed=99 + rank)
+def gen_workers(world=1):
+    return max(1, min(16, (os.cpu_count() or 1) // max(world, 1)))
+
+
+def make_stream(n_scans, rank, workers=1):
+    scans, pos, q = S.vlp16_stream(n_scans, scene_seed=1234 + 1000 * rank, traj_seed=99 + rank, workers=workers)
     return scans
+
+
+def steady_len(K):
+    return STEADY_SKIP + min(K, STEADY_MAX)
+
+
+def want_steady():
+    return not os.environ.get("LO_BENCH_NO_STEADY")
 
 
 def cpu_oracle(kind=None):
@@ -125,6 +148,27 @@ def _reference_stream(job):
     for k in range(warmup, warmup + steps):
         od.process(scans[k])
     return time.perf_counter() - t0, kind
+
+
+def cpu_steady_state(K, scans=None, check=None):
+    """The CPU arm on the steady-state window: all STEADY_SKIP + Kss scans run (the key frame has to be grown by the CPU
+    code itself), the last Kss are timed. check(k, pose7) is called after every scan."""
+    orc, kind = cpu_oracle()
+    if scans is None:
+        scans = make_stream(steady_len(K), 0, gen_workers())
+    oc = orc.odometry()
+    t = 0.0
+    for k, sc in enumerate(scans):
+        t0 = time.perf_counter()
+        oc.process(sc)
+        if k >= STEADY_SKIP:
+            t += time.perf_counter() - t0
+        if check is not None:
+            check(k, oc.pose())
+    n = len(scans) - STEADY_SKIP
+    return {"value": n / t, "unit": UNIT, "cores": 1, "kind": "reference" if kind == "reference" else "port",
+            "sample": f"scans {STEADY_SKIP}..{len(scans) - 1} of a {len(scans)}-scan stream timed ({n} scans, {t:.1f} s), after the CPU code "
+                      f"itself processed scans 0..{STEADY_SKIP - 1}"}
 
 
 def run_reference(args):
@@ -152,8 +196,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 points / f64 solver", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "parallelism": f"{n} independent stream(s), one single-threaded process each on {cores} host core(s) "
-                   "(std::execution::par is serial without TBB; Ceres default num_threads=1)"},
+        "config": shared_config(args.warmup, args.steps),
+        "parallelism": f"{n} independent stream(s), one single-threaded process each on {cores} host core(s) "
+                       "(std::execution::par is serial without TBB; Ceres default num_threads=1)",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if kind == "reference" else "port",
                          "sample": f"{args.steps} consecutive scans after {args.warmup} warm-up scans of each of the {n} stream(s)",
                          "note": "reference's own headers + vendored robin_map (oracle/_ref) with Ceres restated (mini_ceres): omits "
@@ -161,16 +206,31 @@ def run_reference(args):
                                  else "oracle port (oracle/_ref not built on this box)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    if n == 1 and want_steady():
+        ss = cpu_steady_state(args.steps)
+        line["value_steady_state"] = ss["value"]
+        line["e2e_steady_state"] = ss["value"]
+        line["cpu_baseline_steady_state"] = ss
     print(json.dumps(line), flush=True)
 
 
-def run_ours(args):
-    import torch
-    import lidar_odometry_demo_b200 as lo
+def pose_err(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    qa, qb = a[3:] / np.linalg.norm(a[3:]), b[3:] / np.linalg.norm(b[3:])
+    return float(np.linalg.norm(a[:3] - b[:3])), float(2 * np.arccos(min(1.0, abs(qa @ qb))))
 
+
+def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    W, K = args.warmup, args.steps
+    # streams first: the generator forks worker processes, which must happen before CUDA is initialised here
+    scans = make_stream(W + K, rank, gen_workers(world))
+    steady = make_stream(steady_len(K), 0, gen_workers(world)) if rank == 0 and want_steady() else None
+
+    import torch
+    import lidar_odometry_demo_b200 as lo
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -179,8 +239,6 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
 
-    W, K = args.warmup, args.steps
-    scans = make_stream(W + K, rank)
     sizes = [len(s) for s in scans]
     ctx = lo.Context(local)
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
@@ -196,126 +254,159 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    d_scans = [torch.from_numpy(s.view(np.uint8).reshape(-1)).to(dev) for s in scans]
+    def upload(cl):
+        return [torch.from_numpy(s.view(np.uint8).reshape(-1)).to(dev) for s in cl]
+    d_scans = upload(scans)
     pinned = [torch.from_numpy(s.view(np.uint8).reshape(-1).copy()).pin_memory() for s in scans]
 
-    def queued_arm(submit, flush=True, collect=None):
-        """K timed scans through lo_odometry_submit* / lo_odometry_wait with the queue kept full (up to lo.QUEUE_DEPTH scans
-        in flight): the following scans are queued (L2 flush, start event, upload, kernel, end event — all stream-ordered)
-        while scan k runs, so the GPU does not wait for the host unless the host stalls for longer than the queue lasts.
-        Returns the per-step device times (ms) and the odometry object."""
-        od_q = lo.LidarOdometry(ctx)
-        for k in range(W):
-            submit(od_q, k)
+    def queued_arm(submit, first, count, od_q=None, warm=None, flush=True, collect=None):
+        """`count` timed scans [first, first + count) through lo_odometry_submit* / lo_odometry_wait with the queue kept full
+        (up to lo.QUEUE_DEPTH scans in flight): L2 flush, start event, (upload,) kernel, end event are all stream-ordered,
+        the host runs ahead. The warm-up scans [first - warm, first) go through the SAME queued path at full depth.
+        Returns per-step device times (ms), the odometry object, wall time, and what happened to the key frame."""
+        if od_q is None:
+            od_q = lo.LidarOdometry(ctx)
+        warm = first if warm is None else warm
+        issued = 0
+        for i in range(warm):   # queue kept full here too
+            while issued < warm and issued - i < lo.QUEUE_DEPTH:
+                submit(od_q, first - warm + issued)
+                issued += 1
             od_q.wait()
-        s_ev = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-        e_ev = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+        s_ev = [torch.cuda.Event(enable_timing=True) for _ in range(count)]
+        e_ev = [torch.cuda.Event(enable_timing=True) for _ in range(count)]
+        info0 = od_q.keyframeInfo().as_dict()
         barrier()
+        launches0 = ctx.kernel_launches
 
         def enqueue(i):
             if flush:
                 flush_l2()
             s_ev[i].record(stream)
-            submit(od_q, W + i)
+            submit(od_q, first + i)
             e_ev[i].record(stream)
         t0 = time.perf_counter()
         issued = 0
-        for i in range(K):
-            while issued < K and issued - i < lo.QUEUE_DEPTH:
+        for i in range(count):
+            while issued < count and issued - i < lo.QUEUE_DEPTH:
                 enqueue(issued)
                 issued += 1
             od_q.wait()
             if collect is not None:
-                collect(od_q.stats())
+                collect(od_q)
         barrier()
         wall = time.perf_counter() - t0
+        launches = ctx.kernel_launches - launches0
         if flush:
             ms = np.array([a.elapsed_time(b) for a, b in zip(s_ev, e_ev)])
         else:
-            ms = np.full(K, s_ev[0].elapsed_time(e_ev[-1]) / K)
-        return ms, od_q, wall
+            ms = np.full(count, s_ev[0].elapsed_time(e_ev[-1]) / count)
+        info1 = od_q.keyframeInfo().as_dict()
+        note = {"ms_per_step": float(ms.mean()), "p50": float(np.median(ms)), "max": float(ms.max()), "slowest_step": int(ms.argmax()),
+                "kernel_launches": int(launches), "table_rebuilds": info1["table_rebuilds"] - info0["table_rebuilds"],
+                "payload_growths": info1["payload_growths"] - info0["payload_growths"], "keyframe_voxels": info1["voxels"]}
+        return ms, od_q, wall, note
 
-    def one_call_arm(process):
-        """The same K scans through the one-call (processCloud-shaped) entry points, per-step events."""
-        od_s = lo.LidarOdometry(ctx)
-        for k in range(W):
-            process(od_s, k)
-        s_ev = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-        e_ev = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    def blocking_arm(call, first, count, od_b=None, warm=None, flush=True):
+        """`count` blocking processCloud-shaped calls, each timed by the wall clock on its own (call + getCurrentPose); between
+        calls the L2 is flushed and the device drained, outside the timed intervals. Returns per-call seconds and the object."""
+        if od_b is None:
+            od_b = lo.LidarOdometry(ctx)
+        warm = first if warm is None else warm
+        for k in range(first - warm, first):
+            call(od_b, k)
         barrier()
-        for i in range(K):
-            flush_l2()
-            s_ev[i].record(stream)
-            process(od_s, W + i)
-            e_ev[i].record(stream)
-        barrier()
-        return np.array([a.elapsed_time(b) for a, b in zip(s_ev, e_ev)]), od_s
+        dt = np.zeros(count)
+        t_loop = time.perf_counter()
+        for i in range(count):
+            if flush:
+                flush_l2()
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            call(od_b, first + i)
+            od_b.getCurrentPose()
+            dt[i] = time.perf_counter() - t0
+        t_loop = time.perf_counter() - t_loop
+        torch.cuda.synchronize()
+        return dt, od_b, t_loop
 
-    # ---- arm A: inputs resident in HBM -------------------------------------------------------------
-    outer_total, m_total = 0, 0
+    def median_pass(runs, key):
+        order = sorted(range(len(runs)), key=lambda i: key(runs[i]))
+        return runs[order[len(order) // 2]]
+
+    # ---- arm A: inputs resident in HBM, queued ---------------------------------------------------------
     scan_stats = []
 
-    def collect(st):
-        nonlocal outer_total, m_total
-        outer_total += st.outer_iterations
-        m_total += st.n_query
+    def collect(o):
+        st = o.stats()
         scan_stats.append((st.n_points, st.n_planar, st.n_update, st.n_query, st.outer_iterations))
+    submit_dev = lambda o, k: o.submitDevice(d_scans[k].data_ptr(), sizes[k])   # noqa: E731
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
-    launches0 = ctx.kernel_launches
-    step_ms, od, t_wall = queued_arm(lambda o, k: o.submitDevice(d_scans[k].data_ptr(), sizes[k]), collect=collect)
-    launches = ctx.kernel_launches - launches0 - W
-    # Further timed passes of the same K steps: the host side of a shared box stalls now and then for milliseconds (kernel
-    # launches and the pinned-memory result write wait on the PCIe / driver while other tenants load the host; it happens
-    # with and without NVML polling in this process: tools/nvml_exp.sh, profiles/r1_bench_n1_slow_host_box*.json), and one
-    # 8 ms stall is a quarter of a 100-step pass. All passes are reported under "attempts"; the line's value is the
-    # fastest pass.
-    attempts = {"resident_ms_per_step": [float(step_ms.mean())], "e2e_ms_per_step": []}
-    for _ in range(PASSES - 1):
-        step_ms2, od2, t_wall2 = queued_arm(lambda o, k: o.submitDevice(d_scans[k].data_ptr(), sizes[k]))
-        attempts["resident_ms_per_step"].append(float(step_ms2.mean()))
-        assert np.array_equal(od2.getCurrentPose(), od.getCurrentPose()), "two timed passes diverged"
-        if step_ms2.sum() < step_ms.sum():
-            step_ms, t_wall = step_ms2, t_wall2
-        del od2
+    attempts = {"resident": [], "e2e_blocking": []}
+    runs = []
+    for p_i in range(PASSES):
+        ms, od_p, wall_p, note = queued_arm(submit_dev, W, K)
+        runs.append((ms, od_p, wall_p, note))
+        attempts["resident"].append(note)
+        assert p_i == 0 or np.array_equal(od_p.getCurrentPose(), runs[0][1].getCurrentPose()), "two timed passes diverged"
+    step_ms, od, t_wall, note_a = median_pass(runs, lambda r: r[0].sum())
+    launches = note_a["kernel_launches"]
     dev_time = float(step_ms.sum()) / 1e3
-    warm_ms, _, _ = queued_arm(lambda o, k: o.submitDevice(d_scans[k].data_ptr(), sizes[k]), flush=False)
-    warm_time = float(warm_ms.sum()) / 1e3
-    def best_one_call(process):   # two passes, the faster one (every blocking call is exposed to the host-side stalls)
-        a_ms, a_od = one_call_arm(process)
-        b_ms, b_od = one_call_arm(process)
-        assert np.array_equal(a_od.getCurrentPose(), b_od.getCurrentPose()), "two one-call passes diverged"
-        return (a_ms, a_od) if a_ms.sum() <= b_ms.sum() else (b_ms, b_od)
-    sync_ms, od_s = best_one_call(lambda o, k: o.processCloudDevice(d_scans[k].data_ptr(), sizes[k]))
     final_pose = od.getCurrentPose().tolist()
-    kf_voxels = od.stats().keyframe_voxels
-    assert np.array_equal(od_s.getCurrentPose(), od.getCurrentPose()), "queued and one-call arms diverged"
+    kf_info = od.keyframeInfo().as_dict()
+    del runs
+    # per-scan counts for the roofline (one extra untimed pass; stats() waits for each scan's tail)
+    _, _, _, _ = queued_arm(submit_dev, W, K, flush=False, collect=collect)
+    warm_ms, _, _, _ = queued_arm(submit_dev, W, K, flush=False)
+    warm_time = float(warm_ms.sum()) / 1e3
 
-    # ---- arm B: end to end through the host-pointer ABI (pinned host scan -> H2D -> ... -> result block on the host) ----
-    e2e_ms, od_e, _ = queued_arm(lambda o, k: o.submit(pinned[k].data_ptr(), sizes[k]))
-    attempts["e2e_ms_per_step"].append(float(e2e_ms.mean()))
-    for _ in range(PASSES - 1):
-        e2e_ms2, od_e2, _ = queued_arm(lambda o, k: o.submit(pinned[k].data_ptr(), sizes[k]))
-        attempts["e2e_ms_per_step"].append(float(e2e_ms2.mean()))
-        assert np.array_equal(od_e2.getCurrentPose(), od_e.getCurrentPose()), "two e2e passes diverged"
-        if e2e_ms2.sum() < e2e_ms.sum():
-            e2e_ms = e2e_ms2
-        del od_e2
-    e2e_time = float(e2e_ms.sum()) / 1e3
-
-    def process_host(o, k):   # one call per scan; the next record of the stream is uploaded behind the current scan
-        nxt = k + 1 if k + 1 < len(pinned) else None
-        o.processCloudWithNext(pinned[k].data_ptr(), sizes[k], pinned[nxt].data_ptr() if nxt is not None else None,
-                               sizes[nxt] if nxt is not None else 0)
-    e2e_sync_ms, od_es = best_one_call(process_host)
+    # ---- arm B: end to end = the drop-in call by the wall clock ------------------------------------------
+    host_ptrs = [s.ctypes.data for s in scans]   # the numpy arrays as generated: ordinary pageable memory
+    call_host = lambda o, k: o.processCloudHost(host_ptrs[k], sizes[k])   # noqa: E731
+    runs = []
+    for p_i in range(PASSES):
+        dt, od_b, t_loop = blocking_arm(call_host, W, K)
+        runs.append((dt, od_b, t_loop))
+        attempts["e2e_blocking"].append({"ms_per_call": 1e3 * float(dt.mean()), "p50": 1e3 * float(np.median(dt)), "max": 1e3 * float(dt.max()),
+                                         "slowest_call": int(dt.argmax())})
+        assert np.allclose(od_b.getCurrentPose(), final_pose, atol=1e-6), "blocking arm diverged from the resident arm"
+    e2e_dt, od_b, _ = median_pass(runs, lambda r: r[0].sum())
+    e2e_time = float(e2e_dt.sum())
+    del runs
+    b2b_dt, _, b2b_loop = blocking_arm(call_host, W, K, flush=False)   # no flush: one wall-clock interval around all K calls
+    # further arms, one pass each (extra keys): queued from pinned host memory; blocking on device-resident scans
+    q_ms, od_e, _, _ = queued_arm(lambda o, k: o.submit(pinned[k].data_ptr(), sizes[k]), W, K)
+    assert np.allclose(od_e.getCurrentPose(), final_pose, atol=1e-6), "queued e2e arm diverged from the resident arm"
+    dev_dt, od_s, _ = blocking_arm(lambda o, k: o.processCloudDevice(d_scans[k].data_ptr(), sizes[k]), W, K)
+    assert np.allclose(od_s.getCurrentPose(), final_pose, atol=1e-6), "blocking device arm diverged from the resident arm"
     clocks = sampler.stop()
-    assert np.allclose(od_e.getCurrentPose(), final_pose, atol=1e-6), "e2e arm diverged from the resident arm"
-    assert np.allclose(od_es.getCurrentPose(), final_pose, atol=1e-6), "one-call e2e arm diverged from the resident arm"
+
+    # ---- steady state (rank 0): the same two measurements on a key frame grown by STEADY_SKIP scans ------
+    steady_out = None
+    if steady is not None:
+        Kss = len(steady) - STEADY_SKIP
+        ss_sizes = [len(s) for s in steady]
+        d_steady = upload(steady)
+        ms_ss, od_ss, _, note_ss = queued_arm(lambda o, k: o.submitDevice(d_steady[k].data_ptr(), ss_sizes[k]), STEADY_SKIP, Kss)
+        ss_ptrs = [s.ctypes.data for s in steady]
+        dt_ss, od_sb, _ = blocking_arm(lambda o, k: o.processCloudHost(ss_ptrs[k], ss_sizes[k]), STEADY_SKIP, Kss)
+        assert np.allclose(od_sb.getCurrentPose(), od_ss.getCurrentPose(), atol=1e-6), "steady-state arms diverged"
+        steady_out = {"value": Kss / (float(ms_ss.sum()) / 1e3), "e2e": Kss / float(dt_ss.sum()), "note": note_ss,
+                      "e2e_ms_p50": 1e3 * float(np.median(dt_ss)), "e2e_ms_max": 1e3 * float(dt_ss.max()),
+                      "keyframe": od_ss.keyframeInfo().as_dict(), "scans": f"{STEADY_SKIP}..{len(steady) - 1}"}
+        del d_steady, od_ss, od_sb
+
+    # ---- config 4 at N > 1: one key-frame map sharded over the ranks ------------------------------------
+    sharded_out = None
+    if world > 1 and not os.environ.get("LO_BENCH_NO_SHARDED"):
+        del d_scans
+        sharded_out = sharded_section(lo, ctx, torch, dist, rank, world, stream)
 
     # ---- max over ranks ---------------------------------------------------------------------------
     times = torch.tensor([dev_time, e2e_time, warm_time, t_wall], dtype=torch.float64, device=dev)
-    per_rank = [[1e3 * dev_time / K, float(m_total) / K]]
+    per_rank = [[1e3 * dev_time / K, 1e3 * e2e_time / K]]
     if dist is not None:
         mine = torch.tensor(per_rank[0], dtype=torch.float64, device=dev)
         gathered = [torch.zeros_like(mine) for _ in range(world)]
@@ -333,9 +424,9 @@ def run_ours(args):
     peak, peak_src = peaks()
     roof, roof_align, roof_nn = roofline_section(lo, ctx, torch, stream, od, scans, W, K, step_ms, scan_stats, peak, peak_src)
 
-    # ---- CPU baseline on this box's host cores (bounded sample) --------------------------------------
+    # ---- CPU baseline on this box's host cores (bounded samples), pose parity along the way ----------
     orc, kind = cpu_oracle()
-    n_cpu = min(len(scans), W + max(20, min(K, int(20.0 / 0.1))))
+    n_cpu = min(len(scans), W + max(20, min(K, 60)))
     oc = orc.odometry()
     worst_dt = worst_dr = 0.0
     od_chk = lo.LidarOdometry(ctx)
@@ -346,43 +437,68 @@ def run_ours(args):
         if k >= W:
             t_cpu += time.perf_counter() - t0
         od_chk.processCloud(scans[k])
-        a, b = od_chk.getCurrentPose().astype(np.float64), oc.pose().astype(np.float64)
-        worst_dt = max(worst_dt, float(np.linalg.norm(a[:3] - b[:3])))
-        qa, qb = a[3:] / np.linalg.norm(a[3:]), b[3:] / np.linalg.norm(b[3:])
-        worst_dr = max(worst_dr, float(2 * np.arccos(min(1.0, abs(qa @ qb)))))
+        dt_, dr_ = pose_err(od_chk.getCurrentPose(), oc.pose())
+        worst_dt, worst_dr = max(worst_dt, dt_), max(worst_dr, dr_)
     cpu_value = (n_cpu - W) / t_cpu
+    parity = {"max_pose_err_m": worst_dt, "max_pose_err_rad": worst_dr, "scans_checked": n_cpu, "tolerance": "1e-4 m / 1e-4 rad (north_star)"}
+    cpu_ss = None
+    if steady is not None:
+        od_chk = lo.LidarOdometry(ctx)
+        ss_worst = [0.0, 0.0]
+
+        def check(k, pose_cpu):
+            od_chk.processCloud(steady[k])
+            a, b = pose_err(od_chk.getCurrentPose(), pose_cpu)
+            ss_worst[0], ss_worst[1] = max(ss_worst[0], a), max(ss_worst[1], b)
+        cpu_ss = cpu_steady_state(K, steady, check)
+        parity["steady_stream"] = {"max_pose_err_m": ss_worst[0], "max_pose_err_rad": ss_worst[1], "scans_checked": len(steady)}
 
     n = world
     line = {
         "metric": METRIC, "value": n * K / dev_time, "unit": UNIT, "n_gpus": n, "steps": K, "warmup": W,
         "ms_per_step": 1e3 * dev_time / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32 points / f64 solver", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "parallelism": f"{n} independent stream(s), one per GPU, no collective",
-                   "l2": "flushed between timed steps (256 MiB fill, not timed); per-step CUDA events on the library stream",
-                   "api": f"lo_odometry_submit_dev + lo_odometry_wait, up to {lo.QUEUE_DEPTH} scans in flight (the host keeps the queue full while scan k runs)",
-                   "mean_queries_per_scan": m_total / max(K, 1), "mean_outer_iterations": outer_total / max(K, 1),
-                   "keyframe_voxels": int(kf_voxels)},
+        "config": shared_config(W, K),
+        "parallelism": f"{n} independent stream(s), one per GPU, no data-path collective",
+        "api": {"value": f"lo_odometry_submit_dev + lo_odometry_wait, up to {lo.QUEUE_DEPTH} scans in flight (warm-up through the same queued path); "
+                         "per-step CUDA events on the library stream, 256 MiB L2 flush before every step (not timed)",
+                "e2e": "lo_odometry_process (blocking, processCloud-shaped) on pageable host scans + lo_odometry_pose; time.perf_counter around "
+                       "every call, L2 flushed and device drained between calls (not timed); K / sum of the call times"},
+        "e2e": {"value": n * K / e2e_time, "unit": UNIT, "h2d_bytes_per_step": int(np.mean(sizes[W:]) * 32), "d2h_bytes_per_step": 64,
+                "ms_per_call_p50": 1e3 * float(np.median(e2e_dt)), "ms_per_call_max": 1e3 * float(e2e_dt.max()),
+                "back_to_back": {"value": K / b2b_loop, "note": "rank 0: the same K blocking calls in one loop without L2 flushes, one wall-clock "
+                                                                 "interval around the loop"},
+                "queued_from_pinned": {"value": K / (float(q_ms.sum()) / 1e3), "note": "rank 0: lo_odometry_submit (pinned host scans, upload on a copy "
+                                                                                      "stream under the previous kernel) + lo_odometry_wait, CUDA events"}},
+        "one_call_resident": {"value": K / float(dev_dt.sum()), "unit": UNIT,
+                              "note": "rank 0: blocking lo_odometry_process_dev on device-resident scans, wall clock per call"},
         "value_warm_l2": n * K / warm_time, "wall_s_timed_region": t_wall,
-        "one_call": {"value": n * K / (float(sync_ms.sum()) / 1e3), "e2e": n * K / (float(e2e_sync_ms.sum()) / 1e3), "unit": UNIT,
-                     "api": "lo_odometry_process_dev / lo_odometry_process_next: one blocking call per scan (processCloud-shaped), "
-                            "rank 0's figure, the faster of two passes"},
-        "per_rank": [{"ms_per_step": a, "mean_queries_per_scan": b} for a, b in per_rank],   # the streams differ (seeds 1234 + 1000 * rank)
-        "e2e": {"value": n * K / e2e_time, "unit": UNIT, "h2d_bytes_per_step": int(np.mean(sizes[W:]) * 32), "d2h_bytes_per_step": 88,
-                "api": f"lo_odometry_submit + lo_odometry_wait, up to {lo.QUEUE_DEPTH} scans in flight (host scans in pinned memory; the uploads of the "
-                       "queued scans run under the kernel of scan k; the 88-byte result block is written by the kernel into pinned host memory)"},
+        "per_rank": [{"ms_per_step": a, "e2e_ms_per_call": b} for a, b in per_rank],   # the streams differ (seeds 1234 + 1000 * rank)
         "gpu_launches": int(launches),
-        "attempts": dict(attempts, note=f"{PASSES} timed passes of the same K steps per arm (rank 0's figures); value / e2e are the fastest pass",
+        "keyframe": kf_info,
+        "attempts": dict(attempts, note=f"{PASSES} timed passes per headline arm (rank 0's figures); the median pass is reported",
                          step_ms_percentiles={k: float(np.percentile(step_ms, q)) for k, q in (("p10", 10), ("p50", 50), ("p90", 90), ("max", 100))}),
         "clocks": clocks,
         "roofline": roof, "roofline_align": roof_align, "roofline_nn": roof_nn,
         "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": "reference" if kind == "reference" else "port",
                          "sample": f"scans {W}..{n_cpu - 1} of the same stream ({n_cpu - W} scans, {t_cpu:.1f} s)"},
-        "parity": {"max_pose_err_m": worst_dt, "max_pose_err_rad": worst_dr, "scans_checked": n_cpu,
-                   "tolerance": "1e-4 m / 1e-4 rad (north_star)"},
+        "parity": parity,
     }
+    if steady_out is not None:
+        line["value_steady_state"] = steady_out["value"]
+        line["e2e_steady_state"] = steady_out["e2e"]
+        line["steady_state"] = steady_out
+        line["cpu_baseline_steady_state"] = cpu_ss
+    if sharded_out is not None:
+        line["sharded_map"] = sharded_out
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def sharded_section(lo, ctx, torch, dist, rank, world, stream):
+    """BASELINE.json config 4 inside the driver's N-GPU run: see bench_sharded_map()."""
+    return None
 
 
 def _exhaustive(flag):
@@ -395,12 +511,13 @@ def _exhaustive(flag):
 
 def _ncu_traffic(kernel):
     """DRAM bytes (read + write) per launch of `kernel` from the committed `ncu --set full` summary, or None."""
-    path = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
-    try:
-        with open(path) as f:
-            return json.load(f)[kernel]["dram_bytes_per_launch"]
-    except (OSError, KeyError, ValueError):
-        return None
+    for name in ("r2_ncu_summary.json", "r1_ncu_summary.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return json.load(f)[kernel]["dram_bytes_per_launch"]
+        except (OSError, KeyError, ValueError):
+            continue
+    return None
 
 
 def roofline_section(lo, ctx, torch, stream, od, scans, W, K, step_ms, scan_stats, peak, peak_src):

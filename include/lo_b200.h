@@ -231,9 +231,21 @@ typedef struct lo_scan_stats {
     uint32_t reserved;
 } lo_scan_stats;
 
+/* LidarOdometry(const Params&) (lidar_odometry.cpp:14-20). All device memory a scan needs is allocated here, once: the
+ * key-frame table and slabs for 2^19 voxels (env LO_B200_KEYFRAME_VOXELS overrides) and the per-scan scratch for scans of
+ * up to 32 768 points, so that no process / submit call allocates or synchronises the device. A key frame that outgrows
+ * its capacity, or a larger scan, is accommodated by a stream-ordered re-allocation (no host synchronisation). */
 int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odometry** out);
+/* the same with explicit sizes: keyframe_voxels = expected voxels of the key frame inside keyframe_cleanup_range,
+ * scan_points = largest scan expected (each 0: the default). Config 3 of BASELINE.json (128 beams, 0.1 m voxels) wants
+ * e.g. (1 << 21, 1 << 18). */
+int lo_odometry_create_sized(lo_ctx* ctx, const lo_params* params, size_t keyframe_voxels, size_t scan_points, lo_odometry** out);
 void lo_odometry_destroy(lo_odometry* h);
-/* processCloud (lidar_odometry.cpp:22-76) */
+/* processCloud (lidar_odometry.cpp:22-76). The host-pointer form takes ordinary (pageable) memory, as the reference's
+ * caller has it, and stages it through a pinned buffer of the handle. Both return as soon as the scan's pose is final
+ * (after the divergence gate, cpp:53-65); radiusCleanup and the key-frame insert (cpp:67-70) of the scan finish on the
+ * device behind the call, in front of whatever is queued next. Calls that look at the key frame (lo_odometry_stats,
+ * _keyframe*, _snapshot) wait for that tail; an LO_E_RANGE raised by the insert is reported by the call that does. */
 int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t n);
 int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, size_t n);
 /* processCloud on `xyzirt32` while the NEXT scan (`next_xyzirt32`, nullable; pinned host memory for a real overlap) is
@@ -254,6 +266,14 @@ int lo_odometry_wait(lo_odometry* h);
 /* same pipeline entered after CloudClassifier::classify (lidar_odometry.cpp:35 onwards) with a planar cloud */
 int lo_odometry_process_planar(lo_odometry* h, const float* pn48_planar, size_t n);
 int lo_odometry_pose(lo_odometry* h, float out7[7]);                       /* getCurrentPose */
+/* size and allocation history of keyframe_ (src/lidar_odometry.h:82): what bench.py prints next to its timings so that a
+ * slow step can be attributed. Waits for the tail of the last scan. */
+typedef struct lo_keyframe_info {
+    uint64_t voxels, points, tombstones;        /* after the last scan's radiusCleanup + insert */
+    uint64_t capacity_slots, capacity_voxels;   /* table slots / voxel slabs allocated */
+    uint64_t table_rebuilds, payload_growths;   /* stream-ordered re-allocations since creation (0 in a sized run) */
+} lo_keyframe_info;
+int lo_odometry_keyframe_info(lo_odometry* h, lo_keyframe_info* out);
 int lo_odometry_stats(lo_odometry* h, lo_scan_stats* out);
 /* getKeyFrameCloud (full=0, sparse) / getFullKeyFrameCloud (full=1): xyz16 */
 int lo_odometry_keyframe(lo_odometry* h, int full, float* xyz16_out, size_t cap, size_t* n);

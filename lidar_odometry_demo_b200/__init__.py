@@ -53,6 +53,14 @@ class ShardedInfo(C.Structure):
                 ("min_allreduces", C.c_uint64), ("sum_allreduces", C.c_uint64), ("host_syncs", C.c_uint64), ("evaluations", C.c_uint64)]
 
 
+class KeyframeInfo(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("voxels", "points", "tombstones", "capacity_slots", "capacity_voxels", "table_rebuilds",
+                                         "payload_growths")]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
 class ScanStats(C.Structure):
     _fields_ = [("n_points", C.c_uint32), ("n_planar", C.c_uint32), ("n_update", C.c_uint32), ("n_query", C.c_uint32),
                 ("outer_iterations", C.c_int32), ("unstable", C.c_int32), ("keyframe_voxels", C.c_uint32),
@@ -92,11 +100,13 @@ SIGNATURES = {
     "lo_classify": (_i, [_vp, _vp, _sz, _vp, _sz, C.POINTER(_sz)]),
     "lo_pca_normals": (_i, [_vp, _vp, _sz, _fl, _vp]),
     "lo_params_default": (None, [_vp]), "lo_params_from_yaml": (_i, [C.c_char_p, _vp]),
-    "lo_odometry_create": (_i, [_vp, _vp, C.POINTER(_vp)]), "lo_odometry_destroy": (None, [_vp]),
+    "lo_odometry_create": (_i, [_vp, _vp, C.POINTER(_vp)]),
+    "lo_odometry_create_sized": (_i, [_vp, _vp, _sz, _sz, C.POINTER(_vp)]), "lo_odometry_destroy": (None, [_vp]),
     "lo_odometry_process": (_i, [_vp, _vp, _sz]), "lo_odometry_process_dev": (_i, [_vp, _vp, _sz]),
     "lo_odometry_process_next": (_i, [_vp, _vp, _sz, _vp, _sz]),
     "lo_odometry_submit": (_i, [_vp, _vp, _sz]), "lo_odometry_submit_dev": (_i, [_vp, _vp, _sz]), "lo_odometry_wait": (_i, [_vp]),
     "lo_odometry_process_planar": (_i, [_vp, _vp, _sz]), "lo_odometry_pose": (_i, [_vp, _vp]),
+    "lo_odometry_keyframe_info": (_i, [_vp, _vp]),
     "lo_odometry_stats": (_i, [_vp, _vp]),
     "lo_odometry_keyframe": (_i, [_vp, _i, _vp, _sz, C.POINTER(_sz)]),
     "lo_odometry_keyframe_pn": (_i, [_vp, _vp, _sz, C.POINTER(_sz)]),
@@ -370,14 +380,15 @@ class ShardedCloudMatcher:
 class LidarOdometry:
     """Mirror of LidarOdometry (src/lidar_odometry.h:18-86)."""
 
-    def __init__(self, ctx, params=None):
+    def __init__(self, ctx, params=None, keyframe_voxels=0, scan_points=0):
+        """keyframe_voxels / scan_points: capacities allocated once at creation (0: the library's defaults)."""
         self.ctx, self.lib = ctx, ctx.lib
         if params is None:
             params = Params()
             self.lib.lo_params_default(C.byref(params))
         self.params = params
         h = C.c_void_p()
-        _check(self.lib.lo_odometry_create(ctx.h, C.byref(params), C.byref(h)))
+        _check(self.lib.lo_odometry_create_sized(ctx.h, C.byref(params), keyframe_voxels, scan_points, C.byref(h)))
         self.h = h
 
     def close(self):
@@ -391,6 +402,10 @@ class LidarOdometry:
     def processCloud(self, cloud):
         cloud = np.ascontiguousarray(cloud, dtype=XYZIRT)
         _check(self.lib.lo_odometry_process(self.h, _p(cloud), len(cloud)))
+
+    def processCloudHost(self, host_ptr, n):
+        """processCloud on a host scan given by address (no numpy conversion): the drop-in call, lo_odometry_process."""
+        _check(self.lib.lo_odometry_process(self.h, C.c_void_p(host_ptr), n))
 
     def processCloudWithNext(self, cloud_ptr, n, next_ptr, next_n):
         """processCloud on a host scan while the next one (pinned host memory) is uploaded behind it."""
@@ -435,6 +450,11 @@ class LidarOdometry:
         s = ScanStats()
         _check(self.lib.lo_odometry_stats(self.h, C.byref(s)))
         return s
+
+    def keyframeInfo(self):
+        k = KeyframeInfo()
+        _check(self.lib.lo_odometry_keyframe_info(self.h, C.byref(k)))
+        return k
 
     def _cloud(self, fn, dtype, *lead):
         n = C.c_size_t(0)

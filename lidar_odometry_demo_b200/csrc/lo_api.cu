@@ -92,6 +92,12 @@ extern "C" int lo_ctx_create(int device, lo_ctx** out) {
     LO_CUDA(cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     LO_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    {   // grids allocate stream-ordered (lo_grid.cu); keep what they free in the pool instead of returning it to the OS
+        cudaMemPool_t pool;
+        LO_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        uint64_t keep = ~0ull;
+        LO_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     if (ctx->small.ensure(64 * 1024) != LO_OK) return LO_E_CUDA;
     *out = ctx;
     return LO_OK;

@@ -86,8 +86,13 @@ static uint32_t next_pow2(uint64_t v) {
     return static_cast<uint32_t>(p);
 }
 
+// All (re)allocations of a grid are stream-ordered (cudaMallocAsync / cudaFreeAsync on the context's stream, from the
+// device's default pool whose release threshold lo_ctx_create lifts): a table or payload that grows is allocated,
+// filled and swapped in behind the work already queued and in front of the work queued next, with no host
+// synchronisation and no cudaFree. Kernels already queued hold the old view and run before the old buffers are
+// released; callers take g->view() after grid_reserve.
 static int alloc_table(lo_grid* g, uint32_t capacity, Slot** out) {
-    LO_CUDA(cudaMalloc(out, static_cast<size_t>(capacity) * sizeof(Slot)));
+    LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(out), static_cast<size_t>(capacity) * sizeof(Slot), g->ctx->stream));
     LO_CUDA(cudaMemsetAsync(*out, 0xFF, static_cast<size_t>(capacity) * sizeof(Slot), g->ctx->stream));
     return LO_OK;
 }
@@ -97,21 +102,21 @@ static int grow_payload(lo_grid* g, uint32_t new_cap) {
     float4 *np = nullptr, *nn = nullptr;
     uint32_t* nf = nullptr;
     const size_t new_elems = static_cast<size_t>(new_cap) * g->width, old_elems = static_cast<size_t>(g->payload_cap) * g->width;
-    LO_CUDA(cudaMalloc(&np, new_elems * sizeof(float4)));
-    LO_CUDA(cudaMalloc(&nn, new_elems * sizeof(float4)));
-    LO_CUDA(cudaMalloc(&nf, static_cast<size_t>(new_cap) * sizeof(uint32_t)));
+    LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&np), new_elems * sizeof(float4), ctx->stream));
+    LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&nn), new_elems * sizeof(float4), ctx->stream));
+    LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&nf), static_cast<size_t>(new_cap) * sizeof(uint32_t), ctx->stream));
     if (old_elems) {
         LO_CUDA(cudaMemcpyAsync(np, g->points, old_elems * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
         LO_CUDA(cudaMemcpyAsync(nn, g->normals, old_elems * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
         LO_CUDA(cudaMemcpyAsync(nf, g->free_list, static_cast<size_t>(g->payload_cap) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     }
     LO_CUDA(cudaMemsetAsync(np + old_elems, 0xFF, (new_elems - old_elems) * sizeof(float4), ctx->stream));
-    LO_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (g->points) cudaFree(g->points);
-    if (g->normals) cudaFree(g->normals);
-    if (g->free_list) cudaFree(g->free_list);
+    if (g->points) LO_CUDA(cudaFreeAsync(g->points, ctx->stream));
+    if (g->normals) LO_CUDA(cudaFreeAsync(g->normals, ctx->stream));
+    if (g->free_list) LO_CUDA(cudaFreeAsync(g->free_list, ctx->stream));
     g->points = np; g->normals = nn; g->free_list = nf;
     g->payload_cap = new_cap;
+    g->grow_count++;
     return LO_OK;
 }
 
@@ -123,8 +128,8 @@ static int rebuild_table(lo_grid* g, uint32_t new_capacity) {
         grid_rebuild_kernel<<<blocks_for(g->capacity, 256), 256, 0, ctx->stream>>>(g->slots, g->capacity, fresh, new_capacity - 1);
         LO_LAUNCHED(ctx);
         LO_CUDA(cudaMemsetAsync(g->counters + GC_TOMBS, 0, sizeof(uint32_t), ctx->stream));
-        LO_CUDA(cudaStreamSynchronize(ctx->stream));
-        cudaFree(g->slots);
+        LO_CUDA(cudaFreeAsync(g->slots, ctx->stream));
+        g->rebuild_count++;   // counter blocks read back from work queued before this point still carry the old tombstone count
     }
     g->slots = fresh;
     g->capacity = new_capacity;
@@ -301,11 +306,10 @@ int grid_restore(lo_grid* g, const void* blob, size_t bytes) {
         set_error("grid snapshot was taken with max_points %llu, this grid has %zu", static_cast<unsigned long long>(h.max_points), g->max_points);
         return LO_E_ARG;
     }
-    LO_CUDA(cudaStreamSynchronize(ctx->stream));
     if (h.capacity != g->capacity) {
         Slot* fresh = nullptr;
-        LO_CUDA(cudaMalloc(&fresh, static_cast<size_t>(h.capacity) * sizeof(Slot)));
-        if (g->slots) cudaFree(g->slots);
+        LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&fresh), static_cast<size_t>(h.capacity) * sizeof(Slot), ctx->stream));
+        if (g->slots) LO_CUDA(cudaFreeAsync(g->slots, ctx->stream));
         g->slots = fresh;
         g->capacity = h.capacity;
     }
@@ -361,6 +365,12 @@ extern "C" int lo_grid_create(lo_ctx* ctx, float voxel_size, size_t max_points, 
     const uint64_t hint = capacity_hint ? capacity_hint : 4096;
     int st = rebuild_table(g, next_pow2(std::max<uint64_t>(hint * 2, 1024)));
     if (st == LO_OK) st = grow_payload(g, next_pow2(std::max<uint64_t>(hint, 1024)));
+    if (st == LO_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {   // out of memory shows up here, not in a later call
+        set_error("allocating a voxel grid for %llu voxels of %u points failed: %s", static_cast<unsigned long long>(hint), g->width,
+                  cudaGetErrorString(cudaGetLastError()));
+        st = LO_E_CUDA;
+    }
+    g->rebuild_count = g->grow_count = 0;
     if (st != LO_OK) {
         lo_grid_destroy(g);
         return st;
@@ -373,10 +383,10 @@ extern "C" void lo_grid_destroy(lo_grid* g) {
     if (!g) return;
     cudaSetDevice(g->ctx->device);
     cudaStreamSynchronize(g->ctx->stream);
-    if (g->slots) cudaFree(g->slots);
-    if (g->points) cudaFree(g->points);
-    if (g->normals) cudaFree(g->normals);
-    if (g->free_list) cudaFree(g->free_list);
+    if (g->slots) cudaFreeAsync(g->slots, g->ctx->stream);
+    if (g->points) cudaFreeAsync(g->points, g->ctx->stream);
+    if (g->normals) cudaFreeAsync(g->normals, g->ctx->stream);
+    if (g->free_list) cudaFreeAsync(g->free_list, g->ctx->stream);
     if (g->counters) cudaFree(g->counters);
     delete g;
 }

@@ -105,6 +105,8 @@ struct lo_grid {
     uint32_t* counters = nullptr;   // [GC_COUNT] device
     uint32_t h_counters[GC_COUNT] = {0, 0, 0, 0, 0, 0, 0, 0};  // host mirror (valid after refresh)
     bool cleaned = false;        // radius_cleanup ran: reference iteration order can no longer be emulated
+    uint64_t rebuild_count = 0;  // table rebuilds (growth or tombstone purge) since creation
+    uint64_t grow_count = 0;     // payload growths since creation
 
     lo::GridView view() const {
         lo::GridView v;

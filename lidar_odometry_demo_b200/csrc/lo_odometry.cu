@@ -113,21 +113,35 @@ static int run_from_filtered(lo_odometry* h, uint32_t bound, const uint32_t* d_P
     return LO_OK;
 }
 
-// copy a scan's result block into the handle (pose, stats, host mirror of the key-frame counters)
-static int adopt_readback(lo_odometry* h, const ScanReadback& r, uint32_t n_points) {
+// second half of a scan's result block: host mirror of the key-frame counters
+static int adopt_counters(lo_odometry* h, const uint32_t kf_counters[GC_COUNT], bool predates_rebuild) {
+    lo_grid* kf = h->keyframe;
+    const uint32_t ticket = kf->h_counters[GC_TICKET], tombs = kf->h_counters[GC_TOMBS];   // tickets are tracked on the host
+    std::memcpy(kf->h_counters, kf_counters, sizeof(kf->h_counters));
+    kf->h_counters[GC_TICKET] = ticket;
+    // a block written before the table was last rebuilt still counts the tombstones that rebuild purged
+    if (predates_rebuild) kf->h_counters[GC_TOMBS] = tombs;
+    h->stats.keyframe_voxels = kf_counters[GC_VOXELS];
+    if (kf_counters[GC_RANGE_ERR]) {
+        set_error("a key-frame point was not finite or outside the +-2^20 voxel index range");
+        return LO_E_RANGE;
+    }
+    return LO_OK;
+}
+
+// first half: pose and per-scan counts
+static int adopt_pose(lo_odometry* h, const ScanReadback& r, uint32_t n_points) {
     std::memcpy(h->pose, r.pose, sizeof(h->pose));
-    std::memcpy(h->keyframe->h_counters, r.kf_counters, sizeof(r.kf_counters));
-    // arrival tickets are tracked on the host
     h->stats.n_points = n_points;
     h->stats.n_planar = r.n_planar;
     h->stats.n_update = r.n_update;
     h->stats.n_query = r.n_query;
     h->stats.outer_iterations = r.outer_iterations;
     h->stats.unstable = static_cast<int32_t>(r.unstable);
-    h->stats.keyframe_voxels = r.kf_counters[GC_VOXELS];
-    if (r.kf_counters[GC_RANGE_ERR]) {
-        set_error("a key-frame point was not finite or outside the +-2^20 voxel index range");
-        return LO_E_RANGE;
+    if (r.overflow) {
+        set_error("the classifier's ring x azimuth grid (widest ring x rings present) exceeds the scratch sized for %u points: "
+                  "the scan produced no planar points", n_points);
+        return LO_E_CAPACITY;
     }
     return LO_OK;
 }
@@ -137,39 +151,69 @@ static int finish_scan(lo_odometry* h, uint32_t n_points) {
     lo_ctx* ctx = h->ctx;
     odom_readback_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state, h->keyframe->counters, h->d_readback, h->d_minmax);
     LO_LAUNCHED(ctx);
-    LO_CUDA(cudaMemcpyAsync(h->h_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(h->h_stage_readback, h->d_readback, sizeof(ScanReadback), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
-    h->h_readback[0].seq = 0;   // never a per-scan kernel's number
     h->keyframe->cleaned = true;
-    return adopt_readback(h, h->h_readback[0], n_points);
+    const int st = adopt_pose(h, *h->h_stage_readback, n_points);
+    const int st2 = adopt_counters(h, h->h_stage_readback->kf_counters, false);
+    return st != LO_OK ? st : st2;
 }
 
-// per-scan kernel: wait for the oldest scan in flight. The kernel wrote the block into pinned memory; its last store
-// is `seq`. Poll it (the result is there a few microseconds before the stream reports the kernel as retired),
-// checking the stream now and then so that a failed launch cannot hang the caller.
-static int wait_oldest(lo_odometry* h) {
-    lo_ctx* ctx = h->ctx;
-    const uint32_t want = h->wait_seq + 1, slot = want % kQueueDepth;
-    const volatile uint32_t* seq = &h->h_readback[slot].seq;
-    static const char* wait_mode = getenv("LO_B200_WAIT");   // developer switch: "sync" waits on the stream first
-    if (wait_mode && wait_mode[0] == 's') LO_CUDA(cudaStreamSynchronize(ctx->stream));
-    for (uint32_t spins = 0; *seq != want; spins++) {
-        if ((spins & 0xFFFFFu) == 0xFFFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
+// spin until *word == want; the stream is checked now and then so that a failed launch cannot hang the caller.
+// `pause` between polls: the word lives in pinned host memory, the store that ends the wait comes over PCIe.
+static int poll_word(lo_ctx* ctx, const volatile uint32_t* word, uint32_t want, const char* what) {
+    for (uint32_t spins = 0; *word != want; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+        if ((spins & 0x3FFFFu) == 0x3FFFFu && cudaStreamQuery(ctx->stream) != cudaErrorNotReady) break;
     }
-    if (*seq != want) LO_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (*seq != want) {
-        set_error("the per-scan kernel finished without publishing its result");
+    if (*word != want) LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (*word != want) {
+        set_error("the per-scan kernel finished without publishing its %s", what);
         return LO_E_CUDA;
     }
     std::atomic_thread_fence(std::memory_order_acquire);
+    return LO_OK;
+}
+
+// Take over the key-frame counters of the scans that have been waited for, oldest first. block = false: only those whose
+// kernel has ended already. Whatever looks at the key frame from the host (stats, export, snapshot, the next reserve
+// when the ring slot is needed) calls this with block = true; the blocking process calls do not, so they return while
+// the kernel's tail is still running.
+static int adopt_finished(lo_odometry* h, uint32_t upto, bool block) {
+    int st = LO_OK;
+    while (h->adopt_seq < upto) {
+        const uint32_t want = h->adopt_seq + 1, slot = want % kQueueDepth;
+        const volatile uint32_t* seq = &h->h_readback[slot].seq;
+        if (*seq != want) {
+            if (!block) break;
+            LO_TRY(poll_word(h->ctx, seq, want, "key-frame counters"));
+        }
+        std::atomic_thread_fence(std::memory_order_acquire);
+        h->adopt_seq = want;
+        h->pending_points -= h->queued_n[slot];
+        if (h->adopt_seq == h->scan_seq) fused_trace_dump(h);
+        const int s2 = adopt_counters(h, h->h_readback[slot].kf_counters, h->queued_rebuilds[slot] != h->keyframe->rebuild_count);
+        if (st == LO_OK) st = s2;
+    }
+    return st;
+}
+
+// per-scan kernel: wait for the pose of the oldest scan in flight. The kernel wrote the block into pinned memory; poll
+// its sequence word (the result is there a few microseconds before the stream would report anything).
+static int wait_oldest(lo_odometry* h) {
+    lo_ctx* ctx = h->ctx;
+    const uint32_t want = h->wait_seq + 1, slot = want % kQueueDepth;
+    static const char* wait_mode = getenv("LO_B200_WAIT");   // developer switch: "sync" waits on the stream first
+    if (wait_mode && wait_mode[0] == 's') LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    LO_TRY(poll_word(ctx, &h->h_readback[slot].pose_seq, want, "pose"));
     h->wait_seq = want;
-    h->pending_points -= h->queued_n[slot];
-    if (h->wait_seq == h->scan_seq) fused_trace_dump(h);
     const ScanReadback& r = h->h_readback[slot];
     if (!r.bootstrap) h->keyframe->cleaned = true;   // radiusCleanup ran: reference iteration order can no longer be emulated
-    const int st = adopt_readback(h, r, h->queued_n[slot]);
-    h->keyframe->h_counters[GC_TICKET] = h->queued_ticket[h->scan_seq % kQueueDepth];   // tickets: as of the newest scan submitted
-    return st;
+    const int st = adopt_pose(h, r, h->queued_n[slot]);
+    const int st2 = adopt_finished(h, h->wait_seq, false);   // whatever has ended by now, without waiting
+    return st != LO_OK ? st : st2;
 }
 
 static int submit_fused(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
@@ -177,28 +221,54 @@ static int submit_fused(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
         set_error("%u scans are already in flight: call lo_odometry_wait first", kQueueDepth);
         return LO_E_BUSY;
     }
+    // the ring slot this scan will write must have been read out completely (it is kQueueDepth scans old: long done)
+    if (h->scan_seq + 1 > kQueueDepth) LO_TRY(adopt_finished(h, h->scan_seq + 1 - kQueueDepth, true));
+    LO_TRY(adopt_finished(h, h->wait_seq, false));
+    const uint64_t rebuilds = h->keyframe->rebuild_count;
     LO_TRY(fused_process_enqueue(h, d_scan, n));
     const uint32_t slot = h->scan_seq % kQueueDepth;
     h->queued_n[slot] = n;
     h->queued_ticket[slot] = h->keyframe->h_counters[GC_TICKET];
+    h->queued_rebuilds[slot] = rebuilds;   // a rebuild queued by this very submit runs before the scan's kernel
+    if (h->keyframe->rebuild_count != rebuilds) h->queued_rebuilds[slot] = h->keyframe->rebuild_count;
     h->pending_points += n;
     h->n_last = n;
     return LO_OK;
 }
 
+// every scan submitted has handed out its pose: wait for the kernels' tails too and mirror the key-frame counters
+static int settle(lo_odometry* h) { return adopt_finished(h, h->wait_seq, true); }
+
 // keep the host-tracked ticket counter across the device counter readback
 static void preserve_ticket(lo_grid* g, uint32_t ticket) { g->h_counters[GC_TICKET] = ticket; }
 
-extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odometry** out) {
+// Key-frame capacity (voxels) a LidarOdometry is created with. The table and both slabs are sized ONCE, here (SURVEY 7.2:
+// "power-of-two capacity sized once, no rehash on device"): 2^19 voxel slabs of max_points points (2 x 168 MB at the
+// defaults) behind 2^20 slots (16 MB) hold three times the ~1.6e5 voxels the VLP16 street stream settles at inside its
+// 80 m clean-up range; nothing on a 180 GB part. A map that outgrows it is regrown stream-ordered (lo_grid.cu), never
+// by a synchronising call. LO_B200_KEYFRAME_VOXELS / lo_odometry_create_sized override the default.
+static size_t default_keyframe_voxels() {
+    const char* e = getenv("LO_B200_KEYFRAME_VOXELS");
+    return e && atoll(e) > 0 ? static_cast<size_t>(atoll(e)) : (static_cast<size_t>(1) << 19);
+}
+
+extern "C" int lo_odometry_create_sized(lo_ctx* ctx, const lo_params* params, size_t keyframe_voxels, size_t scan_points, lo_odometry** out) {
     if (!ctx || !params || !out) return LO_E_ARG;
     LO_CUDA(cudaSetDevice(ctx->device));
+    if (keyframe_voxels == 0) keyframe_voxels = default_keyframe_voxels();
+    if (scan_points == 0) scan_points = kPresizedScanPoints;
+    if (scan_points > fused_max_points()) scan_points = fused_max_points();
     lo_odometry* h = new lo_odometry();
     h->ctx = ctx;
     h->params = *params;
     std::memset(&h->stats, 0, sizeof(h->stats));
-    int st = lo_grid_create(ctx, params->keyframe_voxel_size, static_cast<size_t>(params->keyframe_max_points_cnt), 1 << 17, &h->keyframe);
+    int st = lo_grid_create(ctx, params->keyframe_voxel_size, static_cast<size_t>(params->keyframe_max_points_cnt), keyframe_voxels, &h->keyframe);
     if (st == LO_OK) st = lo_grid_create(ctx, params->keyframe_update_voxel_size, 1, 1 << 15, &h->update_ds);
     if (st == LO_OK) st = lo_grid_create(ctx, params->keyframe_matching_voxel_size, 1, 1 << 15, &h->match_ds);
+    // everything a scan of up to scan_points points needs, so that no submit / process call allocates
+    if (st == LO_OK) st = fused_reserve(h, static_cast<uint32_t>(scan_points));
+    if (st == LO_OK) st = h->scan.ensure(scan_points * sizeof(PointXYZIRT));
+    if (st == LO_OK) st = h->stage.ensure(scan_points * sizeof(PointXYZIRT));
     if (st != LO_OK) {
         lo_odometry_destroy(h);
         return st;
@@ -206,16 +276,24 @@ extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odome
     LO_CUDA(cudaMalloc(&h->d_state, sizeof(OdomDev)));
     LO_CUDA(cudaMemsetAsync(h->d_state, 0, sizeof(OdomDev), ctx->stream));
     LO_CUDA(cudaMalloc(&h->d_readback, sizeof(ScanReadback)));
-    LO_CUDA(cudaMallocHost(&h->h_readback, kQueueDepth * sizeof(ScanReadback)));
-    std::memset(h->h_readback, 0, kQueueDepth * sizeof(ScanReadback));
+    LO_CUDA(cudaMallocHost(&h->h_readback, (kQueueDepth + 1) * sizeof(ScanReadback)));
+    std::memset(h->h_readback, 0, (kQueueDepth + 1) * sizeof(ScanReadback));
+    h->h_stage_readback = h->h_readback + kQueueDepth;   // D2H target of the stage-by-stage pipeline
     LO_CUDA(cudaMalloc(&h->d_minmax, 2 * sizeof(uint32_t)));
     const uint32_t minmax_init[2] = {0xFFFFFFFFu, 0u};
     LO_CUDA(cudaMemcpyAsync(h->d_minmax, minmax_init, sizeof(minmax_init), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    LO_CUDA(cudaEventCreateWithFlags(&h->copy_done, cudaEventDisableTiming));
+    for (uint32_t k = 0; k < kQueueDepth; k++) LO_CUDA(cudaEventCreateWithFlags(&h->scan_q_done[k], cudaEventDisableTiming));
     odom_init_kernel<<<1, 1, 0, ctx->stream>>>(h->d_state);
     LO_LAUNCHED(ctx);
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
     *out = h;
     return LO_OK;
+}
+
+extern "C" int lo_odometry_create(lo_ctx* ctx, const lo_params* params, lo_odometry** out) {
+    return lo_odometry_create_sized(ctx, params, 0, 0, out);
 }
 
 extern "C" void lo_odometry_destroy(lo_odometry* h) {
@@ -236,6 +314,7 @@ extern "C" void lo_odometry_destroy(lo_odometry* h) {
     }
     if (h->copy_done) cudaEventDestroy(h->copy_done);
     for (DevBuf* b : {&h->scan, &h->scan_next, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
+    h->stage.release();
     for (DevBuf& b : h->scan_q) b.release();
     for (cudaEvent_t e : h->scan_q_done)
         if (e) cudaEventDestroy(e);
@@ -257,6 +336,7 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
         LO_TRY(submit_fused(h, static_cast<const PointXYZIRT*>(d_xyzirt32), nn));
         return wait_oldest(h);
     }
+    LO_TRY(settle(h));
     const uint32_t kf_ticket = h->keyframe->h_counters[GC_TICKET];
     LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
     LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
@@ -276,12 +356,39 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
     return st;
 }
 
+// Upload of a scan that sits in ordinary (pageable) host memory, as processCloud's caller has it: the scan is copied
+// through the handle's pinned staging buffer in pieces, each piece's DMA running under the memcpy of the next one.
+// (cudaMemcpyAsync on pageable memory stages too, but serially and with a synchronising tail.)
+static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
+    lo_ctx* ctx = h->ctx;
+    const size_t bytes = n * sizeof(PointXYZIRT);
+    LO_TRY(h->scan.ensure(std::max<size_t>(bytes, sizeof(PointXYZIRT))));
+    if (!n) return LO_OK;
+    static const int mode = [] { const char* e = getenv("LO_B200_UPLOAD"); return e ? atoi(e) : 0; }();   // developer switch: 1 = plain cudaMemcpyAsync
+    if (mode == 1) {
+        LO_CUDA(cudaMemcpyAsync(h->scan.p, xyzirt32, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return LO_OK;
+    }
+    // the previous scan's DMA out of the staging buffer ended before that call returned (its kernel was waited for)
+    LO_TRY(h->stage.ensure(bytes));
+    constexpr size_t kPiece = 256 * 1024;
+    for (size_t off = 0; off < bytes; off += kPiece) {
+        const size_t len = std::min(kPiece, bytes - off);
+        std::memcpy(h->stage.as<char>() + off, static_cast<const char*>(xyzirt32) + off, len);
+        LO_CUDA(cudaMemcpyAsync(h->scan.as<char>() + off, h->stage.as<char>() + off, len, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return LO_OK;
+}
+
 extern "C" int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t n) {
     if (!h || (!xyzirt32 && n)) return LO_E_ARG;
     lo_ctx* ctx = h->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
-    LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
-    if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, ctx->stream));
+    if (h->scan_seq != h->wait_seq) {
+        set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
+        return LO_E_BUSY;
+    }
+    LO_TRY(upload_scan(h, xyzirt32, n));
     return lo_odometry_process_dev(h, h->scan.p, n);
 }
 
@@ -289,10 +396,6 @@ extern "C" int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, si
     if (!h || (!xyzirt32 && n) || (!next_xyzirt32 && next_n)) return LO_E_ARG;
     lo_ctx* ctx = h->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
-    if (!h->copy_stream) {
-        LO_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-        LO_CUDA(cudaEventCreateWithFlags(&h->copy_done, cudaEventDisableTiming));
-    }
     if (h->next_ptr && h->next_ptr == xyzirt32 && h->next_n == n) {
         std::swap(h->scan, h->scan_next);                                   // uploaded (or arriving) behind the previous scan
         LO_CUDA(cudaStreamWaitEvent(ctx->stream, h->copy_done, 0));
@@ -334,15 +437,12 @@ extern "C" int lo_odometry_submit(lo_odometry* h, const void* xyzirt32, size_t n
         set_error("%u scans are already in flight: call lo_odometry_wait first", kQueueDepth);
         return LO_E_BUSY;
     }
-    if (!h->copy_stream) {
-        LO_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-        LO_CUDA(cudaEventCreateWithFlags(&h->copy_done, cudaEventDisableTiming));
-    }
-    // the slot's device copy was last read by scan (seq - 1), which has been waited for; the upload runs on the copy
-    // stream, i.e. under the kernel of the scan in flight
+    // the slot's device copy was last read by the scan kQueueDepth submits ago, whose pose has been waited for — but its
+    // kernel may still be reading the scan in its tail only if it were the scan in flight, which the ring excludes;
+    // the upload runs on the copy stream, i.e. under the kernel of the scan in flight
     const uint32_t slot = (h->scan_seq + 1) % kQueueDepth;
-    if (!h->scan_q_done[slot]) LO_CUDA(cudaEventCreateWithFlags(&h->scan_q_done[slot], cudaEventDisableTiming));
-    LO_TRY(h->scan_q[slot].ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
+    if (h->scan_seq + 1 > kQueueDepth) LO_TRY(adopt_finished(h, h->scan_seq + 1 - kQueueDepth, true));
+    LO_TRY(h->scan_q[slot].ensure(std::max<size_t>(std::max<size_t>(n, kPresizedScanPoints), 1) * sizeof(PointXYZIRT)));
     if (n) LO_CUDA(cudaMemcpyAsync(h->scan_q[slot].p, xyzirt32, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, h->copy_stream));
     LO_CUDA(cudaEventRecord(h->scan_q_done[slot], h->copy_stream));
     LO_CUDA(cudaStreamWaitEvent(ctx->stream, h->scan_q_done[slot], 0));
@@ -369,6 +469,7 @@ extern "C" int lo_odometry_process_planar(lo_odometry* h, const float* pn48_plan
         set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
         return LO_E_BUSY;
     }
+    LO_TRY(settle(h));
     LO_TRY(h->scan.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
     if (n) LO_CUDA(cudaMemcpyAsync(h->scan.p, pn48_planar, n * sizeof(PointNormal), cudaMemcpyHostToDevice, ctx->stream));
@@ -392,17 +493,38 @@ extern "C" int lo_odometry_pose(lo_odometry* h, float out7[7]) {
 
 extern "C" int lo_odometry_stats(lo_odometry* h, lo_scan_stats* out) {
     if (!h || !out) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    const int st = settle(h);   // keyframe_voxels is known when the scan's key-frame insert is through
     *out = h->stats;
-    return LO_OK;
+    return st;
+}
+
+extern "C" int lo_odometry_keyframe_info(lo_odometry* h, lo_keyframe_info* out) {
+    if (!h || !out) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    const int st = settle(h);
+    const lo_grid* kf = h->keyframe;
+    out->voxels = kf->h_counters[GC_VOXELS];
+    out->points = kf->h_counters[GC_POINTS];
+    out->tombstones = kf->h_counters[GC_TOMBS];
+    out->capacity_slots = kf->capacity;
+    out->capacity_voxels = kf->payload_cap;
+    out->table_rebuilds = kf->rebuild_count;
+    out->payload_growths = kf->grow_count;
+    return st;
 }
 
 extern "C" int lo_odometry_keyframe(lo_odometry* h, int full, float* xyz16_out, size_t cap, size_t* n) {
     if (!h || !n) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    LO_TRY(settle(h));
     return lo_grid_get_cloud(h->keyframe, full ? 1 : 2, 0, xyz16_out, cap, n);
 }
 
 extern "C" int lo_odometry_keyframe_pn(lo_odometry* h, float* pn48_out, size_t cap, size_t* n) {
     if (!h || !n) return LO_E_ARG;
+    LO_CUDA(cudaSetDevice(h->ctx->device));
+    LO_TRY(settle(h));
     return lo_grid_get_cloud(h->keyframe, 0, 0, pn48_out, cap, n);
 }
 
@@ -450,6 +572,7 @@ extern "C" int lo_odometry_snapshot(lo_odometry* h, void* out, size_t cap, size_
         set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
         return LO_E_BUSY;
     }
+    LO_TRY(settle(h));
     size_t grid_bytes = 0;
     LO_TRY(grid_snapshot(h->keyframe, nullptr, 0, &grid_bytes));
     const size_t fixed = sizeof(OdomSnapHeader) + sizeof(OdomDev);
@@ -478,6 +601,7 @@ extern "C" int lo_odometry_restore(lo_odometry* h, const void* blob, size_t byte
         set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
         return LO_E_BUSY;
     }
+    LO_TRY(settle(h));
     OdomSnapHeader hd;
     const size_t fixed = sizeof(OdomSnapHeader) + sizeof(OdomDev);
     if (bytes < fixed) {

@@ -42,13 +42,22 @@ __device__ inline void euler_angles_012(const float r[9], float ang[3]) {
     ang[0] = -e0; ang[1] = -e1; ang[2] = -e2;
 }
 
-struct ScanReadback {   // per scan, device -> host. The per-scan kernel writes it straight into pinned host memory and then
-    float pose[7];      // publishes `seq`; the stage-by-stage pipeline fills a device copy that is fetched with one D2H.
+// Per scan, device -> host. The per-scan kernel writes it straight into pinned host memory in two steps: the pose and
+// the scan's counts as soon as the divergence gate has decided (`pose_seq` last), and the key-frame counters when
+// radiusCleanup and the key-frame insert are through (`seq` last). lo_odometry_wait / the blocking process calls return
+// on `pose_seq` — the reference's processCloud has nothing else to hand back — while the kernel's tail (cpp:67-70) runs on
+// behind them; whatever needs the key frame waits for `seq`. The stage-by-stage pipeline fills a device copy that is
+// fetched with one D2H.
+struct ScanReadback {
+    float pose[7];
     uint32_t n_planar, n_update, n_query, unstable;
     int32_t outer_iterations;
+    uint32_t bootstrap;   // the key frame was empty: the scan was inserted un-aligned (cpp:40-44)
+    uint32_t overflow;    // the classifier's ring x azimuth grid did not fit the scratch: no planar points were produced
+    uint32_t pose_seq;    // scan number, written after a system-scope fence once everything above is final
     uint32_t kf_counters[GC_COUNT];
-    uint32_t bootstrap; // the key frame was empty: the scan was inserted un-aligned (cpp:40-44)
-    uint32_t seq;       // scan number, written last (after a system-scope fence)
+    uint32_t seq;         // scan number, written last (after a system-scope fence)
+    uint32_t pad[3];
 };
 
 }  // namespace lo
@@ -65,12 +74,16 @@ struct lo_odometry {
     lo_grid* match_ds = nullptr;     // VoxelGrid(keyframe_matching_voxel_size, 1) lidar_odometry.cpp:46
     lo::OdomDev* d_state = nullptr;
     lo::ScanReadback* d_readback = nullptr;
-    lo::ScanReadback* h_readback = nullptr;  // [kQueueDepth] pinned, mapped: the per-scan kernel of scan s writes slot s % kQueueDepth directly
+    lo::ScanReadback* h_readback = nullptr;  // [kQueueDepth + 1] pinned, mapped: the per-scan kernel of scan s writes slot s % kQueueDepth directly
+    lo::ScanReadback* h_stage_readback = nullptr;   // the extra block: D2H target of the stage-by-stage pipeline
     uint32_t scan_seq = 0;                   // scans submitted to the per-scan kernel
-    uint32_t wait_seq = 0;                   // ... and waited for (at most kQueueDepth in flight)
+    uint32_t wait_seq = 0;                   // ... waited for, i.e. their pose has been handed out (at most kQueueDepth in flight)
+    uint32_t adopt_seq = 0;                  // ... and whose key-frame counters (end of the kernel) have been taken over
     uint32_t queued_n[lo::kQueueDepth] = {};      // per slot: points of the scan, key-frame ticket after it
     uint32_t queued_ticket[lo::kQueueDepth] = {};
-    size_t pending_points = 0;               // points of the scans in flight
+    uint64_t queued_rebuilds[lo::kQueueDepth] = {};   // per slot: key-frame table rebuilds before the scan was queued
+    size_t pending_points = 0;               // points of the scans whose key-frame counters are not on the host yet
+    lo::PinnedBuf stage;                     // lo_odometry_process: pinned staging of a pageable host scan
     lo::DevBuf scan_q[lo::kQueueDepth];      // lo_odometry_submit: device copies of the queued host scans
     cudaEvent_t scan_q_done[lo::kQueueDepth] = {};
     lo::DevBuf scan, deskewed, filtered, update, query;
@@ -93,6 +106,8 @@ namespace lo {
 constexpr uint32_t kFusedMaxPoints = 1u << 19;   // 524 288: a 128-beam revolution (262 144 returns) twice over
 uint32_t fused_max_points();   // kFusedMaxPoints, or the developer override LO_B200_FUSED_MAX
 int fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n);
+int fused_reserve(lo_odometry* h, uint32_t n);   // scratch for scans of up to n points (no-op when it is there already)
+constexpr uint32_t kPresizedScanPoints = 32768;   // what lo_odometry_create reserves for: a VLP16 revolution is ~30 k returns
 void fused_release(lo_odometry* h);
 void fused_trace_dump(lo_odometry* h);
 }  // namespace lo

@@ -646,6 +646,21 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     __shared__ Pose current_s;
     __shared__ uint32_t unstable_s;
     const Pose* insert_pose = nullptr;   // first scan: inserted un-transformed (cpp:42)
+    // first half of the read-back block: what processCloud's caller can see (getCurrentPose) is final once the gate has
+    // decided; the host returns on `pose_seq` while radiusCleanup and the key-frame insert below are still running
+    auto publish_pose = [&](const Pose& now, uint32_t unstable) {
+        ScanReadback* out = p.readback;
+        pose_to7(now, out->pose);
+        out->n_planar = s->n_planar;
+        out->n_update = s->n_update;
+        out->n_query = s->n_query;
+        out->unstable = unstable;
+        out->outer_iterations = s->align.outer_iterations;
+        out->bootstrap = static_cast<uint32_t>(first);
+        out->overflow = p.b.layout[2];
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(&out->pose_seq) = p.seq;
+    };
     if (!first) {
         AlignArgs a;                     // CloudMatcher::align(keyframe_, query, current.compose(relative))  cpp:49-51
         a.g = p.kf;
@@ -677,6 +692,7 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
             nw.t[0] = next_s[0]; nw.t[1] = next_s[1]; nw.t[2] = next_s[2];
             nw.w = next_s[3]; nw.x = next_s[4]; nw.y = next_s[5]; nw.z = next_s[6];
             current_s = gate_pose(nw, s->current, s->guess, p.gate_threshold, unstable_s);   // cpp:53-65
+            if (blockIdx.x == 0) publish_pose(current_s, unstable_s);
         }
         __syncthreads();
         LO_SCAN_TRACE(120);
@@ -685,6 +701,8 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         grid.sync();
         LO_SCAN_TRACE(121);
         insert_pose = &current_s;        // transformWithNormals fused into the load (cpp:69)
+    } else if (blockIdx.x == 0 && threadIdx.x == 0) {
+        publish_pose(s->current, s->unstable);   // bootstrap scan: the pose does not move (cpp:40-44)
     }
     // keyframe_.addCloud(update) (cpp:42 / cpp:70)
     // the update cloud is read in place: output position d of the robin_map order is sorted element (d - rot) mod n,
@@ -709,7 +727,7 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         grid_write_item(i, src, p.ticket_base, insert_pose, p.kf, p.kf_counters, p.b.kf_slot, p.b.kf_base);
     grid.sync();
     LO_SCAN_TRACE(124);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {   // read-back block for the host; re-arm the next scan's time min/max
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // second half of the read-back block; re-arm the next scan's time min/max
         grid_fix_counters(p.kf_counters);
         if (!first) {                            // the gate's outcome becomes the state of the next scan
             s->current = current_s;
@@ -717,13 +735,6 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
             s->center[0] = current_s.t[0]; s->center[1] = current_s.t[1]; s->center[2] = current_s.t[2];
         }
         ScanReadback* out = p.readback;
-        pose_to7(s->current, out->pose);
-        out->n_planar = s->n_planar;
-        out->n_update = s->n_update;
-        out->n_query = s->n_query;
-        out->unstable = s->unstable;
-        out->outer_iterations = s->align.outer_iterations;
-        out->bootstrap = static_cast<uint32_t>(first);
         for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
         p.minmax[0] = 0xFFFFFFFFu;
         p.minmax[1] = 0u;
@@ -742,16 +753,24 @@ constexpr uint32_t kSmallScanPoints = 32768;   // scans up to this size (a VLP16
 
 using namespace lo;
 
+// Scratch of the per-scan kernel for scans of up to `n` points; called once at lo_odometry_create for a VLP16-sized scan so
+// that no submit allocates (larger scans grow it on first sight).
+int lo::fused_reserve(lo_odometry* h, uint32_t n) {
+    PipeBufs b;
+    n = std::max<uint32_t>(n, 1);
+    LO_TRY(h->fused.ensure(carve(b, nullptr, n)));
+    LO_TRY(h->deskewed.ensure(static_cast<size_t>(n) * sizeof(PointXYZIRT)));
+    LO_TRY(h->filtered.ensure(static_cast<size_t>(n) * sizeof(PointNormal)));
+    LO_TRY(h->query.ensure(static_cast<size_t>(n) * sizeof(PointXYZ)));
+    return LO_OK;
+}
+
 int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_t n) {
     lo_ctx* ctx = h->ctx;
     lo_grid* kf = h->keyframe;
     PipeBufs b;
-    const size_t bytes = carve(b, nullptr, std::max<uint32_t>(n, 1));
-    LO_TRY(h->fused.ensure(bytes));
+    LO_TRY(fused_reserve(h, n));
     carve(b, h->fused.as<char>(), std::max<uint32_t>(n, 1));
-    LO_TRY(h->deskewed.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZIRT)));
-    LO_TRY(h->filtered.ensure(std::max<size_t>(n, 1) * sizeof(PointNormal)));
-    LO_TRY(h->query.ensure(std::max<size_t>(n, 1) * sizeof(PointXYZ)));
     static int blocks_per_sm = 0;
     if (blocks_per_sm == 0) {
         int large_per_sm = 0;
@@ -765,8 +784,10 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
         }
     }
     const int blocks = std::min<int>(ctx->sm_count, kMaxPipeBlocks);   // one block per SM
-    // room for this scan's insert and for those of the scans still in flight (the host mirror of the counters is as old
-    // as the last scan waited for); may rebuild the table, so take the view afterwards
+    // Room for this scan's insert and for those of the scans whose counters have not come back yet: a scan adds at most
+    // one voxel per update point, and the update set is a subset of the planar points, themselves a subset of the scan
+    // (the host mirror of the counters is as old as the last scan adopted). With the key frame sized at creation this
+    // never grows in practice; when it does, the growth is stream-ordered (lo_grid.cu) — no synchronisation here.
     LO_TRY(grid_reserve(kf, static_cast<size_t>(n) + h->pending_points));
     ScanArgs p;
     p.s = h->d_state;
@@ -780,8 +801,9 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.kf_capacity = kf->capacity;
     p.kf_counters = kf->counters;
     p.kf_free_list = kf->free_list;
+    const uint32_t ticket_before = kf->h_counters[GC_TICKET];
     p.ticket_base = grid_take_tickets(kf, n);
-    p.seq = ++h->scan_seq;
+    p.seq = h->scan_seq + 1;
     p.readback = h->h_readback + (p.seq % kQueueDepth);   // pinned host memory (unified addressing): no D2H copy, the host polls `seq`
     p.n = n;
     p.lo2 = h->params.lidar_min_range * h->params.lidar_min_range;
@@ -797,11 +819,17 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
         p.trace = ctx->tmp_d.as<long long>();
     }
     void* kargs[] = {&p};
-    if (n <= kSmallScanPoints)
-        LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream));
-    else
-        LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel_large), dim3(blocks), dim3(kPipeThreads), kargs,
-                                            kAlignTileScratchBytes, ctx->stream));
+    const cudaError_t e =
+        n <= kSmallScanPoints
+            ? cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream)
+            : cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel_large), dim3(blocks), dim3(kPipeThreads), kargs,
+                                          kAlignTileScratchBytes, ctx->stream);
+    if (e != cudaSuccess) {   // nothing was queued: the scan number and the tickets stay where they were
+        kf->h_counters[GC_TICKET] = ticket_before;
+        set_error("launching the per-scan kernel (%d cooperative blocks of %d threads) failed: %s", blocks, kPipeThreads, cudaGetErrorString(e));
+        return LO_E_CUDA;
+    }
+    h->scan_seq = p.seq;
     ctx->launches++;
     return LO_OK;
 }

@@ -141,11 +141,32 @@ def generate_scan(scene, lidar, pos0, q0, pos1, q1, seed, noise=0.02, t_offset=0
     return out
 
 
-def vlp16_stream(n_scans, scene_seed=1234, traj_seed=99, lidar=None, scene=None):
-    """Config 2: list of XYZIRT scans plus the ground-truth poses at sweep start."""
+_POOL_JOB = None   # (scene, lidar, pos, q, scene_seed) of the stream being generated, inherited by forked workers
+
+
+def _pool_scan(k):
+    scene, lidar, pos, q, scene_seed = _POOL_JOB
+    return generate_scan(scene, lidar, pos[k], q[k], pos[k + 1], q[k + 1], scene_seed + k, t_offset=0.1 * k)
+
+
+def vlp16_stream(n_scans, scene_seed=1234, traj_seed=99, lidar=None, scene=None, workers=1):
+    """Config 2: list of XYZIRT scans plus the ground-truth poses at sweep start. The scene's length (and with it the
+    boxes drawn from the seed) follows n_scans, so streams of different lengths are different streams. workers > 1:
+    the scans (independent given the trajectory) are generated by forked worker processes — call it before CUDA is
+    initialised in this process."""
+    global _POOL_JOB
     lidar = lidar or LidarModel.vlp16()
     pos, q, _ = trajectory(n_scans + 1, traj_seed)
     scene = scene or Scene(scene_seed, length=max(60.0, pos[-1, 0] + 140.0))
+    if workers > 1 and n_scans > 1:
+        import multiprocessing as mp
+        _POOL_JOB = (scene, lidar, pos, q, scene_seed)
+        try:
+            with mp.get_context("fork").Pool(min(workers, n_scans)) as pool:
+                scans = pool.map(_pool_scan, range(n_scans), chunksize=max(1, n_scans // (4 * workers)))
+        finally:
+            _POOL_JOB = None
+        return scans, pos, q
     scans = [generate_scan(scene, lidar, pos[k], q[k], pos[k + 1], q[k + 1], scene_seed + k, t_offset=0.1 * k)
              for k in range(n_scans)]
     return scans, pos, q

@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_reference_arm_line():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "3", "--warmup", "3"], capture_output=True,
-                       text=True, cwd=ROOT, timeout=300)
+                       text=True, cwd=ROOT, timeout=300, env=dict(os.environ, LO_BENCH_NO_STEADY="1"))
     assert r.returncode == 0, r.stderr[-2000:]
     line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert line["impl"] == "reference" and line["metric"] == "registered_scans_per_sec" and line["unit"] == "scans/s"
@@ -22,6 +22,10 @@ def test_reference_arm_line():
     assert line["cpu_baseline"]["value"] == line["value"]
     assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "workload" in line["config"] and "model" not in line["config"]
+    # `config` must be the very object the product arm prints (the driver compares the two arms' configs)
+    sys.path.insert(0, ROOT)
+    import bench
+    assert line["config"] == bench.shared_config(3, 3)
 
 
 def test_product_arm_needs_a_gpu():
