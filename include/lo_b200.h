@@ -65,6 +65,8 @@ int lo_voxel_keys(lo_ctx* ctx, float voxel_size, const float* xyz16, size_t n, i
  * grows on demand. The grid keeps, per voxel, the first max_points points in arrival order (:77-93). */
 int lo_grid_create(lo_ctx* ctx, float voxel_size, size_t max_points, size_t capacity_hint, lo_grid** out);
 void lo_grid_destroy(lo_grid* g);
+/* setMaxPoints (:56-59): only the cap changes; voxels keep what they hold */
+int lo_grid_set_max_points(lo_grid* g, size_t max_points);
 /* setVoxelSize (:61-66): clears the grid */
 int lo_grid_set_voxel_size(lo_grid* g, float voxel_size);
 /* size() (:248-251): number of voxels */
@@ -98,6 +100,11 @@ typedef struct lo_pair {   /* VoxelGrid::Correspondence (:40-46) */
  * (entries of invalid queries are zero); *n_valid = number of valid correspondences. */
 int lo_grid_find_matching_pairs(lo_grid* g, const float* xyz16, size_t m, const float pose7[7], float max_dist,
                                 lo_pair* pairs, uint8_t* valid, size_t* n_valid);
+
+/* getCorrespondence (:164-204): nearest stored point among the 27 voxels around `query3` (a point in the grid's frame, no
+ * transform) with squared distance below max_correspondence_distance_sq; plane_origin / plane_normal of *out and *valid as
+ * the reference fills them, source_point_local zero (findMatchingPairs sets it, :225). */
+int lo_grid_get_correspondence(lo_grid* g, const float query3[3], double max_correspondence_distance_sq, lo_pair* out, int* valid);
 
 /* ---- residual + normal equations (src/cloud_matcher.cpp:38-103,134-154) ----------------------- */
 typedef struct lo_normal_eq {
@@ -196,6 +203,11 @@ int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const flo
  * (cloud_transform.h:15-40) with (start7, end7); out may alias in. */
 int lo_deskew(lo_ctx* ctx, const void* xyzirt32_in, size_t n, const float start7[7], const float end7[7],
               void* xyzirt32_out);
+/* utils::pointTimeNormalize alone (point_time_normalize.h:14-39); out may alias in */
+int lo_point_time_normalize(lo_ctx* ctx, const void* xyzirt32_in, size_t n, void* xyzirt32_out);
+/* CloudTransformer::transformNonRigid alone (cloud_transform.h:15-40): `time` is used as it is */
+int lo_transform_non_rigid(lo_ctx* ctx, const void* xyzirt32_in, size_t n, const float start7[7], const float end7[7],
+                           void* xyzirt32_out);
 /* transform<PointXYZ> (cloud_transform.h:42-66) */
 int lo_transform_xyz(lo_ctx* ctx, const float* xyz16_in, size_t n, const float pose7[7], float* xyz16_out);
 /* transformWithNormals (cloud_transform.h:68-97) */
@@ -205,6 +217,11 @@ int lo_range_filter(lo_ctx* ctx, const float* pn48_in, size_t n, float min_range
                     size_t* n_out);
 /* CloudClassifier::classify (cloud_classifier.h:19-168): planar points with normals, reference order */
 int lo_classify(lo_ctx* ctx, const void* xyzirt32_in, size_t n, float* pn48_planar_out, size_t cap, size_t* n_planar);
+/* the pair classify returns (cloud_classifier.h:19,167): {planar points with normals, unclassified points}. The second
+ * cloud holds the organised points that were looked at and did not become planar (intensity = curvature, :104);
+ * at most n of each. LO_E_CAPACITY if the ring x azimuth grid does not fit the scratch or an out buffer is short. */
+int lo_classify_pair(lo_ctx* ctx, const void* xyzirt32_in, size_t n, float* pn48_planar_out, size_t cap, size_t* n_planar,
+                     void* xyzirt32_unclassified_out, size_t cap_unclassified, size_t* n_unclassified);
 
 /* ---- per-point PCA normals: the test's pcl::NormalEstimation (test/test.cpp:196-205) ---------- */
 int lo_pca_normals(lo_ctx* ctx, const float* xyz16, size_t n, float radius, float* normals3_out);

@@ -74,7 +74,10 @@ SIGNATURES = {
     "lo_ctx_stream": (_vp, [_vp]), "lo_ctx_synchronize": (_i, [_vp]), "lo_ctx_kernel_launches": (C.c_uint64, [_vp]),
     "lo_voxel_keys": (_i, [_vp, _fl, _vp, _sz, _vp, _vp]),
     "lo_grid_create": (_i, [_vp, _fl, _sz, _sz, C.POINTER(_vp)]), "lo_grid_destroy": (None, [_vp]),
-    "lo_grid_set_voxel_size": (_i, [_vp, _fl]), "lo_grid_size": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz)]),
+    "lo_grid_set_voxel_size": (_i, [_vp, _fl]), "lo_grid_set_max_points": (_i, [_vp, _sz]),
+    "lo_grid_get_correspondence": (_i, [_vp, _vp, C.c_double, _vp, C.POINTER(_i)]),
+    "lo_point_time_normalize": (_i, [_vp, _vp, _sz, _vp]), "lo_transform_non_rigid": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]),
+    "lo_classify_pair": (_i, [_vp, _vp, _sz, _vp, _sz, C.POINTER(_sz), _vp, _sz, C.POINTER(_sz)]), "lo_grid_size": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz)]),
     "lo_grid_add_cloud": (_i, [_vp, _vp, _sz, _i]), "lo_grid_add_cloud_dev": (_i, [_vp, _vp, _sz, _i]),
     "lo_grid_get_cloud": (_i, [_vp, _i, _i, _vp, _sz, C.POINTER(_sz)]),
     "lo_grid_radius_cleanup": (_i, [_vp, _vp, _fl]),
@@ -188,6 +191,26 @@ class Context:
         _check(self.lib.lo_deskew(self.h, _p(cloud), len(cloud), _p(_pose7(start7)), _p(_pose7(end7)), _p(out)))
         return out
 
+    def point_time_normalize(self, cloud):
+        cloud = np.ascontiguousarray(cloud, dtype=XYZIRT)
+        out = np.empty_like(cloud)
+        _check(self.lib.lo_point_time_normalize(self.h, _p(cloud), len(cloud), _p(out)))
+        return out
+
+    def transform_non_rigid(self, cloud, start7, end7):
+        cloud = np.ascontiguousarray(cloud, dtype=XYZIRT)
+        out = np.empty_like(cloud)
+        _check(self.lib.lo_transform_non_rigid(self.h, _p(cloud), len(cloud), _p(_pose7(start7)), _p(_pose7(end7)), _p(out)))
+        return out
+
+    def classify_pair(self, cloud):
+        """CloudClassifier::classify's pair: (planar with normals, unclassified)."""
+        cloud = np.ascontiguousarray(cloud, dtype=XYZIRT)
+        planar, un = np.zeros(max(len(cloud), 1), PN), np.zeros(max(len(cloud), 1), XYZIRT)
+        n, nu = C.c_size_t(0), C.c_size_t(0)
+        _check(self.lib.lo_classify_pair(self.h, _p(cloud), len(cloud), _p(planar), len(planar), C.byref(n), _p(un), len(un), C.byref(nu)))
+        return planar[:n.value].copy(), un[:nu.value].copy()
+
     def transform_xyz(self, cloud, pose7):
         cloud = np.ascontiguousarray(cloud, dtype=XYZ)
         out = np.empty_like(cloud)
@@ -240,6 +263,16 @@ class VoxelGrid:
 
     def setVoxelSize(self, voxel_size):
         _check(self.lib.lo_grid_set_voxel_size(self.h, voxel_size))
+
+    def setMaxPoints(self, max_points):
+        _check(self.lib.lo_grid_set_max_points(self.h, max_points))
+
+    def getCorrespondence(self, query3, max_correspondence_distance_sq):
+        """VoxelGrid::getCorrespondence: (valid, plane_origin[3], plane_normal[3]) as float64."""
+        q = np.ascontiguousarray(query3, dtype=np.float32)
+        pair, valid = Pair(), C.c_int(0)
+        _check(self.lib.lo_grid_get_correspondence(self.h, _p(q), float(max_correspondence_distance_sq), C.byref(pair), C.byref(valid)))
+        return bool(valid.value), np.array(pair.plane_origin), np.array(pair.plane_normal)
 
     def addCloud(self, cloud):
         cloud = np.ascontiguousarray(cloud, dtype=PN)

@@ -202,7 +202,8 @@ struct GridView {            // passed by value to kernels
     float4* points;          // [vid * width + s]  xyz + w (w = arrival ticket while inserting)
     float4* normals;         // [vid * width + s]
     uint32_t mask;           // capacity - 1
-    uint32_t width;          // max(max_points, 1)
+    uint32_t width;          // entries per voxel slab (stride); >= cap
+    uint32_t cap;            // max(max_points, 1): a voxel accepts points while it holds fewer (voxel_grid.h:89-91)
     float voxel_size;
     uint32_t shard_rank;     // this grid keeps only the voxels whose hash range it owns (lo_grid_set_shard);
     uint32_t shard_world;    // world <= 1: unsharded

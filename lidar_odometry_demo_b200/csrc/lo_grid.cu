@@ -302,10 +302,13 @@ int grid_restore(lo_grid* g, const void* blob, size_t bytes) {
         set_error("grid snapshot: bad magic, version or size");
         return LO_E_IO;
     }
-    if (h.width != g->width || h.max_points != g->max_points) {
-        set_error("grid snapshot was taken with max_points %llu, this grid has %zu", static_cast<unsigned long long>(h.max_points), g->max_points);
+    if (h.width > g->width) LO_TRY(lo_grid_set_max_points(g, h.width));   // slabs laid out for a larger cap (setMaxPoints history)
+    if (h.width != g->width) {
+        set_error("grid snapshot was taken with max_points %llu (slab width %u), this grid has %zu (slab width %u)",
+                  static_cast<unsigned long long>(h.max_points), h.width, g->max_points, g->width);
         return LO_E_ARG;
     }
+    g->max_points = static_cast<size_t>(h.max_points);
     if (h.capacity != g->capacity) {
         Slot* fresh = nullptr;
         LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&fresh), static_cast<size_t>(h.capacity) * sizeof(Slot), ctx->stream));
@@ -397,6 +400,50 @@ extern "C" int lo_grid_set_voxel_size(lo_grid* g, float voxel_size) {
     LO_TRY(grid_clear(g));
     g->voxel_size = voxel_size;
     LO_CUDA(cudaStreamSynchronize(g->ctx->stream));
+    return LO_OK;
+}
+
+// setMaxPoints (voxel_grid.h:56-59) only stores the new cap: voxels keep what they hold, later points are appended while
+// a voxel holds fewer than the cap. A larger cap than the slabs were laid out for re-lays them out (stream-ordered).
+__global__ void grid_relayout_kernel(const float4* __restrict__ old_p, const float4* __restrict__ old_n, uint32_t old_w, float4* __restrict__ new_p,
+                                     float4* __restrict__ new_n, uint32_t new_w, size_t n_new) {
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_new; i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t vid = i / new_w;
+        const uint32_t e = static_cast<uint32_t>(i % new_w);
+        const uint32_t free_bits = 0xFFFFFFFFu;
+        float4 p = make_float4(__uint_as_float(free_bits), __uint_as_float(free_bits), __uint_as_float(free_bits), __uint_as_float(free_bits));
+        float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e < old_w) {
+            p = old_p[vid * old_w + e];
+            nv = old_n[vid * old_w + e];
+        }
+        new_p[i] = p;
+        new_n[i] = nv;
+    }
+}
+
+extern "C" int lo_grid_set_max_points(lo_grid* g, size_t max_points) {
+    if (!g) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const uint32_t want = static_cast<uint32_t>(std::min<size_t>(max_points ? max_points : 1, 1u << 16));
+    if (want > g->width) {
+        float4 *np = nullptr, *nn = nullptr;
+        const size_t n_new = static_cast<size_t>(g->payload_cap) * want;
+        LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&np), n_new * sizeof(float4), ctx->stream));
+        LO_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&nn), n_new * sizeof(float4), ctx->stream));
+        grid_relayout_kernel<<<std::max(1u, std::min<unsigned>(blocks_for(n_new, 256), ctx->sm_count * 16)), 256, 0, ctx->stream>>>(
+            g->points, g->normals, g->width, np, nn, want, n_new);
+        LO_LAUNCHED(ctx);
+        LO_CUDA(cudaFreeAsync(g->points, ctx->stream));
+        LO_CUDA(cudaFreeAsync(g->normals, ctx->stream));
+        g->points = np;
+        g->normals = nn;
+        g->width = want;
+        g->grow_count++;
+    }
+    g->max_points = max_points;
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
     return LO_OK;
 }
 

@@ -92,7 +92,7 @@ __device__ inline void grid_chain_item(uint32_t i, uint32_t ticket_base, const G
     base_of[i] = base;
     uint32_t carry = ticket_base + i;
     uint32_t* lane_w = reinterpret_cast<uint32_t*>(g.points + static_cast<size_t>(vid) * g.width) + 3;
-    for (uint32_t e = base; e < g.width; e++) {
+    for (uint32_t e = base; e < g.cap; e++) {
         const uint32_t old = atomicMin(lane_w + 4 * e, carry);
         if (old == kInvalid) break;     // entry was free: carry placed, nothing displaced
         if (old > carry) carry = old;   // carry placed, the displaced ticket moves on
@@ -108,7 +108,7 @@ __device__ inline void grid_write_item(uint32_t i, const PointSource& src, uint3
     const uint32_t vid = g.slots[s].vid;
     const uint32_t ticket = ticket_base + i;
     float4* slab = g.points + static_cast<size_t>(vid) * g.width;
-    for (uint32_t e = base_of[i]; e < g.width; e++) {
+    for (uint32_t e = base_of[i]; e < g.cap; e++) {
         const uint32_t w = __float_as_uint(slab[e].w);
         if (w == ticket) {
             float p[3], nrm[3];

@@ -95,7 +95,7 @@ struct lo_grid {
     float voxel_size = 0.5f;
     size_t max_points = 10;
     uint32_t shard_rank = 0, shard_world = 1;  // lo_grid_set_shard
-    uint32_t width = 10;         // max(max_points, 1)
+    uint32_t width = 10;         // slab stride: the largest max(max_points, 1) the grid has had
     uint32_t capacity = 0;       // slots (power of two)
     uint32_t payload_cap = 0;    // payload ids allocated
     lo::Slot* slots = nullptr;
@@ -112,6 +112,7 @@ struct lo_grid {
         lo::GridView v;
         v.slots = slots; v.points = points; v.normals = normals;
         v.mask = capacity - 1; v.width = width; v.voxel_size = voxel_size;
+        v.cap = static_cast<uint32_t>(max_points ? (max_points < width ? max_points : width) : 1);
         v.shard_rank = shard_rank; v.shard_world = shard_world;
         return v;
     }

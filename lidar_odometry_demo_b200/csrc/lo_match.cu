@@ -7,6 +7,7 @@
 //                          no host round trip until the final pose
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 
@@ -255,6 +256,38 @@ extern "C" int lo_grid_find_matching_pairs(lo_grid* g, const float* xyz16, size_
     LO_CUDA(cudaMemcpyAsync(&h_n, d_n, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
     if (n_valid) *n_valid = h_n;
+    return LO_OK;
+}
+
+// VoxelGrid::getCorrespondence (src/voxel_grid.h:164-204): one query, already in the grid's frame. The reference compares the
+// float squared distance, widened to double, with the double bound: d2 < T. For a float d2 that is d2 < (T rounded UP to
+// float), which is what the kernel's float comparison gets.
+extern "C" int lo_grid_get_correspondence(lo_grid* g, const float query3[3], double max_correspondence_distance_sq, lo_pair* out, int* valid) {
+    if (!g || !query3 || !out || !valid) return LO_E_ARG;
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    float bound = static_cast<float>(max_correspondence_distance_sq);
+    if (static_cast<double>(bound) < max_correspondence_distance_sq) bound = nextafterf(bound, INFINITY);
+    if (!(max_correspondence_distance_sq > 0.0)) bound = 0.f;   // nothing is nearer than a non-positive (or NaN) bound
+    const float q4[4] = {query3[0], query3[1], query3[2], 1.f};
+    LO_TRY(stage_queries(ctx, q4, 1));
+    LO_TRY(ctx->out_a.ensure(sizeof(lo_pair)));
+    LO_TRY(ctx->out_b.ensure(16));
+    uint32_t* d_n = ctx->small.as<uint32_t>();
+    LO_CUDA(cudaMemsetAsync(d_n, 0, sizeof(uint32_t), ctx->stream));
+    QueryTransform tf;   // identity, exact: 1*x + 0*y + 0*z + 0
+    for (int k = 0; k < 9; k++) tf.r[k] = (k % 4 == 0) ? 1.0 : 0.0;
+    tf.t[0] = tf.t[1] = tf.t[2] = 0.0;
+    find_pairs_kernel<<<1, 32, 0, ctx->stream>>>(g->view(), ctx->in_a.as<PointXYZ>(), 1u, tf, bound, ctx->out_a.as<lo_pair>(),
+                                                 ctx->out_b.as<uint8_t>(), d_n);
+    LO_LAUNCHED(ctx);
+    uint8_t v = 0;
+    LO_CUDA(cudaMemcpyAsync(out, ctx->out_a.p, sizeof(lo_pair), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(&v, ctx->out_b.p, 1, cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    *valid = v ? 1 : 0;
+    // Correspondence::source_point_local is left default-constructed by getCorrespondence (findMatchingPairs fills it, :225)
+    out->source_point_local[0] = out->source_point_local[1] = out->source_point_local[2] = 0.0;
     return LO_OK;
 }
 

@@ -46,6 +46,19 @@ __global__ void deskew_kernel(const PointXYZIRT* __restrict__ in, uint32_t n, co
     reinterpret_cast<float4*>(out)[2 * i + 1] = b;
 }
 
+// utils::pointTimeNormalize alone (point_time_normalize.h:31-36): time <- (time - min) / (max - min), everything else copied
+__global__ void time_normalize_kernel(const PointXYZIRT* __restrict__ in, uint32_t n, const uint32_t* __restrict__ minmax,
+                                      PointXYZIRT* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float t_min = time_min_of(minmax), range = time_max_of(minmax) - t_min;
+    const float4 a = reinterpret_cast<const float4*>(in)[2 * i];
+    float4 b = reinterpret_cast<const float4*>(in)[2 * i + 1];
+    b.z = (b.z - t_min) / range;
+    reinterpret_cast<float4*>(out)[2 * i] = a;
+    reinterpret_cast<float4*>(out)[2 * i + 1] = b;
+}
+
 int deskew_dev(lo_ctx* ctx, const PointXYZIRT* d_in, uint32_t n, const Pose* d_start, const Pose* d_end, PointXYZIRT* d_out) {
     if (n == 0) return LO_OK;
     uint32_t* d_minmax = ctx->small.as<uint32_t>() + 128;
@@ -246,6 +259,45 @@ __global__ void planar_scatter_kernel(uint32_t cell_cap, const float4* __restric
     }
 }
 
+// the second element of classify's pair (:156,160-162): cells of rays >= 1 inside the normals window that did not become
+// planar points and whose curvature is below intensity_max
+__global__ void unclassified_flag_kernel(const uint32_t* __restrict__ layout, const float4* __restrict__ cellp, const float* __restrict__ curv,
+                                         uint32_t cell_cap, uint32_t* __restrict__ flags) {
+    const uint32_t W = layout[0], H = layout[1];
+    const uint32_t total = layout[2] ? 0u : W * H;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < cell_cap; c += gridDim.x * blockDim.x) {
+        uint32_t flag = 0;
+        if (c < total) {
+            const uint32_t ray = c / W, col = c % W;
+            if (ray >= 1 && col >= 4 && col + 4 < W) {
+                float nv[3];
+                flag = (!cell_planar(c, W, cellp, curv, nv) && curv[c] < 1000.0f) ? 1u : 0u;
+            }
+        }
+        flags[c] = flag;
+    }
+}
+
+__global__ void unclassified_scatter_kernel(uint32_t cell_cap, const PointXYZIRT* __restrict__ in, const uint32_t* __restrict__ cell_idx,
+                                            const float* __restrict__ curv, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ offsets,
+                                            PointXYZIRT* __restrict__ out, uint32_t* __restrict__ count) {
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < cell_cap; c += gridDim.x * blockDim.x) {
+        if (flags[c]) {
+            const uint32_t idx = cell_idx[c];
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;   // PointType(): value-initialised
+            if (idx) {
+                a = reinterpret_cast<const float4*>(in)[2 * (idx - 1)];
+                b = reinterpret_cast<const float4*>(in)[2 * (idx - 1) + 1];
+            }
+            b.x = curv[c];   // the curvature pass wrote it into `intensity` (:104)
+            float4* o = reinterpret_cast<float4*>(out + offsets[c]);
+            o[0] = a;
+            o[1] = b;
+        }
+        if (c == cell_cap - 1) *count = offsets[c] + flags[c];
+    }
+}
+
 struct ClassifyScratch {
     uint32_t *hist, *row_of, *layout, *cell_idx, *flags, *offsets;
     float4 *cellp, *normals;
@@ -253,8 +305,10 @@ struct ClassifyScratch {
 };
 
 int classify_dev(lo_ctx* ctx, const PointXYZIRT* d_in, uint32_t n, int filter, float min_range, float max_range, PointNormal* d_out,
-                 uint32_t* d_count) {
+                 uint32_t* d_count, PointXYZIRT* d_unclassified, uint32_t* d_count_unclassified, uint32_t* d_overflow) {
     LO_CUDA(cudaMemsetAsync(d_count, 0, sizeof(uint32_t), ctx->stream));
+    if (d_count_unclassified) LO_CUDA(cudaMemsetAsync(d_count_unclassified, 0, sizeof(uint32_t), ctx->stream));
+    if (d_overflow) LO_CUDA(cudaMemsetAsync(d_overflow, 0, sizeof(uint32_t), ctx->stream));
     if (n == 0) return LO_OK;
     const uint32_t cell_cap = std::max<uint32_t>(8u * n, 65536u);
     // scratch carved out of tmp_a: hist[256] row_of[256] layout[4] | cell_idx | flags | offsets | curv | cellp | normals
@@ -288,6 +342,15 @@ int classify_dev(lo_ctx* ctx, const PointXYZIRT* d_in, uint32_t n, int filter, f
     LO_TRY(exclusive_scan(ctx, s.flags, s.offsets, cell_cap));
     planar_scatter_kernel<<<wide, 256, 0, ctx->stream>>>(cell_cap, s.cellp, s.normals, s.flags, s.offsets, d_out, d_count);
     LO_LAUNCHED(ctx);
+    if (d_unclassified && d_count_unclassified) {
+        unclassified_flag_kernel<<<wide, 256, 0, ctx->stream>>>(s.layout, s.cellp, s.curv, cell_cap, s.flags);
+        LO_LAUNCHED(ctx);
+        LO_TRY(exclusive_scan(ctx, s.flags, s.offsets, cell_cap));
+        unclassified_scatter_kernel<<<wide, 256, 0, ctx->stream>>>(cell_cap, d_in, s.cell_idx, s.curv, s.flags, s.offsets, d_unclassified,
+                                                                   d_count_unclassified);
+        LO_LAUNCHED(ctx);
+    }
+    if (d_overflow) LO_CUDA(cudaMemcpyAsync(d_overflow, s.layout + 2, sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     return LO_OK;
 }
 
@@ -317,6 +380,52 @@ extern "C" int lo_deskew(lo_ctx* ctx, const void* in, size_t n, const float star
     LO_TRY(stage_pose(ctx, end7, 1, &de));
     LO_CUDA(cudaMemcpyAsync(ctx->in_a.p, in, bytes, cudaMemcpyHostToDevice, ctx->stream));
     LO_TRY(deskew_dev(ctx, ctx->in_a.as<PointXYZIRT>(), static_cast<uint32_t>(n), ds, de, ctx->out_a.as<PointXYZIRT>()));
+    LO_CUDA(cudaMemcpyAsync(out, ctx->out_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return LO_OK;
+}
+
+extern "C" int lo_point_time_normalize(lo_ctx* ctx, const void* in, size_t n, void* out) {
+    if (!ctx || (!in && n) || (!out && n)) return LO_E_ARG;
+    if (n == 0) return LO_OK;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const size_t bytes = n * sizeof(PointXYZIRT);
+    LO_TRY(ctx->in_a.ensure(bytes));
+    LO_TRY(ctx->out_a.ensure(bytes));
+    uint32_t* d_minmax = ctx->small.as<uint32_t>() + 128;
+    const uint32_t init[2] = {0xFFFFFFFFu, 0u};
+    LO_CUDA(cudaMemcpyAsync(d_minmax, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(ctx->in_a.p, in, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const uint32_t nn = static_cast<uint32_t>(n);
+    time_minmax_kernel<<<std::min<unsigned>(blocks_for(n, 256), static_cast<unsigned>(ctx->sm_count) * 4), 256, 0, ctx->stream>>>(
+        ctx->in_a.as<PointXYZIRT>(), nn, d_minmax);
+    LO_LAUNCHED(ctx);
+    time_normalize_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->in_a.as<PointXYZIRT>(), nn, d_minmax, ctx->out_a.as<PointXYZIRT>());
+    LO_LAUNCHED(ctx);
+    LO_CUDA(cudaMemcpyAsync(out, ctx->out_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return LO_OK;
+}
+
+// CloudTransformer::transformNonRigid on its own: the `time` field is used as it is (cloud_transform.h:26-30). The
+// deskew kernel is run with min = 0 and max = 1, for which its normalisation (t - 0) / 1 is exact.
+extern "C" int lo_transform_non_rigid(lo_ctx* ctx, const void* in, size_t n, const float start7[7], const float end7[7], void* out) {
+    if (!ctx || (!in && n) || (!out && n) || !start7 || !end7) return LO_E_ARG;
+    if (n == 0) return LO_OK;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    const size_t bytes = n * sizeof(PointXYZIRT);
+    LO_TRY(ctx->in_a.ensure(bytes));
+    LO_TRY(ctx->out_a.ensure(bytes));
+    Pose *ds, *de;
+    LO_TRY(stage_pose(ctx, start7, 0, &ds));
+    LO_TRY(stage_pose(ctx, end7, 1, &de));
+    uint32_t* d_minmax = ctx->small.as<uint32_t>() + 128;
+    const uint32_t unit[2] = {0x80000000u, 0xBF800000u};   // float_to_ordered(0.0f), float_to_ordered(1.0f)
+    LO_CUDA(cudaMemcpyAsync(d_minmax, unit, sizeof(unit), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(ctx->in_a.p, in, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    deskew_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->in_a.as<PointXYZIRT>(), static_cast<uint32_t>(n), d_minmax, ds, de,
+                                                               ctx->out_a.as<PointXYZIRT>());
+    LO_LAUNCHED(ctx);
     LO_CUDA(cudaMemcpyAsync(out, ctx->out_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
     return LO_OK;
@@ -374,22 +483,38 @@ extern "C" int lo_range_filter(lo_ctx* ctx, const float* in, size_t n, float min
     return LO_OK;
 }
 
-extern "C" int lo_classify(lo_ctx* ctx, const void* in, size_t n, float* planar_out, size_t cap, size_t* n_planar) {
+extern "C" int lo_classify_pair(lo_ctx* ctx, const void* in, size_t n, float* planar_out, size_t cap, size_t* n_planar, void* unclassified_out,
+                                size_t cap_unclassified, size_t* n_unclassified) {
     if (!ctx || (!in && n) || !n_planar) return LO_E_ARG;
     *n_planar = 0;
+    if (n_unclassified) *n_unclassified = 0;
     if (n == 0) return LO_OK;
     LO_CUDA(cudaSetDevice(ctx->device));
+    const bool want_un = n_unclassified != nullptr;
     LO_TRY(ctx->in_a.ensure(n * sizeof(PointXYZIRT)));
     LO_TRY(ctx->out_a.ensure(n * sizeof(PointNormal)));
-    uint32_t* d_count = ctx->small.as<uint32_t>() + 192;
+    if (want_un) LO_TRY(ctx->out_b.ensure(n * sizeof(PointXYZIRT)));
+    uint32_t* d_count = ctx->small.as<uint32_t>() + 192;   // [0] planar, [1] unclassified, [2] overflow
     LO_CUDA(cudaMemcpyAsync(ctx->in_a.p, in, n * sizeof(PointXYZIRT), cudaMemcpyHostToDevice, ctx->stream));
-    LO_TRY(classify_dev(ctx, ctx->in_a.as<PointXYZIRT>(), static_cast<uint32_t>(n), 0, 0.f, 0.f, ctx->out_a.as<PointNormal>(), d_count));
-    uint32_t h_count = 0;
-    LO_CUDA(cudaMemcpyAsync(&h_count, d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_TRY(classify_dev(ctx, ctx->in_a.as<PointXYZIRT>(), static_cast<uint32_t>(n), 0, 0.f, 0.f, ctx->out_a.as<PointNormal>(), d_count,
+                        want_un ? ctx->out_b.as<PointXYZIRT>() : nullptr, want_un ? d_count + 1 : nullptr, d_count + 2));
+    uint32_t h_count[3] = {0, 0, 0};
+    LO_CUDA(cudaMemcpyAsync(h_count, d_count, sizeof(h_count), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaStreamSynchronize(ctx->stream));
-    *n_planar = h_count;
-    if (h_count > cap) return LO_E_CAPACITY;
-    if (h_count && planar_out)
-        LO_CUDA(cudaMemcpy(planar_out, ctx->out_a.p, static_cast<size_t>(h_count) * sizeof(PointNormal), cudaMemcpyDeviceToHost));
+    if (h_count[2]) {   // never silently: the reference handles such a scan
+        set_error("the classifier's ring x azimuth grid (widest ring x rings present) exceeds the scratch sized for %zu points", n);
+        return LO_E_CAPACITY;
+    }
+    *n_planar = h_count[0];
+    if (want_un) *n_unclassified = h_count[1];
+    if (h_count[0] > cap || (want_un && unclassified_out && h_count[1] > cap_unclassified)) return LO_E_CAPACITY;
+    if (h_count[0] && planar_out)
+        LO_CUDA(cudaMemcpy(planar_out, ctx->out_a.p, static_cast<size_t>(h_count[0]) * sizeof(PointNormal), cudaMemcpyDeviceToHost));
+    if (want_un && h_count[1] && unclassified_out)
+        LO_CUDA(cudaMemcpy(unclassified_out, ctx->out_b.p, static_cast<size_t>(h_count[1]) * sizeof(PointXYZIRT), cudaMemcpyDeviceToHost));
     return LO_OK;
+}
+
+extern "C" int lo_classify(lo_ctx* ctx, const void* in, size_t n, float* planar_out, size_t cap, size_t* n_planar) {
+    return lo_classify_pair(ctx, in, n, planar_out, cap, n_planar, nullptr, 0, nullptr);
 }

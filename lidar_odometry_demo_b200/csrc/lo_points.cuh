@@ -16,7 +16,9 @@ int range_filter_dev(lo_ctx* ctx, const PointNormal* d_in, uint32_t n, float min
                      uint32_t* d_count);
 // CloudClassifier::classify; planar points (reference order) that also pass [min_range,max_range] when
 // filter != 0 (the pipeline fuses classify + rangeFilter). d_out must hold n records.
+// d_unclassified / d_count_unclassified (nullable): the second element of classify's pair; d_overflow (nullable): set to 1 when
+// the ring x azimuth grid does not fit the scratch (no output is produced then)
 int classify_dev(lo_ctx* ctx, const PointXYZIRT* d_in, uint32_t n, int filter, float min_range, float max_range, PointNormal* d_out,
-                 uint32_t* d_count);
+                 uint32_t* d_count, PointXYZIRT* d_unclassified = nullptr, uint32_t* d_count_unclassified = nullptr, uint32_t* d_overflow = nullptr);
 
 }  // namespace lo

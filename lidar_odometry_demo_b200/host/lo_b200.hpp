@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -47,6 +48,7 @@ inline void check(int code) {
 #ifdef LO_B200_WITH_EIGEN
 using Vector3f = Eigen::Vector3f;
 using Quaternionf = Eigen::Quaternionf;
+using Matrix3f = Eigen::Matrix3f;
 #else
 // just enough of Eigen's interface for Pose3D users: x()/y()/z()/w(), construction in Eigen's (w,x,y,z) order
 struct Vector3f {
@@ -64,6 +66,15 @@ struct Vector3f {
     void setZero() { v[0] = v[1] = v[2] = 0.f; }
     float norm() const { return std::sqrt(v[0] * v[0] + (v[1] * v[1] + v[2] * v[2])); }
 };
+struct Matrix3f {                       // row-major 3x3, Eigen's element access
+    float m[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
+    float& operator()(int r, int c) { return m[3 * r + c]; }
+    float operator()(int r, int c) const { return m[3 * r + c]; }
+    Vector3f operator*(const Vector3f& v) const {
+        return Vector3f((m[0] * v.x() + m[1] * v.y()) + m[2] * v.z(), (m[3] * v.x() + m[4] * v.y()) + m[5] * v.z(),
+                        (m[6] * v.x() + m[7] * v.y()) + m[8] * v.z());
+    }
+};
 struct Quaternionf {
     float qw = 1.f, qx = 0.f, qy = 0.f, qz = 0.f;
     Quaternionf() = default;
@@ -75,6 +86,23 @@ struct Quaternionf {
     float z() const { return qz; }
     void setIdentity() { *this = Quaternionf(); }
     float dot(const Quaternionf& o) const { return (qx * o.qx + qz * o.qz) + (qy * o.qy + qw * o.qw); }
+};
+#endif
+
+#ifdef LO_B200_WITH_ROS2
+}  // namespace lo
+#include <rclcpp/rclcpp.hpp>
+namespace lo {
+using ParameterValue = rclcpp::ParameterValue;
+#else
+// stand-in for rclcpp::ParameterValue in builds without ROS 2: a number with the same get<T>() accessor
+struct ParameterValue {
+    double v = 0.0;
+    ParameterValue() = default;
+    explicit ParameterValue(double d) : v(d) {}
+    explicit ParameterValue(int i) : v(i) {}
+    template <typename T>
+    T get() const { return static_cast<T>(v); }
 };
 #endif
 
@@ -178,7 +206,16 @@ public:
         return Pose3D(lo::Vector3f(t[0], t[1], t[2]), inv);
     }
 
-    // row-major 3x3 of Quaternionf::toRotationMatrix()
+    // Quaternionf::toRotationMatrix() by value, as src/pose_3d.h:41-44 returns it
+    lo::Matrix3f rotationMatrix() const {
+        float r[9];
+        rotationMatrix(r);
+        lo::Matrix3f out;
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) out(i, j) = r[3 * i + j];
+        return out;
+    }
+    // the same, row-major into a plain array
     void rotationMatrix(float r[9]) const {
         const float w = rotation.w(), x = rotation.x(), y = rotation.y(), z = rotation.z();
         const float tx = 2.f * x, ty = 2.f * y, tz = 2.f * z;
@@ -243,6 +280,7 @@ public:
     }
     void restore(const std::vector<uint8_t>& blob) { lo::check(lo_grid_restore(h_, blob.data(), blob.size())); }
 
+    void setMaxPoints(size_t max_points) { max_points_ = max_points; lo::check(lo_grid_set_max_points(h_, max_points)); }   // :56-59
     void setVoxelSize(float voxel_size) { voxel_size_ = voxel_size; lo::check(lo_grid_set_voxel_size(h_, voxel_size)); }
     Indices getIndices(float x, float y, float z) const {
         return {static_cast<int64_t>(x / voxel_size_), static_cast<int64_t>(y / voxel_size_), static_cast<int64_t>(z / voxel_size_)};
@@ -254,6 +292,19 @@ public:
     pcl::PointCloud<pcl::PointNormal>::Ptr getCloud(bool reference_order = true) const { return get<pcl::PointNormal>(0, reference_order); }
     pcl::PointCloud<pcl::PointXYZ>::Ptr getCloudWithoutNormals(bool reference_order = true) const { return get<pcl::PointXYZ>(1, reference_order); }
     pcl::PointCloud<pcl::PointXYZ>::Ptr getSparseCloudWithoutNormals(bool reference_order = true) const { return get<pcl::PointXYZ>(2, reference_order); }
+
+    // :164-204. `query` is a point in the grid's frame; source_point_local stays zero as in the reference.
+    Correspondence getCorrespondence(const lo::Vector3f& query, double max_correspondence_distance_sq) const {
+        const float q[3] = {query.x(), query.y(), query.z()};
+        lo_pair pair;
+        int valid = 0;
+        lo::check(lo_grid_get_correspondence(h_, q, max_correspondence_distance_sq, &pair, &valid));
+        Correspondence c;
+        c.valid = valid != 0;
+        if (c.valid) std::memcpy(c.source_point_local, pair.source_point_local, sizeof(double) * 9);
+        else std::memset(c.source_point_local, 0, sizeof(double) * 9);
+        return c;
+    }
 
     std::vector<Correspondence> findMatchingPairs(const pcl::PointCloud<pcl::PointXYZ>& cloud, const Pose3D& pose, float max_distance) const {
         const size_t m = cloud.points.size();
@@ -358,8 +409,8 @@ private:
 // ---- CloudTransformer (src/utils/cloud_transform.h:13-98) and utils:: (point_time_normalize.h, range_filter.h) ---
 class CloudTransformer {
 public:
-    // transformNonRigid (:15-40). lo_deskew fuses utils::pointTimeNormalize in front of it, as the reference calls the
-    // two back to back (src/lidar_odometry.cpp:25-30); on times already normalised to [0,1] that step is the identity.
+    // transformNonRigid (:15-40): `time` is used as the caller left it. (lo_deskew is the fused form of
+    // utils::pointTimeNormalize + transformNonRigid that src/lidar_odometry.cpp:25-30 calls back to back.)
     static pcl::PointCloud<lidar_point::PointXYZIRT>::Ptr transformNonRigid(const pcl::PointCloud<lidar_point::PointXYZIRT>& cloud, const Pose3D& start,
                                                                   const Pose3D& end, lo::Context& ctx = lo::Context::instance()) {
         auto out = std::make_shared<pcl::PointCloud<lidar_point::PointXYZIRT>>();
@@ -368,7 +419,7 @@ public:
         float s7[7], e7[7];
         start.to7(s7);
         end.to7(e7);
-        lo::check(lo_deskew(ctx.handle(), cloud.points.data(), cloud.points.size(), s7, e7, out->points.data()));
+        lo::check(lo_transform_non_rigid(ctx.handle(), cloud.points.data(), cloud.points.size(), s7, e7, out->points.data()));
         return out;
     }
     static pcl::PointCloud<pcl::PointXYZ>::Ptr transform(const pcl::PointCloud<pcl::PointXYZ>& cloud, const Pose3D& pose,
@@ -396,6 +447,17 @@ public:
 };
 
 namespace utils {
+// pointTimeNormalize (src/utils/point_time_normalize.h:14-39); the reference's template is only ever instantiated for
+// lidar_point::PointXYZIRT (src/lidar_odometry.cpp:25)
+template <typename PointType>
+inline typename pcl::PointCloud<PointType>::Ptr pointTimeNormalize(const pcl::PointCloud<PointType>& input, lo::Context& ctx = lo::Context::instance()) {
+    static_assert(sizeof(PointType) == 32, "pointTimeNormalize takes lidar_point::PointXYZIRT records");
+    auto out = std::make_shared<pcl::PointCloud<PointType>>();
+    out->points.resize(input.points.size());
+    out->width = static_cast<uint32_t>(input.points.size());
+    lo::check(lo_point_time_normalize(ctx.handle(), input.points.data(), input.points.size(), out->points.data()));
+    return out;
+}
 inline pcl::PointCloud<pcl::PointNormal>::Ptr rangeFilter(const pcl::PointCloud<pcl::PointNormal>& cloud, float min_range, float max_range,
                                                            lo::Context& ctx = lo::Context::instance()) {
     auto out = std::make_shared<pcl::PointCloud<pcl::PointNormal>>();
@@ -409,19 +471,26 @@ inline pcl::PointCloud<pcl::PointNormal>::Ptr rangeFilter(const pcl::PointCloud<
 }
 }  // namespace utils
 
-// CloudClassifier::classify (src/utils/cloud_classifier.h:19-168): planar points with normals
+// CloudClassifier::classify (src/utils/cloud_classifier.h:19-168): {planar points with normals, unclassified points}
 class CloudClassifier {
 public:
-    static pcl::PointCloud<pcl::PointNormal>::Ptr classify(const pcl::PointCloud<lidar_point::PointXYZIRT>& cloud,
-                                                            lo::Context& ctx = lo::Context::instance()) {
-        auto out = std::make_shared<pcl::PointCloud<pcl::PointNormal>>();
-        out->points.resize(cloud.points.size() ? cloud.points.size() : 1);
-        size_t n = 0;
-        lo::check(lo_classify(ctx.handle(), cloud.points.data(), cloud.points.size(), reinterpret_cast<float*>(out->points.data()),
-                              out->points.size(), &n));
-        out->points.resize(n);
-        out->width = static_cast<uint32_t>(n);
-        return out;
+    template <typename PointType>
+    static std::pair<pcl::PointCloud<pcl::PointNormal>::Ptr, typename pcl::PointCloud<PointType>::Ptr> classify(
+        const pcl::PointCloud<PointType>& cloud, lo::Context& ctx = lo::Context::instance()) {
+        static_assert(sizeof(PointType) == 32, "classify takes lidar_point::PointXYZIRT records");
+        auto planar = std::make_shared<pcl::PointCloud<pcl::PointNormal>>();
+        auto unclassified = std::make_shared<pcl::PointCloud<PointType>>();
+        const size_t cap = cloud.points.size() ? cloud.points.size() : 1;
+        planar->points.resize(cap);
+        unclassified->points.resize(cap);
+        size_t n = 0, nu = 0;
+        lo::check(lo_classify_pair(ctx.handle(), cloud.points.data(), cloud.points.size(), reinterpret_cast<float*>(planar->points.data()), cap, &n,
+                                   unclassified->points.data(), cap, &nu));
+        planar->points.resize(n);
+        planar->width = static_cast<uint32_t>(n);
+        unclassified->points.resize(nu);
+        unclassified->width = static_cast<uint32_t>(nu);
+        return {planar, unclassified};
     }
 };
 
@@ -436,6 +505,26 @@ public:
         size_t keyframe_max_points_cnt = 20;
         float keyframe_matching_voxel_size = 0.3f, keyframe_update_voxel_size = 0.1f, keyframe_cleanup_range = 80.0f,
               angular_divergence_threshold = 5.0f;
+        // the reference's parameter plumbing, same names (src/lidar_odometry.h:34-62); rclcpp::ParameterValue with -DLO_B200_WITH_ROS2
+        using ROS2ParametersMap = std::map<std::string, lo::ParameterValue>;
+        static ROS2ParametersMap GetROSDeclaration() {
+            return {{"lidar_min_range", lo::ParameterValue(4.0)}, {"lidar_max_range", lo::ParameterValue(80.0)},
+                    {"keyframe_voxel_size", lo::ParameterValue(0.2)}, {"keyframe_max_points_cnt", lo::ParameterValue(20)},
+                    {"keyframe_matching_voxel_size", lo::ParameterValue(0.3)}, {"keyframe_update_voxel_size", lo::ParameterValue(0.1)},
+                    {"keyframe_cleanup_range", lo::ParameterValue(80.0)}, {"angular_divergence_threshold", lo::ParameterValue(5.0)}};
+        }
+        static Params FromROS2Params(const ROS2ParametersMap& params) {
+            Params o;
+            o.lidar_min_range = params.at("lidar_min_range").get<float>();
+            o.lidar_max_range = params.at("lidar_max_range").get<float>();
+            o.keyframe_voxel_size = params.at("keyframe_voxel_size").get<float>();
+            o.keyframe_max_points_cnt = params.at("keyframe_max_points_cnt").get<size_t>();
+            o.keyframe_matching_voxel_size = params.at("keyframe_matching_voxel_size").get<float>();
+            o.keyframe_update_voxel_size = params.at("keyframe_update_voxel_size").get<float>();
+            o.keyframe_cleanup_range = params.at("keyframe_cleanup_range").get<float>();
+            o.angular_divergence_threshold = params.at("angular_divergence_threshold").get<float>();
+            return o;
+        }
         static Params FromYaml(const std::string& path) {   // config/params.yaml layout
             lo_params p;
             lo::check(lo_params_from_yaml(path.c_str(), &p));

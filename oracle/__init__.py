@@ -66,12 +66,13 @@ class Oracle:
             "orc_grid_size": (sz, [vp]), "orc_grid_num_points": (sz, [vp]),
             "orc_grid_get_cloud": (sz, [vp, vp, sz]), "orc_grid_get_cloud_xyz": (sz, [vp, vp, sz]),
             "orc_grid_get_sparse_xyz": (sz, [vp, vp, sz]), "orc_grid_radius_cleanup": (None, [vp, vp, fl]),
+            "orc_grid_set_max_points": (None, [vp, sz]), "orc_grid_get_correspondence": (C.c_int, [vp, vp, C.c_double, vp, vp]),
             "orc_get_indices": (None, [fl, vp, sz, sz, vp]),
             "orc_hash": (C.c_uint64, [C.c_int64, C.c_int64, C.c_int64]),
             "orc_grid_find_matching_pairs": (sz, [vp, vp, sz, vp, fl, vp, vp]),
             "orc_time_normalize": (None, [vp, sz, vp]), "orc_transform_nonrigid": (None, [vp, sz, vp, vp, vp]),
             "orc_transform_xyz": (None, [vp, sz, vp, vp]), "orc_transform_with_normals": (None, [vp, sz, vp, vp]),
-            "orc_range_filter": (sz, [vp, sz, fl, fl, vp]), "orc_classify": (sz, [vp, sz, vp, vp]),
+            "orc_range_filter": (sz, [vp, sz, fl, fl, vp]), "orc_classify": (sz, [vp, sz, vp, vp]), "orc_classify_full": (sz, [vp, sz, vp, vp, vp]),
             "orc_pose_compose": (None, [vp, vp, vp]), "orc_pose_inverse": (None, [vp, vp]),
             "orc_pose_relative_to": (None, [vp, vp, vp]), "orc_pose_rotation_matrix": (None, [vp, vp]),
             "orc_evaluate": (None, [vp, sz, vp, vp, vp, vp, vp, vp, vp]),
@@ -138,6 +139,14 @@ class Oracle:
         nun = C.c_size_t(0)
         n = self.L.orc_classify(_p(cloud), len(cloud), _p(out), C.byref(nun))
         return out[:n].copy(), int(nun.value)
+
+    def classify_full(self, cloud):
+        """CloudClassifier::classify's pair: (planar with normals, unclassified points with intensity = curvature)."""
+        cloud = np.ascontiguousarray(cloud, dtype=XYZIRT)
+        out, un = np.zeros(max(len(cloud), 1), PN), np.zeros(max(len(cloud), 1), XYZIRT)
+        nun = C.c_size_t(0)
+        n = self.L.orc_classify_full(_p(cloud), len(cloud), _p(out), _p(un), C.byref(nun))
+        return out[:n].copy(), un[:nun.value].copy()
 
     def pose_compose(self, a, b):
         out = np.empty(7, np.float32)
@@ -244,6 +253,15 @@ class OracleGrid:
     def radius_cleanup(self, center, radius):
         c = np.ascontiguousarray(center, dtype=np.float32)
         self.o.L.orc_grid_radius_cleanup(self.h, _p(c), radius)
+
+    def set_max_points(self, max_points):
+        self.o.L.orc_grid_set_max_points(self.h, max_points)
+
+    def get_correspondence(self, query3, max_sq):
+        q = np.ascontiguousarray(query3, dtype=np.float32)
+        o, nv = np.zeros(3), np.zeros(3)
+        ok = self.o.L.orc_grid_get_correspondence(self.h, _p(q), float(max_sq), _p(o), _p(nv))
+        return bool(ok), o, nv
 
     def find_matching_pairs(self, cloud, pose7, max_dist=0.3):
         cloud = np.ascontiguousarray(cloud, dtype=XYZ)

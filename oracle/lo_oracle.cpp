@@ -204,6 +204,7 @@ public:
 
     float voxel_size() const { return voxel_size_; }
     size_t size() const { return index_.size(); }
+    void set_max_points(size_t m) { max_points_ = m; }   // voxel_grid.h:56-59
 
     void add(float x, float y, float z, float nx, float ny, float nz) {  // voxel_grid.h:77-110
         const Key k = key_of(x, y, z, voxel_size_);
@@ -478,7 +479,7 @@ namespace port {
 // The reference calls atan2/sqrt/powf unqualified on floats; this restatement (and the oracle/_ref
 // build, which includes <math.h> first) resolves them to the float overloads, as a translation unit
 // that has seen libstdc++'s <math.h> does. See DESIGN.md "numerics".
-inline size_t classify(const OrcXYZIRT* in, size_t n, OrcPN* planar_out, size_t* n_unclassified) {
+inline size_t classify(const OrcXYZIRT* in, size_t n, OrcPN* planar_out, size_t* n_unclassified, OrcXYZIRT* unclassified_out = nullptr) {
     // :21-31 group by ring (narrowed to uint8_t), input order kept inside a ring
     std::map<uint8_t, std::vector<OrcXYZIRT>> rings;
     for (size_t i = 0; i < n; i++) rings[static_cast<uint8_t>(in[i].ring)].push_back(in[i]);
@@ -557,9 +558,11 @@ inline size_t classify(const OrcXYZIRT* in, size_t n, OrcPN* planar_out, size_t*
                     o.nx = nrm[0]; o.ny = nrm[1]; o.nz = nrm[2];
                     planar_out[n_planar++] = o;
                 } else {
+                    if (unclassified_out) unclassified_out[n_other] = p;   // :156 the organised point, intensity = curvature
                     n_other++;
                 }
             } else if (p.intensity < intensity_max) {
+                if (unclassified_out) unclassified_out[n_other] = p;       // :160-162
                 n_other++;
             }
         }
@@ -744,6 +747,28 @@ extern "C" void orc_get_indices(float voxel_size, const float* xyz, size_t strid
 }
 extern "C" uint64_t orc_hash(int64_t ix, int64_t iy, int64_t iz) { return port::hash_of({ix, iy, iz}); }
 
+extern "C" void orc_grid_set_max_points(void* g, size_t max_points) { static_cast<Grid*>(g)->set_max_points(max_points); }
+// getCorrespondence (voxel_grid.h:164-204) for one query in the grid's frame: the per-query code of findMatchingPairs under
+// the identity transform (exact), with the double bound T turned into the float bound that decides the same: d2 < T for a
+// float d2 <=> d2 < T rounded up to float.
+extern "C" int orc_grid_get_correspondence(const void* g, const float q3[3], double max_sq, double origin3[3], double normal3[3]) {
+    const auto* grid = static_cast<const Grid*>(g);
+    float bound = static_cast<float>(max_sq);
+    if (static_cast<double>(bound) < max_sq) bound = std::nextafter(bound, std::numeric_limits<float>::infinity());
+    if (!(max_sq > 0.0)) bound = 0.f;
+    const float ident[7] = {0, 0, 0, 1, 0, 0, 0};
+    float r9[9];
+    port::rotation_matrix(port::quat_of(ident), r9);
+    const OrcXYZ q = {q3[0], q3[1], q3[2], 1.f};
+    double out9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool ok = port::correspondence(*grid, r9, ident, q, bound, out9);
+    for (int k = 0; k < 3; k++) {
+        origin3[k] = ok ? out9[3 + k] : 0.0;
+        normal3[k] = ok ? out9[6 + k] : 0.0;
+    }
+    return ok ? 1 : 0;
+}
+
 extern "C" size_t orc_grid_find_matching_pairs(const void* g, const float* xyz16, size_t n, const float pose7[7],
                                                float max_dist, double* out9, uint8_t* valid) {
     const auto* grid = static_cast<const Grid*>(g);
@@ -774,6 +799,10 @@ extern "C" void orc_transform_with_normals(const float* in, size_t n, const floa
 }
 extern "C" size_t orc_range_filter(const float* in, size_t n, float mn, float mx, float* out) {
     return port::range_filter(reinterpret_cast<const OrcPN*>(in), n, mn, mx, reinterpret_cast<OrcPN*>(out));
+}
+extern "C" size_t orc_classify_full(const void* in, size_t n, float* planar_out, void* unclassified_out, size_t* n_unclassified) {
+    return port::classify(static_cast<const OrcXYZIRT*>(in), n, reinterpret_cast<OrcPN*>(planar_out), n_unclassified,
+                          static_cast<OrcXYZIRT*>(unclassified_out));
 }
 extern "C" size_t orc_classify(const void* in, size_t n, float* planar_out, size_t* n_unclassified) {
     return port::classify(static_cast<const OrcXYZIRT*>(in), n, reinterpret_cast<OrcPN*>(planar_out), n_unclassified);

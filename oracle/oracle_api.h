@@ -40,6 +40,11 @@ uint64_t orc_hash(int64_t ix, int64_t iy, int64_t iz);
 size_t orc_grid_find_matching_pairs(const void* g, const float* xyz16, size_t n, const float pose7[7],
                                     float max_dist, double* out9, uint8_t* valid);
 
+void orc_grid_set_max_points(void* g, size_t max_points);   /* setMaxPoints (voxel_grid.h:56-59) */
+/* getCorrespondence (voxel_grid.h:164-204): 1 if valid; origin / normal of the nearest stored point */
+int orc_grid_get_correspondence(const void* g, const float query3[3], double max_correspondence_distance_sq, double origin3[3],
+                                double normal3[3]);
+
 /* ---- point utilities (src/utils headers) ---- */
 void orc_time_normalize(const void* xyzirt32_in, size_t n, void* xyzirt32_out);
 void orc_transform_nonrigid(const void* xyzirt32_in, size_t n, const float start7[7], const float end7[7],
@@ -49,6 +54,8 @@ void orc_transform_with_normals(const float* pn48_in, size_t n, const float pose
 size_t orc_range_filter(const float* pn48_in, size_t n, float min_range, float max_range, float* pn48_out);
 /* CloudClassifier::classify: planar points with normals; returns #planar, *n_unclassified optional */
 size_t orc_classify(const void* xyzirt32_in, size_t n, float* pn48_planar_out, size_t* n_unclassified);
+/* the same with the second element of the returned pair (cloud_classifier.h:167): xyzirt32 records, capacity n */
+size_t orc_classify_full(const void* xyzirt32_in, size_t n, float* pn48_planar_out, void* xyzirt32_unclassified_out, size_t* n_unclassified);
 
 /* ---- Pose3D (src/pose_3d.h) ---- */
 void orc_pose_compose(const float a7[7], const float b7[7], float out7[7]);

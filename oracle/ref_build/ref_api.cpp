@@ -95,6 +95,15 @@ extern "C" void orc_get_indices(float voxel_size, const float* xyz, size_t strid
 extern "C" uint64_t orc_hash(int64_t ix, int64_t iy, int64_t iz) {
     return VoxelGrid::IndicesHash()(VoxelGrid::Indices{ix, iy, iz});
 }
+extern "C" void orc_grid_set_max_points(void* g, size_t max_points) { static_cast<VoxelGrid*>(g)->setMaxPoints(max_points); }
+extern "C" int orc_grid_get_correspondence(const void* g, const float q3[3], double max_sq, double origin3[3], double normal3[3]) {
+    const auto c = static_cast<const VoxelGrid*>(g)->getCorrespondence(Eigen::Vector3f(q3[0], q3[1], q3[2]), max_sq);   // voxel_grid.h:164
+    for (int k = 0; k < 3; k++) {
+        origin3[k] = c.valid ? c.plane_origin(k) : 0.0;
+        normal3[k] = c.valid ? c.plane_normal(k) : 0.0;
+    }
+    return c.valid ? 1 : 0;
+}
 extern "C" size_t orc_grid_find_matching_pairs(const void* g, const float* xyz16, size_t n, const float pose7[7],
                                                float max_dist, double* out9, uint8_t* valid) {
     // The reference's findMatchingPairs drops invalid queries and (with TBB) scrambles the order
@@ -148,6 +157,14 @@ extern "C" size_t orc_range_filter(const float* in, size_t n, float mn, float mx
 extern "C" size_t orc_classify(const void* in, size_t n, float* planar_out, size_t* n_unclassified) {
     auto [planar, unclassified] = CloudClassifier::classify(to_cloud<lidar_point::PointXYZIRT>(in, n));
     if (n_unclassified) *n_unclassified = unclassified->size();
+    return from_cloud(*planar, planar_out, n);
+}
+
+extern "C" size_t orc_classify_full(const void* in, size_t n, float* planar_out, void* unclassified_out, size_t* n_unclassified) {
+    auto [planar, unclassified] = CloudClassifier::classify(to_cloud<lidar_point::PointXYZIRT>(in, n));   // cloud_classifier.h:167
+    if (n_unclassified) *n_unclassified = unclassified->size();
+    if (unclassified_out && !unclassified->points.empty())
+        std::memcpy(unclassified_out, unclassified->points.data(), unclassified->points.size() * sizeof(lidar_point::PointXYZIRT));
     return from_cloud(*planar, planar_out, n);
 }
 
