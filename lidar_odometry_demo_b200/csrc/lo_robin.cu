@@ -8,9 +8,14 @@
 //   iteration = ascending bucket position; robin-hood probing keeps elements sorted by ideal bucket, so
 //   the order is "by b", ties (same ideal bucket) in a history-dependent order, and a cluster that runs
 //   past the last bucket wraps to the front.
-// Round 1 implementation: sort by (b, arrival ticket) and rotate the wrapped tail to the front. Ties are
-// emitted in arrival order, which is exact unless a later insertion displaced through the tie group
-// (DESIGN.md "robin order" quantifies the residual mismatch against the oracle).
+// The order inside a tie group depends on the whole insertion history (an insertion into an earlier group of the same
+// cluster moves the first element of every following group to that group's end, and every growth re-inserts the
+// elements in the old iteration order), so this export REPLAYS the history: the voxels are sorted by the arrival ticket
+// of their first point (= the order in which the reference created them) and one thread runs tsl::robin_hash's own
+// insertion / rehash procedure (robin_hash.h:1219-1341,1379-1403) over 4-byte bucket records in HBM; the bucket array is
+// then walked in order. Exact for any key set, wrap-around and growth included (tests/test_gpu_robin.py compares with
+// the real tsl::robin_map on random and adversarial key sets). A sequential pass of ~2 n dependent look-ups: this is the
+// VoxelGrid::getCloud* API path (and the stage-by-stage pipeline), not the per-scan kernel.
 #include <cub/cub.cuh>
 
 #include "lo_host.h"
@@ -18,35 +23,108 @@
 namespace lo {
 
 __global__ void robin_keys_kernel(GridView g, uint32_t capacity, const uint32_t* __restrict__ counters,
-                                  unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ cursor) {
+                                  unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ cursor,
+                                  uint32_t* __restrict__ hash_of_slot) {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= capacity) return;
     const Slot slot = g.slots[s];
     if (slot.key == kKeyEmpty || slot.key == kKeyTomb || slot.count == 0) return;
-    const uint32_t n = counters[GC_VOXELS];
-    uint32_t c = 2;
-    while (c < 2 * n) c <<= 1;  // 2 * pow2ceil(n)
     long long ix, iy, iz;
     unpack_key(slot.key, ix, iy, iz);
-    const uint32_t b = reference_hash22(ix, iy, iz) & (c - 1);
+    hash_of_slot[s] = reference_hash22(ix, iy, iz);
+    // the voxel's first point carries the ticket it arrived with: voxels sorted by it are in creation order
     const uint32_t ticket = __float_as_uint(g.points[static_cast<size_t>(slot.vid) * g.width].w);
     const uint32_t at = atomicAdd(cursor, 1u);
-    keys[at] = (static_cast<unsigned long long>(b) << 32) | ticket;
+    keys[at] = ticket;
     vals[at] = s;
 }
 
-// after the sort: how far does the last element sit past the end of the bucket array?
-__global__ void robin_wrap_kernel(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ counters,
-                                  int* __restrict__ max_shift) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t n = counters[GC_VOXELS];
-    if (i >= n) return;
-    const int b = static_cast<int>(keys[i] >> 32);
-    atomicMax(max_shift, b - static_cast<int>(i));
+// keys are sorted by arrival ticket: element e = e-th voxel the reference created. One thread replays the map.
+//   idx[2][cap], dist[2][cap]: two bucket arrays (current and rehash target); dist -1 = empty
+constexpr int kRobinDistLimit = 8192;   // robin_hash.h:327 DIST_FROM_IDEAL_BUCKET_LIMIT
+
+struct RobinTable {
+    int* idx;
+    int* dist;
+    uint32_t mask;
+};
+
+__device__ inline void robin_displace(RobinTable t, uint32_t ib, int carry_idx, int carry_dist, bool may_flag, bool& grow_flag) {
+    // robin_hash.h:1283-1317: the carried element takes the bucket of any element strictly closer to its ideal bucket
+    while (true) {
+        const int d = t.dist[ib];
+        if (d < 0) {
+            t.idx[ib] = carry_idx;
+            t.dist[ib] = carry_dist;
+            return;
+        }
+        if (carry_dist > d) {
+            if (may_flag && carry_dist > kRobinDistLimit) grow_flag = true;
+            const int oi = t.idx[ib];
+            t.idx[ib] = carry_idx;
+            t.dist[ib] = carry_dist;
+            carry_idx = oi;
+            carry_dist = d;
+        }
+        ib = (ib + 1) & t.mask;
+        carry_dist++;
+    }
 }
 
-__global__ void robin_rotate_kernel(const uint32_t* __restrict__ sorted_slots, GridView g, const uint32_t* __restrict__ counters,
-                                    const int* __restrict__ max_shift, int mode, uint32_t bound, uint32_t* __restrict__ slot_rot,
+__global__ void robin_replay_kernel(const unsigned long long* __restrict__ keys_sorted, const uint32_t* __restrict__ hash_of_slot,
+                                    const uint32_t* __restrict__ vals_sorted, const uint32_t* __restrict__ counters, int* __restrict__ idx2,
+                                    int* __restrict__ dist2, uint32_t cap, uint32_t* __restrict__ order) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    const uint32_t n = counters[GC_VOXELS];
+    int cur = 0;
+    RobinTable t{idx2, dist2, 0u};
+    uint32_t buckets = 0, count = 0, threshold = 0;
+    bool grow_flag = false;
+    for (uint32_t e = 0; e < n; e++) {
+        const uint32_t h = hash_of_slot[vals_sorted[e]];
+        uint32_t ib = 0;
+        int dist = 0;
+        auto probe = [&]() {   // robin_hash.h:1226-1243 (the key is known to be absent: one voxel per slot)
+            ib = h & t.mask;
+            dist = 0;
+            while (dist <= t.dist[ib]) {
+                ib = (ib + 1) & t.mask;
+                dist++;
+            }
+        };
+        if (buckets) probe();
+        while (grow_flag || dist > kRobinDistLimit || count >= threshold) {   // rehash_on_extreme_load, :1379-1403
+            const uint32_t nb = buckets ? buckets * 2 : 2;                   // power_of_two_growth_policy<2>
+            RobinTable nt{idx2 + (cur ^ 1) * static_cast<size_t>(cap), dist2 + (cur ^ 1) * static_cast<size_t>(cap), nb - 1};
+            for (uint32_t k = 0; k < nb; k++) nt.dist[k] = -1;
+            bool unused = false;
+            for (uint32_t k = 0; k < buckets; k++) {                         // rehash_impl, :1319-1341: old buckets in order
+                if (t.dist[k] < 0) continue;
+                const int el = t.idx[k];
+                robin_displace(nt, hash_of_slot[vals_sorted[el]] & nt.mask, el, 0, false, unused);
+            }
+            cur ^= 1;
+            t = nt;
+            buckets = nb;
+            threshold = static_cast<uint32_t>(static_cast<float>(nb) * 0.5f);
+            grow_flag = false;
+            probe();
+        }
+        if (t.dist[ib] < 0) {
+            t.idx[ib] = static_cast<int>(e);
+            t.dist[ib] = dist;
+        } else {
+            robin_displace(t, ib, static_cast<int>(e), dist, true, grow_flag);
+        }
+        count++;
+    }
+    uint32_t k = 0;   // iteration = ascending bucket position (robin_hash.h begin()/++)
+    for (uint32_t b = 0; b < buckets; b++)
+        if (t.dist[b] >= 0) order[k++] = static_cast<uint32_t>(t.idx[b]);
+}
+
+__global__ void robin_gather_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ vals_sorted, GridView g,
+                                    const uint32_t* __restrict__ counters, int mode, uint32_t bound, uint32_t* __restrict__ slot_rot,
                                     uint32_t* __restrict__ count_rot) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= bound) return;
@@ -55,15 +133,9 @@ __global__ void robin_rotate_kernel(const uint32_t* __restrict__ sorted_slots, G
         count_rot[i] = 0;
         return;
     }
-    uint32_t c = 2;
-    while (c < 2 * n) c <<= 1;
-    // positions are pos_i = i + max_{j<=i}(b_j - j); the last one is n-1+max_shift; everything at >= C wraps
-    const long long over = static_cast<long long>(n) + static_cast<long long>(*max_shift) - static_cast<long long>(c);
-    const uint32_t w = over > 0 ? static_cast<uint32_t>(over) : 0u;
-    const uint32_t dst = (i + w) % n;
-    const uint32_t s = sorted_slots[i];
-    slot_rot[dst] = s;
-    count_rot[dst] = (mode == 2) ? 1u : g.slots[s].count;
+    const uint32_t s = vals_sorted[order[i]];
+    slot_rot[i] = s;
+    count_rot[i] = (mode == 2) ? 1u : g.slots[s].count;
 }
 
 __global__ void robin_emit_kernel(GridView g, const uint32_t* __restrict__ counters, const uint32_t* __restrict__ slot_rot,
@@ -94,9 +166,12 @@ int robin_export_bounded(lo_grid* g, int mode, void* d_out, uint32_t* d_count, u
     lo_ctx* ctx = g->ctx;
     LO_CUDA(cudaMemsetAsync(d_count, 0, sizeof(uint32_t), ctx->stream));
     if (bound == 0 || !g->capacity) return LO_OK;
-    // scratch layout in tmp_c: keys_in | keys_out | vals_in | vals_out | slot_rot | count_rot | offsets | cursor,max_shift
+    uint32_t cap = 2;                       // buckets of the map after `bound` insertions: 2 * pow2ceil(bound)
+    while (cap < 2u * bound) cap <<= 1;
+    // scratch in tmp_c: keys_in | keys_out | vals_in | vals_out | slot_rot | count_rot | offsets | order | hash_of_slot | idx[2] | dist[2] | cursor
     const size_t kb = static_cast<size_t>(bound) * sizeof(unsigned long long), vb = static_cast<size_t>(bound) * sizeof(uint32_t);
-    LO_TRY(ctx->tmp_c.ensure(2 * kb + 5 * vb + 64));
+    const size_t hb = static_cast<size_t>(g->capacity) * sizeof(uint32_t), tb = static_cast<size_t>(cap) * sizeof(int);
+    LO_TRY(ctx->tmp_c.ensure(2 * kb + 6 * vb + hb + 4 * tb + 64));
     char* base = ctx->tmp_c.as<char>();
     auto* keys_in = reinterpret_cast<unsigned long long*>(base);
     auto* keys_out = reinterpret_cast<unsigned long long*>(base + kb);
@@ -105,26 +180,27 @@ int robin_export_bounded(lo_grid* g, int mode, void* d_out, uint32_t* d_count, u
     auto* slot_rot = vals_out + bound;
     auto* count_rot = slot_rot + bound;
     auto* offsets = count_rot + bound;
-    auto* cursor = offsets + bound;
-    int* max_shift = reinterpret_cast<int*>(cursor + 1);
+    auto* order = offsets + bound;
+    auto* hash_of_slot = order + bound;
+    int* idx2 = reinterpret_cast<int*>(hash_of_slot + g->capacity);
+    int* dist2 = idx2 + 2 * static_cast<size_t>(cap);
+    auto* cursor = reinterpret_cast<uint32_t*>(dist2 + 2 * static_cast<size_t>(cap));
     LO_CUDA(cudaMemsetAsync(keys_in, 0xFF, kb, ctx->stream));
     LO_CUDA(cudaMemsetAsync(cursor, 0, sizeof(uint32_t), ctx->stream));
-    const int neg = INT_MIN;
-    LO_CUDA(cudaMemcpyAsync(max_shift, &neg, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     const GridView v = g->view();
-    robin_keys_kernel<<<blocks_for(g->capacity, 256), 256, 0, ctx->stream>>>(v, g->capacity, g->counters, keys_in, vals_in, cursor);
+    robin_keys_kernel<<<blocks_for(g->capacity, 256), 256, 0, ctx->stream>>>(v, g->capacity, g->counters, keys_in, vals_in, cursor, hash_of_slot);
     LO_LAUNCHED(ctx);
     size_t sort_bytes = 0, scan_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys_in, keys_out, vals_in, vals_out, static_cast<int>(bound), 0, 64, ctx->stream);
     cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, count_rot, offsets, static_cast<int>(bound), ctx->stream);
     LO_TRY(ctx->tmp_d.ensure(std::max(sort_bytes, scan_bytes)));
-    LO_CUDA(cub::DeviceRadixSort::SortPairs(ctx->tmp_d.p, sort_bytes, keys_in, keys_out, vals_in, vals_out, static_cast<int>(bound), 0, 54,
+    LO_CUDA(cub::DeviceRadixSort::SortPairs(ctx->tmp_d.p, sort_bytes, keys_in, keys_out, vals_in, vals_out, static_cast<int>(bound), 0, 32,
                                             ctx->stream));
     ctx->launches += 4;  // cub's sort pipeline (histogram + onesweep passes); counted approximately
-    const unsigned blocks = blocks_for(bound, 256);
-    robin_wrap_kernel<<<blocks, 256, 0, ctx->stream>>>(keys_out, g->counters, max_shift);
+    robin_replay_kernel<<<1, 32, 0, ctx->stream>>>(keys_out, hash_of_slot, vals_out, g->counters, idx2, dist2, cap, order);
     LO_LAUNCHED(ctx);
-    robin_rotate_kernel<<<blocks, 256, 0, ctx->stream>>>(vals_out, v, g->counters, max_shift, mode, bound, slot_rot, count_rot);
+    const unsigned blocks = blocks_for(bound, 256);
+    robin_gather_kernel<<<blocks, 256, 0, ctx->stream>>>(order, vals_out, v, g->counters, mode, bound, slot_rot, count_rot);
     LO_LAUNCHED(ctx);
     LO_CUDA(cub::DeviceScan::ExclusiveSum(ctx->tmp_d.p, scan_bytes, count_rot, offsets, static_cast<int>(bound), ctx->stream));
     ctx->launches += 2;
