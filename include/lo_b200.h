@@ -123,6 +123,19 @@ int lo_nn_residual(lo_grid* g, const float* xyz16, size_t m, const float pose7[7
 int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], const double x7d[7],
                        const double prior_b[3], float max_dist, lo_normal_eq* out_host_or_null);
 
+/* The same fused pass for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). It has no counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree and no allocating library routine, copies nothing and does not synchronise: it only
+ * enqueues its two kernels on the context's stream. The per-block partial sums go to a fixed 256 KiB device array inside
+ * the library (one per GPU that loads it, held until the process exits) instead of the context's growable scratch, so:
+ *   - at most LO_NN_STATIC_MAX_QUERIES queries per call, LO_E_CAPACITY beyond that;
+ *   - every call on a device shares that array: calls that overlap on the GPU (two streams / contexts) race; calls on
+ *     one stream, one after the other, are fine (nothing is carried over from the previous call);
+ *   - d_xyz16 and d_out are DEVICE pointers the caller owns; *d_out is valid once the stream has reached that point. */
+#define LO_NN_STATIC_MAX_QUERIES (1u << 22)
+int lo_nn_residual_static_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], const double x7d[7],
+                              const double prior_b[3], float max_dist, lo_normal_eq* d_out);
+
 /* ---- CloudMatcher::align (src/cloud_matcher.h:13-17, src/cloud_matcher.cpp:105-178) ----------- */
 typedef struct lo_align_stats {
     int32_t outer_iterations;        /* 1..35 */

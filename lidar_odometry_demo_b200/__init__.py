@@ -86,6 +86,7 @@ SIGNATURES = {
     "lo_grid_find_matching_pairs": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp, C.POINTER(_sz)]),
     "lo_nn_residual": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
     "lo_nn_residual_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
+    "lo_nn_residual_static_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _fl, _vp]),
     "lo_align": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]), "lo_align_dev": (_i, [_vp, _vp, _sz, _vp, _vp, _vp]),
     "lo_grid_set_shard": (_i, [_vp, C.c_uint32, C.c_uint32]),
     "lo_shard_search_dev": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]),

@@ -323,6 +323,63 @@ extern "C" int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, con
     return LO_OK;
 }
 
+// ---- the fused NN + residual pass for callers that must not allocate (CUDA graph capture, serving loops) -------------
+// No counterpart in the reference. Same kernels as lo_nn_residual_dev, but
+// the per-block partial sums live in a file-scope device array instead of the context's growable scratch, and the result
+// goes to a device block the caller owns, so the call is launches only: no cudaMalloc / cudaFree, no copy, no
+// synchronisation. The array exists once per device for the life of the process (256 KiB); every call uses it, so two
+// calls that overlap on the GPU (different streams / contexts of one device) race. Nothing in it has to start at zero:
+// every block overwrites its whole row before the finalize kernel reads it, so a call never sees the previous call's sums.
+constexpr int kStaticNnMaxBlocks = 1024;                          // rows of 32 doubles
+static __device__ __align__(256) double g_static_nn_partials[kStaticNnMaxBlocks * 32];
+
+// In host code `g_static_nn_partials` is a host-side stand-in, not a device address: the address is asked for once per
+// device, with that device current, and handed to the kernels as an ordinary pointer.
+static int static_nn_partials(int device, double** out) {
+    constexpr int kMaxDevices = 64;
+    static double* ptr[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) {
+        set_error("lo_nn_residual_static_dev: device %d out of range (at most %d devices)", device, kMaxDevices);
+        return LO_E_ARG;
+    }
+    if (!ptr[device]) {
+        void* p = nullptr;
+        LO_CUDA(cudaGetSymbolAddress(&p, g_static_nn_partials));   // the caller made `device` current
+        ptr[device] = static_cast<double*>(p);
+    }
+    *out = ptr[device];
+    return LO_OK;
+}
+
+extern "C" int lo_nn_residual_static_dev(lo_grid* g, const void* d_xyz16, size_t m, const float pose7[7], const double x7d[7],
+                                         const double prior_b[3], float max_dist, lo_normal_eq* d_out) {
+    if (!g || (!d_xyz16 && m) || !pose7 || !x7d || !prior_b || !d_out) return LO_E_ARG;
+    if (m > LO_NN_STATIC_MAX_QUERIES) {
+        set_error("lo_nn_residual_static_dev takes at most %u queries per call (got %zu): its scratch is a fixed device array; "
+                  "split the batch or use lo_nn_residual_dev", static_cast<unsigned>(LO_NN_STATIC_MAX_QUERIES), m);
+        return LO_E_CAPACITY;
+    }
+    lo_ctx* ctx = g->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    double* partials = nullptr;
+    LO_TRY(static_nn_partials(ctx->device, &partials));
+    const QueryTransform tf = make_query_transform(pose_from7(pose7));
+    const EvalPoint ep = make_eval_point(x7d);
+    const uint32_t tiles = static_cast<uint32_t>((m + 31) / 32);
+    const int max_blocks = std::min(ctx->sm_count * 4, kStaticNnMaxBlocks);   // the same launch shape as lo_nn_residual_dev on any GPU of <= 256 SMs
+    const int blocks = std::max(1, std::min<int>(max_blocks, static_cast<int>((tiles + kNnThreads / 32 - 1) / (kNnThreads / 32))));
+    if (g->width > kTileMaxWidth)
+        nn_residual_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m),
+                                                                   tf, ep, max_dist * max_dist, partials);
+    else
+        nn_residual_tile_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16),
+                                                                        static_cast<uint32_t>(m), tf, ep, max_dist * max_dist, partials);
+    LO_LAUNCHED(ctx);
+    normal_eq_finalize_kernel<<<1, 256, 0, ctx->stream>>>(partials, blocks, ep, prior_b[0], prior_b[1], prior_b[2], d_out);
+    LO_LAUNCHED(ctx);
+    return LO_OK;
+}
+
 extern "C" int lo_nn_residual(lo_grid* g, const float* xyz16, size_t m, const float pose7[7], const double x7d[7],
                               const double prior_b[3], float max_dist, lo_normal_eq* out) {
     if (!g || (!xyz16 && m) || !out) return LO_E_ARG;
