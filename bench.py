@@ -497,8 +497,119 @@ def run_ours(args):
 
 
 def sharded_section(lo, ctx, torch, dist, rank, world, stream):
-    """BASELINE.json config 4 inside the driver's N-GPU run: see bench_sharded_map()."""
-    return None
+    """BASELINE.json config 4 inside the driver's N-GPU run: one key-frame map (50 M points on planar patches in a 1 km x 1 km
+    x 40 m volume) sharded by voxel-hash range over the N ranks, 262 144 replicated queries, one
+    CloudMatcher::align through lo_sharded_align_dev — device time, max over ranks — in its exchange variants:
+      peer_memory     exchange 1 (nearest point per query across ranks) as atomicMin into the query's home rank inside the
+                      search kernel + one cross-rank barrier + one pull; exchange 2 (32 sums) inside the LM step kernel
+      nccl_min        exchange 1 as ncclAllReduce(MIN, u64[m]), exchange 2 through peer memory
+      nccl            both through NCCL
+    plus the per-rank search pass on its own and, on rank 0, the same align against ONE table holding the whole map."""
+    points = int(os.environ.get("LO_BENCH_SHARDED_POINTS", "50000000"))
+    m_q = 262144
+    dev = torch.device("cuda", torch.cuda.current_device())
+    uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        uid = torch.from_numpy(lo.sharded_unique_id()).to(dev)
+    dist.broadcast(uid, 0)
+    native = lo.ShardedCloudMatcher(ctx, uid.cpu().numpy(), rank, world, 0.2, 20, capacity_hint=points // (6 * world))
+    single = lo.VoxelGrid(ctx, 0.2, 20, capacity_hint=points // 6) if rank == 0 else None
+    t0 = time.perf_counter()
+    chunk, made, qsel, k = 2_000_000, 0, [], 0
+    rng = np.random.default_rng(4242)
+    while made < points:   # identical on every rank; a rank keeps the voxels it owns
+        n = min(chunk, points - made)
+        pn = S.planar_patch_map(n, seed=777 + k, extent=(1000.0, 1000.0, 40.0))
+        native.grid.addCloud(pn)
+        if single is not None:
+            single.addCloud(pn)
+        take = rng.choice(len(pn), max(1, m_q * n // points), replace=False)
+        qsel.append(np.stack([pn["x"][take], pn["y"][take], pn["z"][take]], 1))
+        made += len(pn)
+        k += 1
+    q3 = np.concatenate(qsel)[:m_q]
+    # queries: map points moved by a small pose the align has to recover (1 deg about the centre of a 1 km map would move
+    # the rim by 8.7 m, far outside the 0.3 m matching radius: 0.01 deg keeps every displacement below 0.2 m)
+    ang = np.deg2rad(0.01)
+    Rz = np.array([[np.cos(ang), -np.sin(ang), 0], [np.sin(ang), np.cos(ang), 0], [0, 0, 1]])
+    c = np.array([500.0, 500.0, 20.0])
+    queries = S.to_xyz(((q3 - c) @ Rz.T + c + np.array([0.06, -0.05, 0.06])).astype(np.float32))
+    d_q = torch.from_numpy(queries.view(np.uint8).reshape(-1)).to(dev)
+    build_s = time.perf_counter() - t0
+    guess = np.array([0, 0, 0, 1, 0, 0, 0], np.float32)
+
+    def timed(call, reps=5):
+        ts = []
+        for it in range(reps + 1):
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            res = call()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            if it:
+                ts.append(e0.elapsed_time(e1))
+        t = torch.tensor([float(np.mean(ts))], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), res
+
+    out = {"nranks": world, "queries": int(len(queries))}
+    poses = {}
+    for name, fmin, fsum in (("peer_memory", 1, 1), ("nccl_min", 0, 1), ("nccl", 0, 0)):
+        try:
+            native.setFusedMin(fmin)
+            native.setFusedSum(fsum)
+        except lo.LoError as e:
+            out[name] = {"unavailable": str(e)}
+            continue
+        i0 = native.info()
+        ms, (pose, st) = timed(lambda: native.alignDevice(d_q.data_ptr(), len(queries), guess))
+        i1 = native.info()
+        poses[name] = pose
+        out[name] = {"align_ms": ms, "outer_iterations": int(st.outer_iterations), "evaluations": int(i1.evaluations),
+                     "valid_pairs_last": int(st.valid_pairs), "final_cost": float(st.final_cost),
+                     "nccl_min_allreduces_per_align": (i1.min_allreduces - i0.min_allreduces) // 6,
+                     "nccl_sum_allreduces_per_align": (i1.sum_allreduces - i0.sum_allreduces) // 6,
+                     "peer_memory_min_exchanges_per_align": (i1.min_exchanges_fused - i0.min_exchanges_fused) // 6,
+                     "host_syncs_per_align": (i1.host_syncs - i0.host_syncs) // 6, "pose": [float(v) for v in pose]}
+    # the per-rank search pass alone (what a rank does between two exchanges), max over ranks
+    d_packed = torch.empty(len(queries), dtype=torch.int64, device=dev)
+    d_hit = torch.empty(len(queries) * 4, dtype=torch.float32, device=dev)
+    ms_search, _ = timed(lambda: lo._check(ctx.lib.lo_shard_search_dev(native.grid.h, C.c_void_p(d_q.data_ptr()), len(queries),
+                                                                       guess.ctypes.data_as(C.c_void_p), C.c_float(0.3),
+                                                                       C.c_void_p(d_packed.data_ptr()), C.c_void_p(d_hit.data_ptr()))))
+    sizes = torch.tensor([native.grid.size(), native.grid.numPoints()], dtype=torch.int64, device=dev)
+    dist.all_reduce(sizes)
+    out.update({"points": int(sizes[1]), "voxels": int(sizes[0]), "search_ms_per_pass": ms_search, "map_build_s": build_s})
+    ref = poses.get("peer_memory", poses.get("nccl"))
+    out["pose_equal_across_variants"] = bool(all(np.array_equal(p.view(np.uint32), ref.view(np.uint32)) for p in poses.values()))
+    eq = torch.tensor([1], dtype=torch.int32, device=dev)
+    if rank == 0:   # the whole map in one table on one GPU: same pose, bit for bit
+        out1 = np.empty(7, np.float32)
+        st1 = lo.AlignStats()
+        ts = []
+        for it in range(4):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            lo._check(ctx.lib.lo_align_dev(single.h, C.c_void_p(d_q.data_ptr()), len(queries), guess.ctypes.data_as(C.c_void_p),
+                                           out1.ctypes.data_as(C.c_void_p), C.byref(st1)))
+            e1.record(stream)
+            torch.cuda.synchronize()
+            if it:
+                ts.append(e0.elapsed_time(e1))
+        out["single_table"] = {"align_ms": float(np.mean(ts)), "outer_iterations": int(st1.outer_iterations), "pose": [float(v) for v in out1],
+                               "note": "lo_align_dev on one GPU holding the whole map (rank 0), the same queries"}
+        out["pose_equal_to_single_table"] = bool(np.array_equal(out1.view(np.uint32), ref.view(np.uint32)))
+        single.close()
+    pb = torch.from_numpy(ref.view(np.int32).copy()).to(dev)
+    gathered = [torch.zeros_like(pb) for _ in range(world)]
+    dist.all_gather(gathered, pb)
+    out["pose_bits_equal_on_all_ranks"] = bool(all(torch.equal(g, gathered[0]) for g in gathered))
+    del eq
+    native.close()
+    return out
 
 
 def _exhaustive(flag):

@@ -193,6 +193,9 @@ typedef struct lo_sharded_info {
     int32_t nccl_version;     /* ncclGetVersion, 0 for world = 1 */
     uint64_t min_allreduces, sum_allreduces, host_syncs;   /* since creation */
     uint64_t evaluations;     /* cost / Jacobian evaluations of the last align */
+    int32_t fused_min;        /* 1: exchange 1 runs inside the search kernel over peer memory; 0: ncclAllReduce(MIN) */
+    int32_t reserved;
+    uint64_t min_exchanges_fused;   /* exchanges 1 done through peer memory since creation */
 } lo_sharded_info;
 /* rank 0 makes the id (ncclGetUniqueId) and ships it to the other ranks by whatever channel the job has */
 int lo_sharded_unique_id(uint8_t id[LO_SHARDED_ID_BYTES]);
@@ -206,6 +209,19 @@ int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out);
 /* choose exchange 2 at run time: 1 = inside the step kernel over peer memory, 0 = ncclAllReduce. Every rank must make
  * the same choice before the same align; LO_E_ARG if the peers' memory could not be mapped at creation. */
 int lo_sharded_set_fused_sum(lo_sharded* s, int enable);
+/* the same choice for exchange 1: 1 = every rank folds its packed keys into the query's home rank with atomicMin through
+ * peer memory inside the search kernel, one cross-rank barrier, one pull of the winners; 0 = ncclAllReduce(MIN, u64[m]).
+ * The peer-memory form takes at most LO_SHARDED_MAX_QUERIES (env, default 2^20) queries per align. */
+int lo_sharded_set_fused_min(lo_sharded* s, int enable);
+/* The shards of ONE process, without NCCL: `world` contexts, each with a stream of its own, on different GPUs of the box or
+ * several on one GPU (how the one-GPU test rig exercises the exchanges). out[world] receives the shards in rank order.
+ * They are driven together: lo_sharded_align_group enqueues every shard's schedule before it waits for any (a shard's
+ * kernels wait on the device for its peers). d_xyz16[k] = the replicated queries on shard k's device; out7s = world x 7. */
+int lo_sharded_create_group(lo_ctx* const* ctxs, int world, float voxel_size, size_t max_points, size_t capacity_hint, lo_sharded** out);
+int lo_sharded_align_group(lo_sharded* const* shards, int world, const void* const* d_xyz16, size_t m, const float guess7[7],
+                           float max_dist, float* out7s, lo_align_stats* stats /* nullable */);
+int lo_sharded_align_group_host(lo_sharded* const* shards, int world, const float* xyz16, size_t m, const float guess7[7],
+                                float max_dist, float* out7s, lo_align_stats* stats /* nullable */);
 int lo_sharded_align(lo_sharded* s, const float* xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
                      lo_align_stats* stats /* nullable */);
 int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],

@@ -50,7 +50,8 @@ class Params(C.Structure):
 
 class ShardedInfo(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("fused_sum", C.c_int32), ("nccl_version", C.c_int32),
-                ("min_allreduces", C.c_uint64), ("sum_allreduces", C.c_uint64), ("host_syncs", C.c_uint64), ("evaluations", C.c_uint64)]
+                ("min_allreduces", C.c_uint64), ("sum_allreduces", C.c_uint64), ("host_syncs", C.c_uint64), ("evaluations", C.c_uint64),
+                ("fused_min", C.c_int32), ("reserved", C.c_int32), ("min_exchanges_fused", C.c_uint64)]
 
 
 class KeyframeInfo(C.Structure):
@@ -94,7 +95,10 @@ SIGNATURES = {
     "lo_sharded_unique_id": (_i, [_vp]),
     "lo_sharded_create": (_i, [_vp, _vp, _i, _i, _fl, _sz, _sz, C.POINTER(_vp)]), "lo_sharded_destroy": (None, [_vp]),
     "lo_sharded_grid": (_vp, [_vp]), "lo_sharded_info_get": (_i, [_vp, _vp]),
-    "lo_sharded_set_fused_sum": (_i, [_vp, _i]),
+    "lo_sharded_set_fused_sum": (_i, [_vp, _i]), "lo_sharded_set_fused_min": (_i, [_vp, _i]),
+    "lo_sharded_create_group": (_i, [_vp, _i, _fl, _sz, _sz, _vp]),
+    "lo_sharded_align_group": (_i, [_vp, _i, _vp, _sz, _vp, _fl, _vp, _vp]),
+    "lo_sharded_align_group_host": (_i, [_vp, _i, _vp, _sz, _vp, _fl, _vp, _vp]),
     "lo_sharded_align": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]), "lo_sharded_align_dev": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp]),
     "lo_lm_create": (_vp, []), "lo_lm_destroy": (None, [_vp]), "lo_lm_begin": (_i, [_vp, _vp, _vp, _vp]),
     "lo_lm_propose": (_i, [_vp, _vp]), "lo_lm_update": (_i, [_vp, _vp]), "lo_lm_result": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
@@ -392,6 +396,9 @@ class ShardedCloudMatcher:
     def setFusedSum(self, enable):
         _check(self.lib.lo_sharded_set_fused_sum(self.h, int(bool(enable))))
 
+    def setFusedMin(self, enable):
+        _check(self.lib.lo_sharded_set_fused_min(self.h, int(bool(enable))))
+
     def info(self):
         out = ShardedInfo()
         _check(self.lib.lo_sharded_info_get(self.h, C.byref(out)))
@@ -408,6 +415,64 @@ class ShardedCloudMatcher:
         out = np.empty(7, np.float32)
         stats = AlignStats()
         _check(self.lib.lo_sharded_align_dev(self.h, C.c_void_p(device_ptr), m, _p(_pose7(position_guess7)), max_dist, _p(out), C.byref(stats)))
+        return out, stats
+
+
+class ShardedGroup:
+    """The shards of one process (lo_sharded_create_group): one Context (stream) per shard, on one GPU or several; both
+    exchanges run through peer memory, no NCCL. Driven together by align()."""
+
+    def __init__(self, ctxs, voxel_size=0.2, max_points=20, capacity_hint=0):
+        self.ctxs, self.lib, self.world = list(ctxs), ctxs[0].lib, len(ctxs)
+        arr = (C.c_void_p * self.world)(*[c.h for c in self.ctxs])
+        out = (C.c_void_p * self.world)()
+        _check(self.lib.lo_sharded_create_group(arr, self.world, voxel_size, max_points, capacity_hint, out))
+        self.h = [C.c_void_p(v) for v in out]
+        self.grids = []
+        for ctx, h in zip(self.ctxs, self.h):
+            g = VoxelGrid.__new__(VoxelGrid)          # borrowed view of the shard (owned by lo_sharded)
+            g.ctx, g.lib, g.h = ctx, ctx.lib, C.c_void_p(self.lib.lo_sharded_grid(h))
+            g.close = lambda: None
+            self.grids.append(g)
+
+    def close(self):
+        for g in getattr(self, "grids", []):
+            g.h = None
+        for ctx, h in zip(getattr(self, "ctxs", []), getattr(self, "h", [])):
+            if h and getattr(ctx, "h", None):
+                self.lib.lo_sharded_destroy(h)
+        self.h = []
+
+    def __del__(self):
+        self.close()
+
+    def addCloud(self, cloud):
+        """The replicated key-frame cloud: every shard keeps the voxels it owns."""
+        for g in self.grids:
+            g.addCloud(cloud)
+
+    def info(self, k=0):
+        out = ShardedInfo()
+        _check(self.lib.lo_sharded_info_get(self.h[k], C.byref(out)))
+        return out
+
+    def _handles(self):
+        return (C.c_void_p * self.world)(*[h.value for h in self.h])
+
+    def align(self, planar_cloud, position_guess7, max_dist=0.3):
+        """Returns (poses [world, 7] — one per shard, all alike —, stats)."""
+        cloud = np.ascontiguousarray(planar_cloud, dtype=XYZ)
+        out = np.empty((self.world, 7), np.float32)
+        stats = AlignStats()
+        _check(self.lib.lo_sharded_align_group_host(self._handles(), self.world, _p(cloud), len(cloud), _p(_pose7(position_guess7)), max_dist,
+                                                    _p(out), C.byref(stats)))
+        return out, stats
+
+    def alignDevice(self, device_ptrs, m, position_guess7, max_dist=0.3):
+        ptrs = (C.c_void_p * self.world)(*device_ptrs)
+        out = np.empty((self.world, 7), np.float32)
+        stats = AlignStats()
+        _check(self.lib.lo_sharded_align_group(self._handles(), self.world, ptrs, m, _p(_pose7(position_guess7)), max_dist, _p(out), C.byref(stats)))
         return out, stats
 
 

@@ -86,9 +86,16 @@ __host__ __device__ inline void lm_take_point(LmState& s, const double acc[kAcc]
 #pragma unroll
     for (int k = 0; k < 6; k++) s.g[k] = acc[21 + k];
     s.x_cost = acc[27];
+    // gradient_max_norm as Ceres computes it: the infinity norm of x - Plus(x, -g) over the 7 ambient coordinates
+    // (TrustRegionMinimizer::EvaluateGradientAndJacobian); s.x is the point the sums were taken at
+    const double ng[3] = {-s.g[0], -s.g[1], -s.g[2]};
+    double qp[4];
+    quaternion_plus(s.x, ng, qp);
     double gm = 0.0;
 #pragma unroll
-    for (int k = 0; k < 6; k++) gm = fmax(gm, fabs(s.g[k]));
+    for (int k = 0; k < 4; k++) gm = fmax(gm, fabs(s.x[k] - qp[k]));
+#pragma unroll
+    for (int k = 0; k < 3; k++) gm = fmax(gm, fabs(s.x[4 + k] - (s.x[4 + k] - s.g[3 + k])));
     s.grad_max = gm;
 }
 

@@ -69,6 +69,9 @@ __global__ void odom_readback_kernel(const OdomDev* s, const uint32_t* kf_counte
     out->n_query = s->n_query;
     out->unstable = s->unstable;
     out->outer_iterations = s->align.outer_iterations;
+    out->bootstrap = 0;
+    out->overflow = 0;   // the stage-by-stage classifier reports an overflow through classify_dev's own flag
+    out->pose_seq = out->seq = 0;
     for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = kf_counters[k];
 }
 

@@ -89,6 +89,8 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
         off += (bytes + 255) & ~static_cast<size_t>(255);
         return p;
     };
+    // first, at an offset that does not depend on n: the rows of exchange_sum are written by nothing else, ever
+    b.partials = reinterpret_cast<double*>(take(static_cast<size_t>(2) * kMaxPipeBlocks * 32 * 8));
     b.hist = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
     b.layout = reinterpret_cast<uint32_t*>(take(16));
     b.block_counts = reinterpret_cast<uint32_t*>(take(3 * kMaxPipeBlocks * 4));
@@ -115,7 +117,6 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.kf_base = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.pair_o = reinterpret_cast<float4*>(take(static_cast<size_t>(n) * 16));
     b.pair_n = reinterpret_cast<float4*>(take(static_cast<size_t>(n) * 16));
-    b.partials = reinterpret_cast<double*>(take(static_cast<size_t>(2) * kMaxPipeBlocks * 32 * 8));
     return off;
 }
 
@@ -670,6 +671,7 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         a.pair_o = p.b.pair_o;
         a.pair_n = p.b.pair_n;
         a.partials = p.b.partials;
+        a.epoch_base = static_cast<unsigned long long>(p.seq) << 16;   // exchange_sum: epochs are unique across the scans of a handle
         a.guess = reinterpret_cast<const float*>(&s->guess);
         a.out_pose = reinterpret_cast<float*>(&s->next);
         a.stats = &s->align;
@@ -681,9 +683,9 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         // ~6 k queries stay on the per-query search. Same winners either way (lo_tile_search.cuh).
         if constexpr (kTiled) {
             extern __shared__ __align__(16) unsigned char tile_scratch[];
-            align_device(a, grid, reinterpret_cast<TileScratch*>(tile_scratch));
+            align_device(a, reinterpret_cast<TileScratch*>(tile_scratch));
         } else {
-            align_device(a, grid);
+            align_device(a);
         }
         if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_n = static_cast<int>(p.trace[1000]);
         // every block runs the gate on the (identical) result: no grid-wide hand-over; block 0 stores the state at the end
@@ -758,7 +760,11 @@ using namespace lo;
 int lo::fused_reserve(lo_odometry* h, uint32_t n) {
     PipeBufs b;
     n = std::max<uint32_t>(n, 1);
-    LO_TRY(h->fused.ensure(carve(b, nullptr, n)));
+    const size_t fused_bytes = carve(b, nullptr, n);
+    if (h->fused.cap < fused_bytes) {   // the rows of exchange_sum live in here: their epoch words must start out as "no epoch"
+        LO_TRY(h->fused.ensure(fused_bytes));
+        LO_CUDA(cudaMemsetAsync(h->fused.p, 0, h->fused.cap, h->ctx->stream));
+    }
     LO_TRY(h->deskewed.ensure(static_cast<size_t>(n) * sizeof(PointXYZIRT)));
     LO_TRY(h->filtered.ensure(static_cast<size_t>(n) * sizeof(PointNormal)));
     LO_TRY(h->query.ensure(static_cast<size_t>(n) * sizeof(PointXYZ)));

@@ -9,10 +9,23 @@
 namespace lo {
 
 constexpr int kShardThreads = 256;
+constexpr int kMaxShardWorld = 16;
+
+// Exchange 1 fused into the search (nullable in every body below): query i has a HOME rank, i / chunk; a rank that finds a
+// stored point for it folds its packed (d2 bits, probe, slot) key into the home rank's best[] with an atomicMin through
+// peer memory (NVLink P2P, or plain device memory for shards that share a GPU). A voxel lives on exactly one rank, so keys
+// are unique across ranks and the minimum is the reference's first strict minimum in scan order (voxel_grid.h:175-190).
+struct PeerMin {
+    unsigned long long* best[kMaxShardWorld];   // best[r] = rank r's array for the buffer in use, as seen from this device
+    uint32_t chunk;                              // queries per home rank: ceil(m / world)
+};
+__device__ __forceinline__ void peer_min_push(const PeerMin* pm, uint32_t i, unsigned long long key) {
+    if (pm && key != ~0ull) atomicMin(pm->best[i / pm->chunk] + i, key);
+}
 
 __device__ __forceinline__ void shard_search_body(GridView g, const PointXYZ* __restrict__ queries, uint32_t m, const QueryTransform& tf,
                                                                       float max_d2, unsigned long long* __restrict__ packed,
-                                                                      float4* __restrict__ hit) {
+                                                                      float4* __restrict__ hit, const PeerMin* pm = nullptr) {
     __shared__ uint2 work[(kShardThreads / 32) * kWorkListStride];
     const int lane = threadIdx.x & 31;
     uint2* wl = work + (threadIdx.x >> 5) * kWorkListStride;
@@ -29,6 +42,7 @@ __device__ __forceinline__ void shard_search_body(GridView g, const PointXYZ* __
         if (lane == 0) {
             packed[qi] = h.key;
             hit[qi] = make_float4(h.o[0], h.o[1], h.o[2], __uint_as_float(h.at));
+            peer_min_push(pm, qi, h.key);
         }
     }
 }
@@ -36,7 +50,8 @@ __device__ __forceinline__ void shard_search_body(GridView g, const PointXYZ* __
 // the same with the tile search (lo_tile_search.cuh): a warp takes 32 consecutive queries
 __device__ __forceinline__ void shard_search_tile_body(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
                                                                            const QueryTransform& tf, float max_d2,
-                                                                           unsigned long long* __restrict__ packed, float4* __restrict__ hit) {
+                                                                           unsigned long long* __restrict__ packed, float4* __restrict__ hit,
+                                                                           const PeerMin* pm = nullptr) {
     __shared__ TileScratch scratch[kShardThreads / 32];
     const int lane = threadIdx.x & 31;
     TileScratch* ts = scratch + (threadIdx.x >> 5);
@@ -57,6 +72,7 @@ __device__ __forceinline__ void shard_search_tile_body(GridView g, const PointXY
             }
             packed[i] = b.key;
             hit[i] = o;
+            peer_min_push(pm, i, b.key);
         }
     }
 }

@@ -32,7 +32,6 @@
 
 namespace lo {
 
-constexpr int kMaxShardWorld = 16;
 constexpr int kEvalBlocksPerSm = 4;   // evaluate passes are latency-bound gathers: one or two queries per thread
 constexpr int kStepThreads = 256;     // (512 threads and half the partials measured no better: the sums are L2-resident)
 
@@ -45,10 +44,24 @@ struct ShardMailbox {       // lives on every rank; peers write into it through 
     ShardMail slot[2][kMaxShardWorld];
 };
 
+// One device allocation per rank, which the peers map (CUDA IPC between processes) or simply point at (shards of one
+// process): the mailbox of exchange 2, the arrival flags of the cross-rank barrier, and the two best[] buffers of the fused
+// exchange 1 (max_q packed keys each; only this rank's home range of each is used).
+constexpr size_t kSharedBarOffset = (sizeof(ShardMailbox) + 255) & ~static_cast<size_t>(255);
+constexpr size_t kSharedBestOffset = kSharedBarOffset + 256;   // uint32_t bar[2][kMaxShardWorld] = 128 B
+static_assert(2 * kMaxShardWorld * sizeof(uint32_t) <= 256, "barrier flags fit their slot");
+
 struct ShardPeers {
-    ShardMailbox* box[kMaxShardWorld];   // box[r] = rank r's mailbox as seen from this device (own one included)
-    uint32_t rank, world;
+    ShardMailbox* box[kMaxShardWorld];          // box[r] = rank r's mailbox as seen from this device (own one included)
+    uint32_t* bar[kMaxShardWorld];              // bar[r][(seq & 1) * kMaxShardWorld + sender] = seq
+    unsigned long long* best[kMaxShardWorld];   // best[r][buf * max_q + i]
+    uint32_t rank, world, max_q, pad;
 };
+__host__ __device__ inline void shard_peer_pointers(ShardPeers& p, int r, void* base) {
+    p.box[r] = static_cast<ShardMailbox*>(base);
+    p.bar[r] = reinterpret_cast<uint32_t*>(static_cast<char*>(base) + kSharedBarOffset);
+    p.best[r] = reinterpret_cast<unsigned long long*>(static_cast<char*>(base) + kSharedBestOffset);
+}
 
 struct ShardCtl {
     LmState lm;
@@ -62,7 +75,7 @@ struct ShardCtl {
     uint32_t seq;           // exchanges performed so far
     uint32_t error;         // 1: a peer did not arrive
     uint32_t evaluations;
-    uint32_t pad;
+    uint32_t bar_seq;       // cross-rank barriers passed so far
     lo_align_stats stats;
 };
 
@@ -106,6 +119,73 @@ __global__ void __launch_bounds__(kShardThreads) shard_evaluate_ctl_kernel(GridV
     if (c->done || (phase == 1 && !c->active)) return;
     const EvalPoint ep = c->ep;
     shard_evaluate_body(g, queries, m, ep, local, global, hit, partials);
+}
+
+// ---- exchange 1 without NCCL: search + atomicMin into the home rank's best[] | barrier | pull ------------------------------
+__global__ void __launch_bounds__(kShardThreads) shard_search_peer_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+                                                                           const ShardCtl* __restrict__ c, float max_d2, int tiled,
+                                                                           unsigned long long* __restrict__ packed, float4* __restrict__ hit, PeerMin pm) {
+    if (c->done) return;
+    const QueryTransform tf = c->tf;
+    if (tiled) shard_search_tile_body(g, queries, m, tf, max_d2, packed, hit, &pm);
+    else shard_search_body(g, queries, m, tf, max_d2, packed, hit, &pm);
+}
+
+// Cross-rank barrier, one block: my arrival into every peer's flag array, then wait for theirs in mine. Everything this
+// rank's earlier kernels wrote through peer memory (the atomicMins of the search) is out before the flags go. Two flag
+// sets alternate: a peer can be one barrier ahead of me, never two (it needs my next arrival for that).
+__global__ void shard_barrier_kernel(ShardCtl* c, ShardPeers peers, int always, long long timeout_cycles) {
+    __shared__ uint32_t seq_s;
+    __shared__ int late_s;
+    if (!always && c->done) return;   // identical on every rank
+    if (threadIdx.x == 0) {
+        seq_s = c->bar_seq + 1;
+        c->bar_seq = seq_s;
+        late_s = 0;
+    }
+    __syncthreads();
+    const uint32_t seq = seq_s, set = (seq & 1u) * kMaxShardWorld, me = peers.rank;
+    __threadfence_system();
+    if (threadIdx.x < peers.world && threadIdx.x != me) {
+        *reinterpret_cast<volatile uint32_t*>(peers.bar[threadIdx.x] + set + me) = seq;
+        const volatile uint32_t* flag = peers.bar[me] + set + threadIdx.x;
+        const long long t0 = clock64();
+        while (*flag != seq) {
+            if (clock64() - t0 > timeout_cycles) {
+                late_s = 1;
+                break;
+            }
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (late_s && threadIdx.x == 0) {   // a peer is gone: stop this rank's schedule instead of hanging the stream
+        c->error = 1;
+        c->done = 1;
+    }
+}
+
+// After the barrier: the winners of all queries from their home ranks' best[] (coalesced reads over NVLink, m x 8 B in
+// all) into this rank's `global` array, which the evaluate passes compare with `local` exactly as after the NCCL MIN;
+// and this rank's home range of the OTHER buffer back to "none" for the next outer iteration (nobody touches that buffer
+// before the step kernel's exchange of this iteration, which every rank enters after this kernel).
+__global__ void shard_pull_kernel(const ShardCtl* __restrict__ c, ShardPeers peers, uint32_t m, uint32_t chunk, uint32_t buf,
+                                  unsigned long long* __restrict__ global) {
+    if (c->done) return;
+    const size_t cur = static_cast<size_t>(buf) * peers.max_q, nxt = static_cast<size_t>(buf ^ 1u) * peers.max_q;
+    const uint32_t lo_i = peers.rank * chunk, hi_i = min(m, lo_i + chunk);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        global[i] = *reinterpret_cast<const volatile unsigned long long*>(peers.best[i / chunk] + cur + i);
+        if (i >= lo_i && i < hi_i) peers.best[peers.rank][nxt + i] = ~0ull;
+    }
+}
+
+// start of an align: both buffers of this rank's home range to "none" (followed by a barrier before anybody searches)
+__global__ void shard_best_reset_kernel(ShardPeers peers, uint32_t m) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        peers.best[peers.rank][i] = ~0ull;
+        peers.best[peers.rank][static_cast<size_t>(peers.max_q) + i] = ~0ull;
+    }
 }
 
 // end of one ceres::Solve: float round trip of the pose (cloud_matcher.cpp:161-167), outer stop rule (:169), and either
@@ -285,14 +365,17 @@ struct lo_sharded {
     lo_grid* grid = nullptr;
     int rank = 0, world = 1;
     NcclApi* api = nullptr;
-    ncclComm_t comm = nullptr;
+    ncclComm_t comm = nullptr;          // null for world = 1 and for the shards of a process-local group
     ShardCtl* d_ctl = nullptr;
     ShardCtl* h_ctl = nullptr;          // pinned read-back copy
-    ShardMailbox* d_box = nullptr;      // this rank's mailbox
+    void* d_shared = nullptr;           // this rank's mailbox + barrier flags + best[] buffers (ShardPeers layout)
+    uint32_t max_q = 0;                 // queries per align the best[] buffers hold
     ShardPeers peers;
     void* peer_mapped[kMaxShardWorld] = {nullptr};
     bool fused_sum = false;             // exchange 2 through peer memory inside shard_step_kernel
-    bool peers_mapped = false;          // every rank could map every peer's mailbox
+    bool fused_min = false;             // exchange 1 through peer memory inside the search kernel
+    bool peers_mapped = false;          // every rank can reach every peer's shared block
+    bool local_group = false;           // created by lo_sharded_create_group: the peers are objects of this process
     DevBuf queries, local, global, hit, partials, acc32, guess;
     long long timeout_cycles = 19000000000LL;   // ~10 s of SM clocks (LO_SHARDED_TIMEOUT_MS)
     lo_sharded_info info;
@@ -308,7 +391,7 @@ static void sharded_release(lo_sharded* s) {
     if (s->grid) lo_grid_destroy(s->grid);
     if (s->d_ctl) cudaFree(s->d_ctl);
     if (s->h_ctl) cudaFreeHost(s->h_ctl);
-    if (s->d_box) cudaFree(s->d_box);
+    if (s->d_shared) cudaFree(s->d_shared);
     for (DevBuf* b : {&s->queries, &s->local, &s->global, &s->hit, &s->partials, &s->acc32, &s->guess}) b->release();
     delete s;
 }
@@ -324,43 +407,13 @@ extern "C" int lo_sharded_unique_id(uint8_t id[LO_SHARDED_ID_BYTES]) {
     return LO_OK;
 }
 
-// map every peer's mailbox; any failure (no peer access, IPC not permitted) leaves the NCCL sum in place
-static bool sharded_map_peers(lo_sharded* s) {
-    lo_ctx* ctx = s->ctx;
-    cudaIpcMemHandle_t mine;
-    if (cudaIpcGetMemHandle(&mine, s->d_box) != cudaSuccess) return false;
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-    DevBuf hs;
-    if (hs.ensure(64 * (s->world + 1)) != LO_OK) return false;
-    char* d_all = hs.as<char>();
-    char* d_mine = d_all + 64 * s->world;
-    bool ok = cudaMemcpyAsync(d_mine, &mine, 64, cudaMemcpyHostToDevice, ctx->stream) == cudaSuccess &&
-              s->api->AllGather(d_mine, d_all, 64, ncclChar, s->comm, ctx->stream) == ncclSuccess;
-    std::vector<cudaIpcMemHandle_t> all(s->world);
-    ok = ok && cudaMemcpyAsync(all.data(), d_all, 64 * s->world, cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess &&
-         cudaStreamSynchronize(ctx->stream) == cudaSuccess;
-    hs.release();
-    int mapped_ok = ok ? 1 : 0;
-    for (int r = 0; r < s->world && mapped_ok; r++) {
-        if (r == s->rank) {
-            s->peers.box[r] = s->d_box;
-            continue;
-        }
-        void* p = nullptr;
-        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
-            mapped_ok = 0;
-            break;
-        }
-        s->peer_mapped[r] = p;
-        s->peers.box[r] = static_cast<ShardMailbox*>(p);
-    }
-    cudaGetLastError();   // a failed IPC call must not poison later launches
-    return mapped_ok == 1;
+static uint32_t sharded_max_queries() {
+    const char* e = getenv("LO_SHARDED_MAX_QUERIES");
+    return e && atoll(e) > 0 ? static_cast<uint32_t>(std::min<long long>(atoll(e), 1ll << 28)) : (1u << 20);
 }
 
-extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYTES], int rank, int world, float voxel_size, size_t max_points,
-                                 size_t capacity_hint, lo_sharded** out) {
-    if (!ctx || !out || world < 1 || world > kMaxShardWorld || rank < 0 || rank >= world || (world > 1 && !id)) return LO_E_ARG;
+// everything of a shard that does not depend on how its peers are reached
+static int sharded_new(lo_ctx* ctx, int rank, int world, float voxel_size, size_t max_points, size_t capacity_hint, lo_sharded** out) {
     LO_CUDA(cudaSetDevice(ctx->device));
     lo_sharded* s = new lo_sharded();
     s->ctx = ctx;
@@ -369,22 +422,89 @@ extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYT
     std::memset(&s->peers, 0, sizeof(s->peers));
     s->peers.rank = static_cast<uint32_t>(rank);
     s->peers.world = static_cast<uint32_t>(world);
+    s->max_q = world > 1 ? sharded_max_queries() : 0;
+    s->peers.max_q = s->max_q;
     std::memset(&s->info, 0, sizeof(s->info));
+    int st = lo_grid_create(ctx, voxel_size, max_points, capacity_hint, &s->grid);
+    if (st == LO_OK) st = lo_grid_set_shard(s->grid, static_cast<uint32_t>(rank), static_cast<uint32_t>(world));
+    if (st != LO_OK) {
+        sharded_release(s);
+        return st;
+    }
+    const size_t shared_bytes = kSharedBestOffset + 2 * static_cast<size_t>(s->max_q) * sizeof(unsigned long long);
+    if (cudaMalloc(&s->d_ctl, sizeof(ShardCtl)) != cudaSuccess || cudaMallocHost(&s->h_ctl, sizeof(ShardCtl)) != cudaSuccess ||
+        cudaMalloc(&s->d_shared, shared_bytes) != cudaSuccess || cudaMemsetAsync(s->d_ctl, 0, sizeof(ShardCtl), ctx->stream) != cudaSuccess ||
+        cudaMemsetAsync(s->d_shared, 0, kSharedBestOffset, ctx->stream) != cudaSuccess ||
+        cudaMemsetAsync(static_cast<char*>(s->d_shared) + kSharedBestOffset, 0xFF, shared_bytes - kSharedBestOffset, ctx->stream) != cudaSuccess ||
+        s->acc32.ensure(32 * sizeof(double)) != LO_OK || s->guess.ensure(8 * sizeof(float)) != LO_OK ||
+        cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+        set_error("lo_sharded_create: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        sharded_release(s);
+        return LO_E_CUDA;
+    }
+    std::memset(s->h_ctl, 0, sizeof(ShardCtl));
+    shard_peer_pointers(s->peers, rank, s->d_shared);
+    const char* to = getenv("LO_SHARDED_TIMEOUT_MS");
+    if (to && atof(to) > 0) s->timeout_cycles = static_cast<long long>(atof(to) * 1.9e6);
+    s->info.rank = rank;
+    s->info.world = world;
+    *out = s;
+    return LO_OK;
+}
+
+// Map every peer's shared block (processes: CUDA IPC). Every rank takes part in the all-gather of the handles whatever
+// happened before it on this rank (a rank that could not make its handle sends zeros and an ok flag of 0), so no rank is
+// left waiting in the collective; any failure leaves the NCCL exchanges in place on all ranks (agreed right after).
+static bool sharded_map_peers(lo_sharded* s) {
+    lo_ctx* ctx = s->ctx;
+    struct Entry {
+        cudaIpcMemHandle_t handle;
+        int ok;
+        int pad[15];
+    };
+    static_assert(sizeof(Entry) == 128, "all-gather record");
+    Entry mine;
+    std::memset(&mine, 0, sizeof(mine));
+    mine.ok = cudaIpcGetMemHandle(&mine.handle, s->d_shared) == cudaSuccess ? 1 : 0;
+    DevBuf hs;
+    const bool have_buf = hs.ensure(sizeof(Entry) * (s->world + 1)) == LO_OK;
+    std::vector<Entry> all(s->world);
+    bool ok = have_buf;
+    if (have_buf) {
+        char* d_all = hs.as<char>();
+        char* d_mine = d_all + sizeof(Entry) * s->world;
+        ok = cudaMemcpyAsync(d_mine, &mine, sizeof(Entry), cudaMemcpyHostToDevice, ctx->stream) == cudaSuccess;
+        // the collective itself is entered unconditionally (with whatever d_mine holds)
+        ok = (s->api->AllGather(d_mine, d_all, sizeof(Entry), ncclChar, s->comm, ctx->stream) == ncclSuccess) && ok;
+        ok = ok && cudaMemcpyAsync(all.data(), d_all, sizeof(Entry) * s->world, cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess &&
+             cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+        hs.release();
+    }
+    int mapped_ok = ok ? 1 : 0;
+    for (int r = 0; r < s->world && mapped_ok; r++) mapped_ok = all[r].ok;
+    for (int r = 0; r < s->world && mapped_ok; r++) {
+        if (r == s->rank) continue;
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            mapped_ok = 0;
+            break;
+        }
+        s->peer_mapped[r] = p;
+        shard_peer_pointers(s->peers, r, p);
+    }
+    cudaGetLastError();   // a failed IPC call must not poison later launches
+    return mapped_ok == 1;
+}
+
+extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYTES], int rank, int world, float voxel_size, size_t max_points,
+                                 size_t capacity_hint, lo_sharded** out) {
+    if (!ctx || !out || world < 1 || world > kMaxShardWorld || rank < 0 || rank >= world || (world > 1 && !id)) return LO_E_ARG;
+    lo_sharded* s = nullptr;
+    LO_TRY(sharded_new(ctx, rank, world, voxel_size, max_points, capacity_hint, &s));
     auto fail = [&](int code) {
         sharded_release(s);
         return code;
     };
-    int st = lo_grid_create(ctx, voxel_size, max_points, capacity_hint, &s->grid);
-    if (st == LO_OK) st = lo_grid_set_shard(s->grid, static_cast<uint32_t>(rank), static_cast<uint32_t>(world));
-    if (st != LO_OK) return fail(st);
-    if (cudaMalloc(&s->d_ctl, sizeof(ShardCtl)) != cudaSuccess || cudaMallocHost(&s->h_ctl, sizeof(ShardCtl)) != cudaSuccess ||
-        cudaMalloc(&s->d_box, sizeof(ShardMailbox)) != cudaSuccess || cudaMemsetAsync(s->d_ctl, 0, sizeof(ShardCtl), ctx->stream) != cudaSuccess ||
-        cudaMemsetAsync(s->d_box, 0, sizeof(ShardMailbox), ctx->stream) != cudaSuccess || s->acc32.ensure(32 * sizeof(double)) != LO_OK ||
-        s->guess.ensure(8 * sizeof(float)) != LO_OK || cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
-        set_error("lo_sharded_create: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
-        return fail(LO_E_CUDA);
-    }
-    s->peers.box[rank] = s->d_box;
     if (world > 1) {
         s->api = nccl_api();
         if (!s->api) return fail(LO_E_CUDA);
@@ -397,9 +517,11 @@ extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYT
             return fail(LO_E_CUDA);
         }
         const char* mode = getenv("LO_SHARDED_SUM");
-        const bool want_fused = !(mode && mode[0] == 'n');
+        const bool want_fused_sum = !(mode && mode[0] == 'n');
+        const char* min_mode = getenv("LO_SHARDED_MIN");
+        const bool want_fused_min = !(min_mode && min_mode[0] == 'n');
         // every rank maps (the all-gather of the handles is a collective), then all must agree, or the ranks would mix
-        // the two exchange protocols: MIN over "I can and want to"
+        // the exchange protocols: MIN over "I can"
         const bool mapped = sharded_map_peers(s);
         int both = mapped ? 1 : 0;
         int* d_flag = s->acc32.as<int>();
@@ -411,17 +533,66 @@ extern "C" int lo_sharded_create(lo_ctx* ctx, const uint8_t id[LO_SHARDED_ID_BYT
             return fail(LO_E_CUDA);
         }
         s->peers_mapped = both == 1;
-        s->fused_sum = s->peers_mapped && want_fused;   // LO_SHARDED_SUM is read by every rank of the job alike
+        s->fused_sum = s->peers_mapped && want_fused_sum;   // the LO_SHARDED_* switches are read by every rank of the job alike
+        s->fused_min = s->peers_mapped && want_fused_min;
         int version = 0;
         s->api->GetVersion(&version);
         s->info.nccl_version = version;
     }
-    const char* to = getenv("LO_SHARDED_TIMEOUT_MS");
-    if (to && atof(to) > 0) s->timeout_cycles = static_cast<long long>(atof(to) * 1.9e6);
-    s->info.rank = rank;
-    s->info.world = world;
     s->info.fused_sum = s->fused_sum ? 1 : 0;
+    s->info.fused_min = s->fused_min ? 1 : 0;
     *out = s;
+    return LO_OK;
+}
+
+// The shards of ONE process: `world` contexts (each its own stream; on different GPUs of the box, or several on the same
+// GPU), no NCCL at all — both exchanges run through peer memory, which for two shards on one device is plain device
+// memory. The shards must be driven together (lo_sharded_align_group): a shard's kernels wait on the device for its
+// peers' arrivals, so a blocking call on one shard alone would wait for work nobody has queued.
+extern "C" int lo_sharded_create_group(lo_ctx* const* ctxs, int world, float voxel_size, size_t max_points, size_t capacity_hint,
+                                       lo_sharded** out) {
+    if (!ctxs || !out || world < 1 || world > kMaxShardWorld) return LO_E_ARG;
+    for (int r = 0; r < world; r++) {
+        if (!ctxs[r]) return LO_E_ARG;
+        for (int q = 0; q < r; q++)
+            if (ctxs[q] == ctxs[r]) {
+                set_error("lo_sharded_create_group: every shard needs a context (stream) of its own");
+                return LO_E_ARG;
+            }
+        out[r] = nullptr;
+    }
+    auto fail = [&](int code) {
+        for (int r = 0; r < world; r++) {
+            sharded_release(out[r]);
+            out[r] = nullptr;
+        }
+        return code;
+    };
+    for (int r = 0; r < world; r++) {
+        const int st = sharded_new(ctxs[r], r, world, voxel_size, max_points, capacity_hint, &out[r]);
+        if (st != LO_OK) return fail(st);
+        out[r]->local_group = true;
+    }
+    for (int r = 0; r < world; r++) {
+        if (cudaSetDevice(ctxs[r]->device) != cudaSuccess) return fail(LO_E_CUDA);
+        for (int q = 0; q < world; q++) {
+            if (ctxs[q]->device != ctxs[r]->device) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, ctxs[r]->device, ctxs[q]->device);
+                const cudaError_t e = can ? cudaDeviceEnablePeerAccess(ctxs[q]->device, 0) : cudaErrorPeerAccessUnsupported;
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                    set_error("lo_sharded_create_group: device %d cannot access device %d: %s", ctxs[r]->device, ctxs[q]->device, cudaGetErrorString(e));
+                    cudaGetLastError();
+                    return fail(LO_E_CUDA);
+                }
+                cudaGetLastError();
+            }
+            shard_peer_pointers(out[r]->peers, q, out[q]->d_shared);
+        }
+        out[r]->peers_mapped = true;
+        out[r]->fused_sum = out[r]->fused_min = world > 1;
+        out[r]->info.fused_sum = out[r]->info.fused_min = world > 1 ? 1 : 0;
+    }
     return LO_OK;
 }
 
@@ -431,6 +602,10 @@ extern "C" lo_grid* lo_sharded_grid(lo_sharded* s) { return s ? s->grid : nullpt
 
 extern "C" int lo_sharded_set_fused_sum(lo_sharded* s, int enable) {
     if (!s) return LO_E_ARG;
+    if (!enable && s->local_group && s->world > 1) {
+        set_error("the shards of a process-local group have no NCCL communicator: the peer-memory exchanges stay in place");
+        return LO_E_ARG;
+    }
     if (enable && s->world > 1 && !s->peers_mapped) {
         set_error("the peers' mailboxes could not be mapped on this job (no peer access / IPC): the NCCL sum stays in place");
         return LO_E_ARG;
@@ -440,15 +615,31 @@ extern "C" int lo_sharded_set_fused_sum(lo_sharded* s, int enable) {
     return LO_OK;
 }
 
+extern "C" int lo_sharded_set_fused_min(lo_sharded* s, int enable) {
+    if (!s) return LO_E_ARG;
+    if (!enable && s->local_group && s->world > 1) {
+        set_error("the shards of a process-local group have no NCCL communicator: the peer-memory exchanges stay in place");
+        return LO_E_ARG;
+    }
+    if (enable && s->world > 1 && !s->peers_mapped) {
+        set_error("the peers' memory could not be mapped on this job (no peer access / IPC): the NCCL MIN stays in place");
+        return LO_E_ARG;
+    }
+    s->fused_min = enable && s->world > 1;
+    s->info.fused_min = s->fused_min ? 1 : 0;
+    return LO_OK;
+}
+
 extern "C" int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out) {
     if (!s || !out) return LO_E_ARG;
     *out = s->info;
     return LO_OK;
 }
 
-static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max_d2) {
+static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max_d2, uint32_t outer) {
     lo_ctx* ctx = s->ctx;
     lo_grid* g = s->grid;
+    LO_CUDA(cudaSetDevice(ctx->device));
     const GridView v = g->view();
     unsigned long long* local = s->local.as<unsigned long long>();
     unsigned long long* global = s->world > 1 ? s->global.as<unsigned long long>() : local;
@@ -459,11 +650,27 @@ static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max
     const int eblocks = std::max(1, std::min<int>(ctx->sm_count * kEvalBlocksPerSm, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
     double* partials = s->partials.as<double>();
     double* acc32 = s->acc32.as<double>();
-    shard_search_ctl_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit);
-    LO_LAUNCHED(ctx);
-    if (s->world > 1 && m) {
-        LO_NCCL(s->api, s->api->AllReduce(local, global, m, ncclUint64, ncclMin, s->comm, ctx->stream));   // exchange 1
-        s->info.min_allreduces++;
+    if (s->world > 1 && m && s->fused_min) {
+        // exchange 1 inside the search: atomicMin into the home ranks' best[], one cross-rank barrier, one pull
+        const uint32_t buf = outer & 1u, chunk = (m + s->world - 1) / static_cast<uint32_t>(s->world);
+        PeerMin pm;
+        for (int r = 0; r < kMaxShardWorld; r++) pm.best[r] = r < s->world ? s->peers.best[r] + static_cast<size_t>(buf) * s->max_q : nullptr;
+        pm.chunk = chunk;
+        shard_search_peer_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit, pm);
+        LO_LAUNCHED(ctx);
+        shard_barrier_kernel<<<1, 32, 0, ctx->stream>>>(s->d_ctl, s->peers, 0, s->timeout_cycles);
+        LO_LAUNCHED(ctx);
+        shard_pull_kernel<<<std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((m + 255) / 256))), 256, 0, ctx->stream>>>(
+            s->d_ctl, s->peers, m, chunk, buf, global);
+        LO_LAUNCHED(ctx);
+        s->info.min_exchanges_fused++;
+    } else {
+        shard_search_ctl_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit);
+        LO_LAUNCHED(ctx);
+        if (s->world > 1 && m) {
+            LO_NCCL(s->api, s->api->AllReduce(local, global, m, ncclUint64, ncclMin, s->comm, ctx->stream));   // exchange 1
+            s->info.min_allreduces++;
+        }
     }
     const int exchange = (s->world > 1 && m) ? kStepExchange : kStepLocal;   // without queries every rank's sums are zero
     for (int phase = 0; phase < 5; phase++) {   // x0, then at most 4 LM candidates (max_num_iterations = 4, cloud_matcher.cpp:111)
@@ -485,39 +692,94 @@ static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max
     return LO_OK;
 }
 
-extern "C" int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
-                                    lo_align_stats* stats) {
-    if (!s || !guess7 || !out7 || (!d_xyz16 && m) || m > 0x7FFFFFFFu) return LO_E_ARG;
+// buffers first, for every shard, before anything is enqueued: a growing buffer frees its old storage, which waits for the
+// device — and a device on which a peer's barrier kernel is already spinning would never get there
+static int align_reserve(lo_sharded* s, size_t m) {
     lo_ctx* ctx = s->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
-    const uint32_t mm = static_cast<uint32_t>(m);
+    if (s->world > 1 && s->fused_min && m > s->max_q) {
+        set_error("sharded align: %zu queries exceed the %u the peer-memory MIN exchange was sized for (LO_SHARDED_MAX_QUERIES)", m, s->max_q);
+        return LO_E_CAPACITY;
+    }
     const size_t mr = std::max<size_t>(m, 1);
     LO_TRY(s->local.ensure(mr * 8));
     if (s->world > 1) LO_TRY(s->global.ensure(mr * 8));
     LO_TRY(s->hit.ensure(mr * 16));
     LO_TRY(s->partials.ensure(static_cast<size_t>(ctx->sm_count) * kEvalBlocksPerSm * 32 * sizeof(double)));
+    return LO_OK;
+}
+
+// control block and (fused MIN) clean best[] buffers behind a cross-rank barrier
+static int align_begin(lo_sharded* s, size_t m, const float guess7[7]) {
+    lo_ctx* ctx = s->ctx;
+    LO_CUDA(cudaSetDevice(ctx->device));
     LO_CUDA(cudaMemcpyAsync(s->guess.p, guess7, 7 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     shard_ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(s->d_ctl, s->guess.as<float>());
     LO_LAUNCHED(ctx);
-    const PointXYZ* q = static_cast<const PointXYZ*>(d_xyz16);
+    if (s->world > 1 && s->fused_min && m) {
+        const uint32_t mm = static_cast<uint32_t>(m);
+        shard_best_reset_kernel<<<std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((mm + 255) / 256))), 256, 0, ctx->stream>>>(s->peers, mm);
+        LO_LAUNCHED(ctx);
+        shard_barrier_kernel<<<1, 32, 0, ctx->stream>>>(s->d_ctl, s->peers, 1, s->timeout_cycles);   // nobody searches before everybody has reset
+        LO_LAUNCHED(ctx);
+    }
+    return LO_OK;
+}
+
+// CloudMatcher::align over `n` shards driven by this process (n = 1: this rank of a multi-process job, the peers are
+// driven by theirs). Every shard's schedule is enqueued before anything is waited for.
+static int align_many(lo_sharded* const* ss, int n, const void* const* d_xyz16, size_t m, const float guess7[7], float max_dist, float* out7s,
+                      lo_align_stats* stats) {
+    const uint32_t mm = static_cast<uint32_t>(m);
     const float max_d2 = max_dist * max_dist;   // voxel_grid.h:215
-    for (int outer = 0; outer < 35; outer++) {
-        LO_TRY(enqueue_outer(s, q, mm, max_d2));
+    for (int k = 0; k < n; k++) LO_TRY(align_reserve(ss[k], m));
+    for (int k = 0; k < n; k++) LO_TRY(align_begin(ss[k], m, guess7));
+    for (uint32_t outer = 0; outer < 35; outer++) {
+        for (int k = 0; k < n; k++) LO_TRY(enqueue_outer(ss[k], static_cast<const PointXYZ*>(d_xyz16[k]), mm, max_d2, outer));
         if (outer >= 4) {   // the stop rule can first hold after the fifth solve (cloud_matcher.cpp:169)
-            LO_CUDA(cudaMemcpyAsync(s->h_ctl, s->d_ctl, sizeof(ShardCtl), cudaMemcpyDeviceToHost, ctx->stream));
-            LO_CUDA(cudaStreamSynchronize(ctx->stream));
-            s->info.host_syncs++;
-            if (s->h_ctl->done) break;
+            for (int k = 0; k < n; k++) {
+                LO_CUDA(cudaSetDevice(ss[k]->ctx->device));
+                LO_CUDA(cudaMemcpyAsync(ss[k]->h_ctl, ss[k]->d_ctl, sizeof(ShardCtl), cudaMemcpyDeviceToHost, ss[k]->ctx->stream));
+            }
+            for (int k = 0; k < n; k++) {
+                LO_CUDA(cudaSetDevice(ss[k]->ctx->device));
+                LO_CUDA(cudaStreamSynchronize(ss[k]->ctx->stream));
+                ss[k]->info.host_syncs++;
+            }
+            if (ss[0]->h_ctl->done) break;   // every shard holds the same control state
         }
     }
-    if (s->h_ctl->error) {
-        set_error("sharded align: a peer rank did not deliver its sums within the time limit");
-        return LO_E_CUDA;
+    for (int k = 0; k < n; k++) {
+        if (ss[k]->h_ctl->error) {
+            set_error("sharded align: a peer rank did not arrive within the time limit");
+            return LO_E_CUDA;
+        }
+        std::memcpy(out7s + 7 * k, ss[k]->h_ctl->out_pose, 7 * sizeof(float));
+        ss[k]->info.evaluations = ss[k]->h_ctl->evaluations;
     }
-    std::memcpy(out7, s->h_ctl->out_pose, 7 * sizeof(float));
-    if (stats) *stats = s->h_ctl->stats;
-    s->info.evaluations = s->h_ctl->evaluations;
+    if (stats) *stats = ss[0]->h_ctl->stats;
     return LO_OK;
+}
+
+extern "C" int lo_sharded_align_dev(lo_sharded* s, const void* d_xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
+                                    lo_align_stats* stats) {
+    if (!s || !guess7 || !out7 || (!d_xyz16 && m) || m > 0x7FFFFFFFu) return LO_E_ARG;
+    if (s->local_group && s->world > 1) {
+        set_error("this shard belongs to a process-local group: drive the group with lo_sharded_align_group");
+        return LO_E_ARG;
+    }
+    return align_many(&s, 1, &d_xyz16, m, guess7, max_dist, out7, stats);
+}
+
+extern "C" int lo_sharded_align_group(lo_sharded* const* shards, int world, const void* const* d_xyz16, size_t m, const float guess7[7],
+                                      float max_dist, float* out7s, lo_align_stats* stats) {
+    if (!shards || world < 1 || world > kMaxShardWorld || !guess7 || !out7s || (!d_xyz16 && m) || m > 0x7FFFFFFFu) return LO_E_ARG;
+    for (int k = 0; k < world; k++)
+        if (!shards[k] || shards[k]->world != world || shards[k]->rank != k || !shards[k]->local_group || (m && !d_xyz16[k])) {
+            set_error("lo_sharded_align_group wants the %d shards lo_sharded_create_group made, in rank order, and one query pointer per shard", world);
+            return LO_E_ARG;
+        }
+    return align_many(shards, world, d_xyz16, m, guess7, max_dist, out7s, stats);
 }
 
 extern "C" int lo_sharded_align(lo_sharded* s, const float* xyz16, size_t m, const float guess7[7], float max_dist, float out7[7],
@@ -528,4 +790,20 @@ extern "C" int lo_sharded_align(lo_sharded* s, const float* xyz16, size_t m, con
     LO_TRY(s->queries.ensure(std::max<size_t>(m, 1) * sizeof(PointXYZ)));
     if (m) LO_CUDA(cudaMemcpyAsync(s->queries.p, xyz16, m * sizeof(PointXYZ), cudaMemcpyHostToDevice, ctx->stream));
     return lo_sharded_align_dev(s, s->queries.p, m, guess7, max_dist, out7, stats);
+}
+
+// host-pointer form of lo_sharded_align_group: the queries are uploaded to every shard's device first
+extern "C" int lo_sharded_align_group_host(lo_sharded* const* shards, int world, const float* xyz16, size_t m, const float guess7[7],
+                                           float max_dist, float* out7s, lo_align_stats* stats) {
+    if (!shards || world < 1 || world > kMaxShardWorld || (!xyz16 && m)) return LO_E_ARG;
+    const void* d_q[kMaxShardWorld];
+    for (int k = 0; k < world; k++) {
+        if (!shards[k]) return LO_E_ARG;
+        lo_ctx* ctx = shards[k]->ctx;
+        LO_CUDA(cudaSetDevice(ctx->device));
+        LO_TRY(shards[k]->queries.ensure(std::max<size_t>(m, 1) * sizeof(PointXYZ)));
+        if (m) LO_CUDA(cudaMemcpyAsync(shards[k]->queries.p, xyz16, m * sizeof(PointXYZ), cudaMemcpyHostToDevice, ctx->stream));
+        d_q[k] = shards[k]->queries.p;
+    }
+    return lo_sharded_align_group(shards, world, d_q, m, guess7, max_dist, out7s, stats);
 }

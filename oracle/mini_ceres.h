@@ -272,11 +272,19 @@ inline void solve(const Problem& problem, double x_inout[7], Summary* summary) {
         for (int c = 0; c < nc; c++) gradient[c] = 0.0;
         for (std::size_t i = 0; i < m; i++)
             for (int c = 0; c < nc; c++) gradient[c] += jac[i * nc + c] * residuals[i];
+        // TrustRegionMinimizer::EvaluateGradientAndJacobian: the norms are those of the projected gradient step in the
+        // AMBIENT space, x - Plus(x, -gradient) (7 coordinates), not of the tangent-space gradient itself
         gradient_max_norm = 0.0;
         gradient_norm = 0.0;
-        for (int c = 0; c < nc; c++) {
-            gradient_max_norm = std::max(gradient_max_norm, std::fabs(gradient[c]));
-            gradient_norm += gradient[c] * gradient[c];
+        {
+            double negative_gradient[6], projected[7];
+            for (int c = 0; c < nc; c++) negative_gradient[c] = -gradient[c];
+            Problem::plus(x, negative_gradient, projected);
+            for (int k = 0; k < 7; k++) {
+                const double d = x[k] - projected[k];
+                gradient_max_norm = std::max(gradient_max_norm, std::fabs(d));
+                gradient_norm += d * d;
+            }
         }
         gradient_norm = std::sqrt(gradient_norm);
         if (opt.jacobi_scaling) {

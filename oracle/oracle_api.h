@@ -78,7 +78,8 @@ int orc_solve(const double* pairs9, size_t n, const double prior_b[3], double x7
 #define ORC_ALIGN_LOG_STRIDE 16
 /* CloudMatcher::align. log (optional, 35*ORC_ALIGN_LOG_STRIDE doubles), per outer iteration:
  * {0:num_pairs, 1:lm_iterations_recorded, 2:last_step_norm, 3:final_cost, 4:termination,
- *  5..11: pose7 after the float round-trip, 12: initial_cost, 13..15: reserved}. Returns outer iterations run. */
+ *  5..11: pose7 after the float round-trip, 12: initial_cost, 13: recorded LM iterations with a rejected step,
+ *  14: ... with an invalid step, 15: trust-region radius after the last recorded iteration}. Returns outer iterations run. */
 int orc_align(const void* grid, const float* xyz16, size_t n, const float guess7[7], float out7[7], double* log);
 
 /* ---- PCA normals: the test's pcl::NormalEstimation radius search (test/test.cpp:196-205), restated ----

@@ -44,7 +44,7 @@ def test_world_one_matches_align_and_oracle(ctx, port, stream12):
     dt, dr = pose_error(pose, ref_pose)
     assert dt < 1e-6 and dr < 1e-6, (dt, dr)
     info = m.info()
-    assert (info.world, info.fused_sum, info.min_allreduces, info.sum_allreduces) == (1, 0, 0, 0)
+    assert (info.world, info.fused_sum, info.fused_min, info.min_allreduces, info.sum_allreduces) == (1, 0, 0, 0, 0)
     assert info.host_syncs == max(1, st.outer_iterations - 4)      # one synchronisation for the usual five iterations
     # an empty query set is the prior-only solve (cloud_matcher.cpp:153-154): the guess comes back
     pose0, st0 = m.align(q[:0], GUESS, with_stats=True)
@@ -55,12 +55,14 @@ def test_world_one_matches_align_and_oracle(ctx, port, stream12):
 
 @pytest.mark.parametrize("sum_mode", ["fused", "nccl"])
 def test_world_two_on_two_gpus(ctx, port, stream12, tmp_path, sum_mode):
+    """fused: both exchanges through NVLink peer memory (atomicMin into the home rank inside the search + barrier + pull; the 32
+    sums inside the LM step kernel); nccl: ncclAllReduce(MIN) and ncclAllReduce(SUM)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     kf, q = scene(port, stream12[0])
     np.savez(tmp_path / "scene.npz", kf=kf, q=q, guess=GUESS)
-    env = dict(os.environ, LO_SHARDED_SUM=sum_mode, LO_SHARDED_TIMEOUT_MS="20000")
+    env = dict(os.environ, LO_SHARDED_SUM=sum_mode, LO_SHARDED_MIN=sum_mode, LO_SHARDED_TIMEOUT_MS="20000")
     procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "sharded_nccl_worker.py"), str(r), "2", str(tmp_path)], env=env,
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(2)]
     outs = []
@@ -88,5 +90,6 @@ def test_world_two_on_two_gpus(ctx, port, stream12, tmp_path, sum_mode):
     assert res[0]["empty_pose"] == res[1]["empty_pose"] == [float(v) for v in lo.CloudMatcher().align(g, q[:0], GUESS)]
     for r in res:
         assert r["info"]["world"] == 2 and r["info"]["fused_sum"] == (1 if sum_mode == "fused" else 0), r["info"]
-        assert r["info"]["min_allreduces"] >= 15
-        assert (r["info"]["sum_allreduces"] == 0) == (sum_mode == "fused")
+        assert r["info"]["fused_min"] == (1 if sum_mode == "fused" else 0), r["info"]
+        assert (r["info"]["min_allreduces"] if sum_mode == "nccl" else r["info"]["min_exchanges_fused"]) >= 15
+        assert (r["info"]["sum_allreduces"] == 0) == (sum_mode == "fused") and (r["info"]["min_allreduces"] == 0) == (sum_mode == "fused")
