@@ -620,9 +620,10 @@ def _exhaustive(flag):
         os.environ.pop("LO_B200_NN_EXHAUSTIVE", None)
 
 
-def _ncu_traffic(kernel):
-    """DRAM bytes (read + write) per launch of `kernel` from the committed `ncu --set full` summary, or None."""
-    for name in ("r2_ncu_summary.json", "r1_ncu_summary.json"):
+def _ncu_traffic(kernel, this_round_only=False):
+    """DRAM bytes (read + write) per launch of `kernel` from a committed `ncu --set full` summary (tools/ncu_summary.py), or
+    None. profiles/r2_ncu_summary.json is this round's capture; the r1 file is only a stand-in for kernels that did not change."""
+    for name in ("r2_ncu_summary.json",) + (() if this_round_only else ("r1_ncu_summary.json",)):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 return json.load(f)[kernel]["dram_bytes_per_launch"]
@@ -732,22 +733,34 @@ def roofline_section(lo, ctx, torch, stream, od, scans, W, K, step_ms, scan_stat
         return float(np.median(ts)), neq.candidates / len(qq), int(neq.n_valid), float(neq.cost)   # median, as for align
 
     t_nn, c_visited, valid_t, cost_t = timed_nn(10)
+    occ_visited = neq.occupied / len(qq)
     _exhaustive(True)
     t_ex, c_big, valid_e, cost_e = timed_nn(6)
     _exhaustive(False)
     assert valid_t == valid_e and abs(cost_t - cost_e) <= 1e-9 * abs(cost_e), "tile search and exhaustive search disagree"
-    bytes_nn = len(qq) * (464 + 16 * c_big)                 # the reference's exhaustive visit
-    bytes_visited = len(qq) * (16 + 16 * c_visited + 32)    # what the pruned search has to touch besides table slots
+    # Algorithmic bytes of the kernel that is timed: what the pruned search has to touch per query — the query (16 B), one
+    # 16-byte slot per occupied voxel it visits (empty probes are not counted: a lower bound), 16 B per stored point it
+    # compares, the winner's point and normal (32 B). `traffic` / `dram_frac` are the DRAM bytes ncu saw for the same launch
+    # shape in THIS round's capture (profiles/r2_ncu_summary.json); the reference's exhaustive 27-voxel visit (464 + 16 C
+    # bytes per query) is what the pruning avoids and is reported apart, under `reference_visit`.
+    bytes_nn = len(qq) * (16 + 16 * occ_visited + 16 * c_visited + 32)
+    bytes_ref = len(qq) * (464 + 16 * c_big)
+    traffic = _ncu_traffic("nn_residual_tile_kernel", this_round_only=True)
+    traffic_ex = _ncu_traffic("nn_residual_kernel", this_round_only=True)
     roof_nn = {"bound": "hbm", "kernel": "nn_residual_tile_kernel (+ 1-block finalize)", "achieved": bytes_nn / t_nn / 1e9, "peak": peak,
-               "unit": "GB/s", "frac": bytes_nn / t_nn / 1e9 / peak, "traffic": _ncu_traffic("nn_residual_tile_kernel"),
+               "unit": "GB/s", "frac": bytes_nn / t_nn / 1e9 / peak, "traffic": traffic,
+               "dram_frac": (traffic / t_nn / 1e9 / peak) if traffic else None,
                "peak_source": peak_src, "launch_ms": 1e3 * t_nn, "queries": int(len(qq)), "mpts_per_s": len(qq) / t_nn / 1e6,
-               "map_points": int(gb.numPoints()), "map_voxels": int(gb.size()), "mean_candidates_per_query": c_big,
-               "candidates_visited_per_query": c_visited, "visited_bytes_GBps": bytes_visited / t_nn / 1e9, "valid_pairs": valid_t,
-               "exhaustive_kernel": {"kernel": "nn_residual_kernel", "launch_ms": 1e3 * t_ex, "achieved": bytes_nn / t_ex / 1e9,
-                                     "frac": bytes_nn / t_ex / 1e9 / peak, "traffic": _ncu_traffic("nn_residual_kernel")},
-               "note": "achieved counts the ALGORITHMIC bytes of the reference's exhaustive 27-voxel visit (464 + 16 C per query); the "
-                       "tile search skips neighbours that cannot hold a nearer point (bit-identical result), so it can exceed the "
-                       "bandwidth needed to read them all; traffic is what it really moved"}
+               "map_points": int(gb.numPoints()), "map_voxels": int(gb.size()), "candidates_visited_per_query": c_visited,
+               "occupied_voxels_visited_per_query": occ_visited, "valid_pairs": valid_t, "speedup_vs_exhaustive": t_ex / t_nn,
+               "reference_visit": {"mean_candidates_per_query": c_big, "bytes_per_launch": bytes_ref, "GBps_if_counted": bytes_ref / t_nn / 1e9,
+                                   "note": "the reference visits all 27 neighbours (464 + 16 C bytes per query); the tile search proves most of "
+                                           "them unnecessary (bit-identical result) and skips them — a speed-up, not bandwidth"},
+               "exhaustive_kernel": {"kernel": "nn_residual_kernel", "launch_ms": 1e3 * t_ex, "achieved": bytes_ref / t_ex / 1e9,
+                                     "frac": bytes_ref / t_ex / 1e9 / peak, "traffic": traffic_ex,
+                                     "dram_frac": (traffic_ex / t_ex / 1e9 / peak) if traffic_ex else None},
+               "note": "traffic / dram_frac come from profiles/r2_ncu_summary.json (ncu --set full of tools/profile_hot.py, same map and "
+                       "queries, this round); null until that capture is committed"}
     return roof, roof_align, roof_nn
 
 

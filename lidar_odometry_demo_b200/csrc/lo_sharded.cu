@@ -636,7 +636,19 @@ extern "C" int lo_sharded_info_get(const lo_sharded* s, lo_sharded_info* out) {
     return LO_OK;
 }
 
-static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max_d2, uint32_t outer) {
+// One outer iteration is a fixed schedule of kOuterParts steps per shard. A caller that drives several shards issues it
+// BREADTH-FIRST — step p for every shard before step p + 1 for any: a kernel that waits for a peer on the device (barrier,
+// step kernel) is then always followed at once by the peer's counterpart, with nothing of the first shard's own stream
+// in between. Streams may share a hardware work queue (CUDA_DEVICE_MAX_CONNECTIONS), which dispatches in issue order and
+// stalls at an entry whose stream predecessor is still running: depth-first issue would put shard 0's later kernels
+// between its spinning barrier and shard 1's arrival, and nothing would ever move.
+//   part 0          search (+ exchange 1 fused into it, or ncclAllReduce(MIN) after it)
+//   part 1          cross-rank barrier              (peer-memory MIN only)
+//   part 2          pull of the winners             (peer-memory MIN only)
+//   part 3 + 2 k    evaluate, k = 0: at x0; k = 1..4: at the LM candidates (max_num_iterations = 4, cloud_matcher.cpp:111)
+//   part 4 + 2 k    step: sum, exchange 2, LM logic
+constexpr int kOuterParts = 3 + 2 * 5;
+static int enqueue_outer_part(lo_sharded* s, const PointXYZ* q, uint32_t m, float max_d2, uint32_t outer, int part) {
     lo_ctx* ctx = s->ctx;
     lo_grid* g = s->grid;
     LO_CUDA(cudaSetDevice(ctx->device));
@@ -650,45 +662,59 @@ static int enqueue_outer(lo_sharded* s, const PointXYZ* q, uint32_t m, float max
     const int eblocks = std::max(1, std::min<int>(ctx->sm_count * kEvalBlocksPerSm, static_cast<int>((m + kShardThreads - 1) / kShardThreads)));
     double* partials = s->partials.as<double>();
     double* acc32 = s->acc32.as<double>();
-    if (s->world > 1 && m && s->fused_min) {
-        // exchange 1 inside the search: atomicMin into the home ranks' best[], one cross-rank barrier, one pull
-        const uint32_t buf = outer & 1u, chunk = (m + s->world - 1) / static_cast<uint32_t>(s->world);
-        PeerMin pm;
-        for (int r = 0; r < kMaxShardWorld; r++) pm.best[r] = r < s->world ? s->peers.best[r] + static_cast<size_t>(buf) * s->max_q : nullptr;
-        pm.chunk = chunk;
-        shard_search_peer_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit, pm);
-        LO_LAUNCHED(ctx);
-        shard_barrier_kernel<<<1, 32, 0, ctx->stream>>>(s->d_ctl, s->peers, 0, s->timeout_cycles);
-        LO_LAUNCHED(ctx);
-        shard_pull_kernel<<<std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((m + 255) / 256))), 256, 0, ctx->stream>>>(
-            s->d_ctl, s->peers, m, chunk, buf, global);
-        LO_LAUNCHED(ctx);
-        s->info.min_exchanges_fused++;
-    } else {
-        shard_search_ctl_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit);
-        LO_LAUNCHED(ctx);
-        if (s->world > 1 && m) {
-            LO_NCCL(s->api, s->api->AllReduce(local, global, m, ncclUint64, ncclMin, s->comm, ctx->stream));   // exchange 1
-            s->info.min_allreduces++;
+    const bool peer_min = s->world > 1 && m && s->fused_min;
+    const uint32_t buf = outer & 1u, chunk = m ? (m + s->world - 1) / static_cast<uint32_t>(s->world) : 1u;
+    if (part == 0) {
+        if (peer_min) {   // exchange 1 inside the search: atomicMin into the home ranks' best[]
+            PeerMin pm;
+            for (int r = 0; r < kMaxShardWorld; r++) pm.best[r] = r < s->world ? s->peers.best[r] + static_cast<size_t>(buf) * s->max_q : nullptr;
+            pm.chunk = chunk;
+            shard_search_peer_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit, pm);
+            LO_LAUNCHED(ctx);
+            s->info.min_exchanges_fused++;
+        } else {
+            shard_search_ctl_kernel<<<sblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, max_d2, tiled, local, hit);
+            LO_LAUNCHED(ctx);
+            if (s->world > 1 && m) {
+                LO_NCCL(s->api, s->api->AllReduce(local, global, m, ncclUint64, ncclMin, s->comm, ctx->stream));   // exchange 1
+                s->info.min_allreduces++;
+            }
         }
+        return LO_OK;
     }
+    if (part == 1) {
+        if (peer_min) {
+            shard_barrier_kernel<<<1, 32, 0, ctx->stream>>>(s->d_ctl, s->peers, 0, s->timeout_cycles);
+            LO_LAUNCHED(ctx);
+        }
+        return LO_OK;
+    }
+    if (part == 2) {
+        if (peer_min) {
+            shard_pull_kernel<<<std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((m + 255) / 256))), 256, 0, ctx->stream>>>(
+                s->d_ctl, s->peers, m, chunk, buf, global);
+            LO_LAUNCHED(ctx);
+        }
+        return LO_OK;
+    }
+    const int ph = (part - 3) / 2 ? 1 : 0;   // phase 0: x0; phase 1: an LM candidate
     const int exchange = (s->world > 1 && m) ? kStepExchange : kStepLocal;   // without queries every rank's sums are zero
-    for (int phase = 0; phase < 5; phase++) {   // x0, then at most 4 LM candidates (max_num_iterations = 4, cloud_matcher.cpp:111)
-        const int ph = phase ? 1 : 0;
+    if ((part - 3) % 2 == 0) {
         shard_evaluate_ctl_kernel<<<eblocks, kShardThreads, 0, ctx->stream>>>(v, q, m, s->d_ctl, ph, local, global, hit, partials);
         LO_LAUNCHED(ctx);
-        if (exchange == kStepExchange && !s->fused_sum) {
-            // NCCL variant: local sums -> acc32, all-reduce in place, then the step logic on the global sums
-            shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, kStepSumOnly, ph, s->timeout_cycles, acc32);
-            LO_LAUNCHED(ctx);
-            LO_NCCL(s->api, s->api->AllReduce(acc32, acc32, 32, ncclDouble, ncclSum, s->comm, ctx->stream));   // exchange 2
-            s->info.sum_allreduces++;
-            shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(acc32, 1, s->d_ctl, s->peers, kStepLocal, ph, s->timeout_cycles, nullptr);
-        } else {
-            shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, exchange, ph, s->timeout_cycles, nullptr);
-        }
-        LO_LAUNCHED(ctx);
+        return LO_OK;
     }
+    if (exchange == kStepExchange && !s->fused_sum) {
+        // NCCL variant: local sums -> acc32, all-reduce in place, then the step logic on the global sums
+        shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, kStepSumOnly, ph, s->timeout_cycles, acc32);
+        LO_LAUNCHED(ctx);
+        LO_NCCL(s->api, s->api->AllReduce(acc32, acc32, 32, ncclDouble, ncclSum, s->comm, ctx->stream));   // exchange 2
+        s->info.sum_allreduces++;
+        shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(acc32, 1, s->d_ctl, s->peers, kStepLocal, ph, s->timeout_cycles, nullptr);
+    } else {
+        shard_step_kernel<<<1, kStepThreads, 0, ctx->stream>>>(partials, eblocks, s->d_ctl, s->peers, exchange, ph, s->timeout_cycles, nullptr);
+    }
+    LO_LAUNCHED(ctx);
     return LO_OK;
 }
 
@@ -709,17 +735,21 @@ static int align_reserve(lo_sharded* s, size_t m) {
     return LO_OK;
 }
 
-// control block and (fused MIN) clean best[] buffers behind a cross-rank barrier
-static int align_begin(lo_sharded* s, size_t m, const float guess7[7]) {
+// control block and (fused MIN) clean best[] buffers; part 1: the cross-rank barrier behind them (breadth-first, see above)
+static int align_begin(lo_sharded* s, size_t m, const float guess7[7], int part) {
     lo_ctx* ctx = s->ctx;
     LO_CUDA(cudaSetDevice(ctx->device));
-    LO_CUDA(cudaMemcpyAsync(s->guess.p, guess7, 7 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    shard_ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(s->d_ctl, s->guess.as<float>());
-    LO_LAUNCHED(ctx);
-    if (s->world > 1 && s->fused_min && m) {
-        const uint32_t mm = static_cast<uint32_t>(m);
-        shard_best_reset_kernel<<<std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((mm + 255) / 256))), 256, 0, ctx->stream>>>(s->peers, mm);
+    const bool peer_min = s->world > 1 && s->fused_min && m;
+    if (part == 0) {
+        LO_CUDA(cudaMemcpyAsync(s->guess.p, guess7, 7 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        shard_ctl_init_kernel<<<1, 1, 0, ctx->stream>>>(s->d_ctl, s->guess.as<float>());
         LO_LAUNCHED(ctx);
+        if (peer_min) {
+            const uint32_t mm = static_cast<uint32_t>(m);
+            shard_best_reset_kernel<<<std::max(1, std::min<int>(ctx->sm_count * 2, static_cast<int>((mm + 255) / 256))), 256, 0, ctx->stream>>>(s->peers, mm);
+            LO_LAUNCHED(ctx);
+        }
+    } else if (peer_min) {
         shard_barrier_kernel<<<1, 32, 0, ctx->stream>>>(s->d_ctl, s->peers, 1, s->timeout_cycles);   // nobody searches before everybody has reset
         LO_LAUNCHED(ctx);
     }
@@ -733,9 +763,11 @@ static int align_many(lo_sharded* const* ss, int n, const void* const* d_xyz16, 
     const uint32_t mm = static_cast<uint32_t>(m);
     const float max_d2 = max_dist * max_dist;   // voxel_grid.h:215
     for (int k = 0; k < n; k++) LO_TRY(align_reserve(ss[k], m));
-    for (int k = 0; k < n; k++) LO_TRY(align_begin(ss[k], m, guess7));
+    for (int part = 0; part < 2; part++)
+        for (int k = 0; k < n; k++) LO_TRY(align_begin(ss[k], m, guess7, part));
     for (uint32_t outer = 0; outer < 35; outer++) {
-        for (int k = 0; k < n; k++) LO_TRY(enqueue_outer(ss[k], static_cast<const PointXYZ*>(d_xyz16[k]), mm, max_d2, outer));
+        for (int part = 0; part < kOuterParts; part++)
+            for (int k = 0; k < n; k++) LO_TRY(enqueue_outer_part(ss[k], static_cast<const PointXYZ*>(d_xyz16[k]), mm, max_d2, outer, part));
         if (outer >= 4) {   // the stop rule can first hold after the fifth solve (cloud_matcher.cpp:169)
             for (int k = 0; k < n; k++) {
                 LO_CUDA(cudaSetDevice(ss[k]->ctx->device));
@@ -751,7 +783,9 @@ static int align_many(lo_sharded* const* ss, int n, const void* const* d_xyz16, 
     }
     for (int k = 0; k < n; k++) {
         if (ss[k]->h_ctl->error) {
-            set_error("sharded align: a peer rank did not arrive within the time limit");
+            const ShardCtl* c = ss[k]->h_ctl;
+            set_error("sharded align: a peer rank did not arrive within the time limit (rank %d of %d: outer iteration %u, %u barriers and %u sum "
+                      "exchanges entered, %u evaluations)", ss[k]->rank, ss[k]->world, c->outer, c->bar_seq, c->seq, c->evaluations);
             return LO_E_CUDA;
         }
         std::memcpy(out7s + 7 * k, ss[k]->h_ctl->out_pose, 7 * sizeof(float));
