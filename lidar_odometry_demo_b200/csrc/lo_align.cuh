@@ -5,8 +5,6 @@
 
 #include <cooperative_groups.h>
 
-#include <cstddef>
-
 #include "lo_host.h"
 #include "lo_lm.cuh"
 #include "lo_tile_search.cuh"
@@ -173,279 +171,9 @@ __device__ inline void reduce_partials(const double* partials, int nblocks, doub
 }
 
 // ---------------------------------------------------------------------------------------------------
-// Grid-wide sum of the blocks' column sums with the barrier folded into the exchange. Every block writes its kAcc column
-// sums into its row of `partials` (256 B), publishes the row by storing the epoch into the row's last slot, then waits for
-// all rows of this epoch and adds them up in block order — one L2 round trip from "my sums are ready" to "everybody's
-// sums are here", instead of a grid barrier (fence + arrival counter + spin) followed by the reads. The sum is the same
-// in every block, bit for bit (fixed order). Two row sets alternate: a block can be at most one exchange ahead of the
-// slowest one (it needs that block's row to finish the exchange in between), so a row is never overwritten while
-// somebody still reads it, and a flag never moves on before everybody has seen it.
-//   cols    : the block's kAcc column sums (shared), zeroed on return
-//   scratch : (blockDim.x / 32) * 32 doubles of shared memory, zeroed on return
-//   total   : kAcc sums, shared memory
-//   epoch   : unique per exchange among all launches that share `partials` (never 0), identical in all blocks
-__device__ inline void exchange_sum(double* cols, double* scratch, double* partials, int nblocks, int buf, unsigned long long epoch,
-                                    double* total) {
-    double* mine = partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32;
-    __syncthreads();
-    if (threadIdx.x < kAcc) {
-        __stcg(mine + threadIdx.x, cols[threadIdx.x]);
-        cols[threadIdx.x] = 0.0;
-        __threadfence();
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(mine + 31) = epoch;
-    const double* all = partials + static_cast<size_t>(buf) * nblocks * 32;
-    // one poller per row (measured: one warp sweeping 32 flags per load was 1.5x slower — five dependent sweeps)
-    for (int b = threadIdx.x; b < nblocks; b += blockDim.x) {
-        const volatile unsigned long long* flag = reinterpret_cast<const volatile unsigned long long*>(all + static_cast<size_t>(b) * 32 + 31);
-        while (*flag != epoch) {
-        }
-        __threadfence();
-    }
-    __syncthreads();
-    reduce_partials(all, nblocks, scratch, total);
-}
-
-// per-warp rows (accumulate_warp) -> the block's column sums; rows are zeroed for the next pass
-__device__ inline void rows_to_cols(double* rows, double* cols) {
-    __syncthreads();
-    const int nwarps = blockDim.x >> 5;
-    if (threadIdx.x < kAcc) {
-        double v = cols[threadIdx.x];
-        for (int w = 0; w < nwarps; w++) {
-            v += rows[w * kRow + threadIdx.x];
-            rows[w * kRow + threadIdx.x] = 0.0;
-        }
-        cols[threadIdx.x] = v;
-    }
-    __syncthreads();
-}
-
-// The block's pairs (one per thread, threads 0 .. kPairs-1) added to its column sums through a transposed staging area in
-// shared memory: every thread stores its 29 products (conflict-free), then 8 threads per column add kPairs / 8 values each
-// in a fixed order and finish with three shuffles. ~600 cycles for 64 pairs; reducing the 29 values one after the other
-// by warp shuffles into a shared accumulator took ~6 000. `stage` holds 29 * kPairs doubles. Every thread of the block
-// calls; `t` is only meaningful where `valid`.
-template <int kPairs>
-__device__ inline void block_accumulate(const Terms& t, bool valid, double* stage, double* cols) {
-    static_assert(kPairs % 8 == 0, "8 adders per column");
-    const int tid = threadIdx.x;
-    if (tid < kPairs) {
-        int at = 0;
-#pragma unroll
-        for (int a = 0; a < 6; a++)
-#pragma unroll
-            for (int b = a; b < 6; b++) stage[(at++) * kPairs + tid] = valid ? t.j[a] * t.j[b] : 0.0;
-#pragma unroll
-        for (int a = 0; a < 6; a++) stage[(21 + a) * kPairs + tid] = valid ? t.j[a] * t.rc : 0.0;
-        stage[27 * kPairs + tid] = valid ? t.cost : 0.0;
-        stage[28 * kPairs + tid] = valid ? 1.0 : 0.0;
-    }
-    __syncthreads();
-    if (tid < 29 * 8) {
-        const int c = tid >> 3, part = tid & 7;
-        constexpr int kEach = kPairs / 8;
-        double v = 0.0;
-#pragma unroll
-        for (int k = 0; k < kEach; k++) v += stage[c * kPairs + part * kEach + k];
-        const unsigned mask = tid < 224 ? kFullMask : 0xFFu;   // 29 * 8 = 232 threads: seven whole warps and eight lanes of the eighth
-        v += __shfl_xor_sync(mask, v, 4);
-        v += __shfl_xor_sync(mask, v, 2);
-        v += __shfl_xor_sync(mask, v, 1);
-        if (part == 0) cols[c] += v;
-    }
-    __syncthreads();
-}
-
-// ---------------------------------------------------------------------------------------------------
-// Correspondence search of one block's share of the queries, all threads of the block working on all of them
-// (VoxelGrid::findMatchingPairs + getCorrespondence, src/voxel_grid.h:164-234). A VLP16 scan leaves ~40 queries per
-// block: with one warp per query a block waited for its slowest warp and every warp walked through five dependent
-// memory round trips per query. Here the block goes through the same work in flat steps, each one round of
-// independent loads over all threads:
-//   A  threads 0..nq-1: transform their query (double) and take its voxel;
-//   B  one thread per (query, neighbour) pair — 27 nq look-ups: key, probe hash, slot load, resolve;
-//   C  block-wide prefix sum over the pieces (4 stored points = 64 B) of the voxels found;
-//   D  one thread per piece: distances, the piece's first strict minimum folded into the query's 64-bit
-//      (d2 bits, neighbour, slot) key with a shared-memory atomicMin — the lexicographic minimum is the reference's
-//      "first strict minimum in ix -> iy -> iz -> slot scan order", whatever the order of the visit;
-//   E  threads 0..nq-1: fetch the winner's point and normal.
+// CloudMatcher::align (src/cloud_matcher.cpp:105-178) as one persistent cooperative kernel.
 constexpr int kAlignThreads = 512;
-constexpr int kBlockQueries = 64;                 // queries of one block per pass (two warps hold one each in registers)
-constexpr int kBlockProbes = kBlockQueries * 27;
 
-struct BlockSearch {                              // shared memory
-    float wq[3][kBlockQueries];
-    int oi[3][kBlockQueries];
-    unsigned long long best[kBlockQueries];
-    uint2 found[kBlockProbes];                    // vid, count of neighbour l of query q at [l * nq + q]
-    uint32_t piece_start[kBlockProbes + 1];       // exclusive prefix of ceil(count / 4)
-};
-
-struct PairRegs {                                 // one correspondence, kept by the thread that owns the query
-    float p[3], o[3], n[3];
-    bool valid;
-};
-
-// query k of this block in pass `pass` is global query (pass * kBlockQueries + k) * gridDim.x + blockIdx.x: neighbouring
-// queries (which cost about the same) go to different blocks
-__device__ inline uint32_t block_query_index(uint32_t pass, uint32_t k) { return (pass * kBlockQueries + k) * gridDim.x + blockIdx.x; }
-
-#define LO_BS_TRACE(tag)                                                               \
-    do {                                                                               \
-        if (trace && blockIdx.x == trace_block && threadIdx.x == 0 && *trace_n < 500) { \
-            trace[2 * *trace_n] = (tag);                                               \
-            trace[2 * *trace_n + 1] = clock64();                                       \
-            (*trace_n)++;                                                              \
-        }                                                                              \
-    } while (0)
-
-__device__ inline PairRegs block_search(const GridView& g, const PointXYZ* __restrict__ queries, uint32_t m, uint32_t pass, const QueryTransform& tf,
-                                        float max_d2, BlockSearch& bs, long long* trace = nullptr, int* trace_n = nullptr, uint32_t trace_block = 0) {
-    const uint32_t tid = threadIdx.x;
-    const uint32_t first = block_query_index(pass, 0);
-    const uint32_t nq = first < m ? min(static_cast<uint32_t>(kBlockQueries), (m - first + gridDim.x - 1) / gridDim.x) : 0u;
-    PairRegs pr;
-    pr.valid = false;
-    for (int k = 0; k < 3; k++) pr.p[k] = pr.o[k] = pr.n[k] = 0.f;
-    // A
-    if (tid < nq) {
-        const PointXYZ q = queries[block_query_index(pass, tid)];
-        pr.p[0] = q.x; pr.p[1] = q.y; pr.p[2] = q.z;
-        float w[3];
-        transform_query(tf, q.x, q.y, q.z, w);
-        for (int k = 0; k < 3; k++) {
-            bs.wq[k][tid] = w[k];
-            bs.oi[k][tid] = clamp_axis(axis_index(w[k], g.voxel_size));
-        }
-        bs.best[tid] = ~0ull;
-    }
-    __syncthreads();
-    LO_BS_TRACE(10);
-    // B: the look-ups, neighbour-major (entry e = l * nq + q): consecutive threads look at different queries, so that the
-    // pieces consecutive threads fold in step D mostly belong to different queries
-    const uint32_t n_probe = nq * 27;
-    for (uint32_t base = 0; base < n_probe; base += 4 * blockDim.x) {   // 4 look-ups per thread in flight
-        Probe pb[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const uint32_t e = base + tid + u * blockDim.x;
-            pb[u].active = false;
-            if (e < n_probe) {
-                const uint32_t l = e / nq, q = e - l * nq;
-                LaneOffset lo;
-                lo.probing = true;
-                lo.dx = static_cast<int>(l / 9) - 1;
-                lo.dy = static_cast<int>((l / 3) % 3) - 1;
-                lo.dz = static_cast<int>(l % 3) - 1;
-                pb[u] = probe_issue_at(g, bs.oi[0][q], bs.oi[1][q], bs.oi[2][q], lo);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const uint32_t e = base + tid + u * blockDim.x;
-            if (e < n_probe) {
-                uint32_t vid, cnt;
-                probe_resolve(g, pb[u], vid, cnt);
-                bs.found[e] = make_uint2(vid, cnt);
-            }
-        }
-    }
-    __syncthreads();
-    LO_BS_TRACE(11);
-    // C: thread t owns look-ups kPer * t .. kPer * t + kPer - 1 of the prefix sum
-    uint32_t total_pieces;
-    {
-        constexpr int kPer = (kBlockProbes + kAlignThreads) / kAlignThreads;
-        static_assert(kPer * kAlignThreads > kBlockProbes, "every entry and the total need an owner");
-        uint32_t c[kPer], sum = 0;
-#pragma unroll
-        for (int u = 0; u < kPer; u++) {
-            const uint32_t e = tid * kPer + u;
-            c[u] = e < n_probe ? (bs.found[e].y + 3) >> 2 : 0u;
-            sum += c[u];
-        }
-        __shared__ uint32_t warp_sums[kAlignThreads / 32];
-        const int lane = tid & 31, warp = tid >> 5;
-        uint32_t incl = sum;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t v = __shfl_up_sync(kFullMask, incl, off);
-            if (lane >= off) incl += v;
-        }
-        if (lane == 31) warp_sums[warp] = incl;
-        __syncthreads();
-        uint32_t before = 0, all = 0;
-        for (int w = 0; w < kAlignThreads / 32; w++) {
-            const uint32_t ws = warp_sums[w];
-            if (w < warp) before += ws;
-            all += ws;
-        }
-        total_pieces = all;
-        uint32_t run = before + incl - sum;
-#pragma unroll
-        for (int u = 0; u < kPer; u++) {
-            const uint32_t e = tid * kPer + u;
-            if (e <= n_probe) bs.piece_start[e] = run;   // entry n_probe = total
-            run += c[u];
-        }
-    }
-    __syncthreads();
-    LO_BS_TRACE(12);
-    // D
-    for (uint32_t pc = tid; pc < total_pieces; pc += blockDim.x) {
-        uint32_t lo_e = 0, hi_e = n_probe;               // last e with piece_start[e] <= pc
-        while (hi_e - lo_e > 1) {
-            const uint32_t mid = (lo_e + hi_e) >> 1;
-            if (bs.piece_start[mid] <= pc) lo_e = mid;
-            else hi_e = mid;
-        }
-        const uint32_t e = lo_e, l = e / nq, q = e - l * nq;
-        const uint2 f = bs.found[e];
-        const uint32_t e0 = (pc - bs.piece_start[e]) * 4, cnt = min(4u, f.y - e0);
-        const float4* slab = g.points + static_cast<size_t>(f.x) * g.width + e0;
-        float4 p[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) p[u] = (static_cast<uint32_t>(u) < cnt) ? __ldg(slab + u) : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float qx = bs.wq[0][q], qy = bs.wq[1][q], qz = bs.wq[2][q];
-        float best_d2 = max_d2;
-        uint32_t best_u = 0;
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const float dx = qx - p[u].x, dy = qy - p[u].y, dz = qz - p[u].z;
-            const float d2 = dx * dx + (dy * dy + dz * dz);   // Vector3f::squaredNorm order
-            if (static_cast<uint32_t>(u) < cnt && d2 < best_d2) {   // strict: the piece's first minimum in slot order
-                best_d2 = d2;
-                best_u = u;
-            }
-        }
-        if (best_d2 < max_d2) {
-            const unsigned long long key = (static_cast<unsigned long long>(__float_as_uint(best_d2)) << 32) | (l << 24) | (e0 + best_u);
-            if (key < bs.best[q]) atomicMin(&bs.best[q], key);
-        }
-    }
-    __syncthreads();
-    LO_BS_TRACE(13);
-    // E
-    if (tid < nq) {
-        const unsigned long long key = bs.best[tid];
-        if (key != ~0ull) {
-            const uint32_t l = (static_cast<uint32_t>(key) >> 24) & 31u, slot = static_cast<uint32_t>(key) & 0xFFFFFFu;
-            const size_t at = static_cast<size_t>(bs.found[l * nq + tid].x) * g.width + slot;
-            const float4 o = __ldg(g.points + at), nv = __ldg(g.normals + at);
-            pr.valid = true;
-            pr.o[0] = o.x; pr.o[1] = o.y; pr.o[2] = o.z;
-            pr.n[0] = nv.x; pr.n[1] = nv.y; pr.n[2] = nv.z;
-        }
-    }
-    __syncthreads();   // bs is reused by the next pass
-    LO_BS_TRACE(14);
-    return pr;
-}
-
-// ---------------------------------------------------------------------------------------------------
-// CloudMatcher::align (src/cloud_matcher.cpp:105-178) as one persistent kernel of co-resident blocks.
 struct AlignArgs {
     GridView g;
     const PointXYZ* queries;
@@ -453,66 +181,57 @@ struct AlignArgs {
     const uint32_t* m_dev; // nullable: actual query count on the device (m is then an upper bound)
     float4* pair_o;        // [m] plane_origin, w = 1 if the query has a correspondence
     float4* pair_n;        // [m] plane_normal
-    double* partials;      // [2][gridDim.x][32]: rows of exchange_sum; zero-filled when allocated, written by nothing else
-    unsigned long long epoch_base = 0;   // unique per launch among the launches that share `partials`; low 16 bits zero
+    double* partials;      // [2][gridDim.x][32]
     const float* guess;    // device pose7
     float* out_pose;       // device pose7 (written by block 0)
     float* out_pose_block = nullptr;  // nullable: 7 floats in the caller's shared memory, written in every block
     lo_align_stats* stats; // device, nullable
     float max_dist;
-    long long* trace;      // nullable: (tag, clock64) pairs written by thread 0 of block trace_block (LO_ALIGN_TRACE / LO_SCAN_TRACE)
+    long long* trace;      // nullable: (tag, clock64) pairs written by block 0 thread 0 (LO_ALIGN_TRACE=1)
     int trace_start = 0;   // first free trace entry (the per-scan kernel has written some already)
-    uint32_t trace_block = 0;
 };
 
-#define LO_TRACE(tag)                                                                      \
-    do {                                                                                   \
-        if (a.trace && blockIdx.x == a.trace_block && threadIdx.x == 0 && trace_n < 500) { \
-            a.trace[2 * trace_n] = (tag);                                                  \
-            a.trace[2 * trace_n + 1] = clock64();                                          \
-            trace_n++;                                                                     \
-        }                                                                                  \
+#define LO_TRACE(tag)                                                          \
+    do {                                                                       \
+        if (a.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < 500) { \
+            a.trace[2 * trace_n] = (tag);                                      \
+            a.trace[2 * trace_n + 1] = clock64();                              \
+            trace_n++;                                                         \
+        }                                                                      \
     } while (0)
 
-// The body of align_kernel; also the middle part of the per-scan kernel of lo_pipeline.cu. Every thread of a grid of
-// co-resident kAlignThreads-wide blocks must call it. The blocks meet only in exchange_sum: there is no other
-// cross-block data flow (a block evaluates the correspondences it found itself; the LM step logic runs redundantly in
-// every block on identical sums).
-// `tile_scratch`: nullable, (kAlignThreads / 32) TileScratch in shared memory; with it, large query sets (>= 8 queries
-// per warp) are searched 32 per warp with exact neighbour pruning (lo_tile_search.cuh) instead of block-wide.
+// The body of align_kernel; also the middle part of the per-scan kernel of lo_pipeline.cu. Every thread of a
+// cooperative grid of kAlignThreads-wide blocks must call it.
+// `tile_scratch`: nullable, (kAlignThreads / 32) TileScratch in shared memory; with it, large query sets (several queries
+// per warp) are searched 32 per warp with exact neighbour pruning (lo_tile_search.cuh) instead of one per warp.
 constexpr size_t kAlignTileScratchBytes = (kAlignThreads / 32) * sizeof(TileScratch);
-__device__ inline void align_device(AlignArgs a, TileScratch* tile_scratch = nullptr) {
+__device__ inline void align_device(AlignArgs a, cg::grid_group& grid, TileScratch* tile_scratch = nullptr) {
     if (a.m_dev) a.m = min(a.m, *a.m_dev);
     __shared__ double rows[(kAlignThreads / 32) * kRow];
-    __shared__ double cols[32];   // the block's column sums of the evaluation in progress
     __shared__ double total[32];
     __shared__ LmState lm;
     __shared__ EvalPoint ep_s;
     __shared__ float pose_s[7];
     __shared__ int flag_s;
-    __shared__ BlockSearch bs;
+    __shared__ uint2 work[(kAlignThreads / 32) * kWorkListStride];
+    uint2* wl = work + (threadIdx.x >> 5) * kWorkListStride;
 
     const int lane = threadIdx.x & 31;
-    // tile search: consecutive tiles go to different SMs: warp w of block b is global warp w * gridDim.x + b
+    // consecutive queries / tiles go to different SMs: warp w of block b is global warp w * gridDim.x + b
     const uint32_t gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const uint32_t total_warps = (gridDim.x * blockDim.x) >> 5;
     const int nblocks = gridDim.x;
-    // the tile search handles voxels of up to kTileMaxWidth points; the block search walks a voxel in pieces of 4 whatever its width
+    const LaneOffset lofs = lane_offset(lane);
+    const uint32_t my_queries = gwarp < a.m ? (a.m - gwarp + total_warps - 1) / total_warps : 0u;
     const bool tiled = tile_scratch != nullptr && a.g.width <= kTileMaxWidth && a.m >= 8 * total_warps;
-    const uint32_t passes = (a.m + kBlockQueries * gridDim.x - 1) / (kBlockQueries * gridDim.x);   // block search: passes of 64 queries per block
     TileScratch* ts = tile_scratch ? tile_scratch + (threadIdx.x >> 5) : nullptr;
     double* row = rows + (threadIdx.x >> 5) * kRow;
     for (int k = threadIdx.x; k < (kAlignThreads / 32) * kRow; k += blockDim.x) rows[k] = 0.0;
-    if (threadIdx.x < 32) cols[threadIdx.x] = 0.0;
-    double* stage = reinterpret_cast<double*>(bs.found);   // 29 x 64 doubles over found + piece_start, free between two searches
-    static_assert(sizeof(bs.found) + sizeof(bs.piece_start) >= 29 * kBlockQueries * sizeof(double), "staging area of block_accumulate");
-    static_assert(offsetof(BlockSearch, piece_start) == offsetof(BlockSearch, found) + sizeof(bs.found), "found and piece_start are contiguous");
     if (threadIdx.x < 7) pose_s[threadIdx.x] = a.guess[threadIdx.x];
     __syncthreads();
     const double prior_b[3] = {static_cast<double>(a.guess[0]), static_cast<double>(a.guess[1]), static_cast<double>(a.guess[2])};
     const float max_d2 = a.max_dist * a.max_dist;  // voxel_grid.h:215
     int buf = 0;
-    unsigned long long epoch = a.epoch_base;
     int lm_total = 0;
     bool cont = false;  // meaningful in thread 0 only
     int trace_n = a.trace_start;
@@ -526,9 +245,12 @@ __device__ inline void align_device(AlignArgs a, TileScratch* tile_scratch = nul
         const QueryTransform tf = make_query_transform(pf);
         double x0[7] = {pf.w, pf.x, pf.y, pf.z, pf.t[0], pf.t[1], pf.t[2]};  // cloud_matcher.cpp:122-131
         const EvalPoint ep0 = make_eval_point(x0);
-        PairRegs mine;   // block search: the correspondence of this thread's query of pass 0 stays in registers for the LM evaluations
-        mine.valid = false;
-        // large query sets: query i in lane (i & 31) of the warp that owns tile i / 32
+        // every warp walks its queries (gwarp, gwarp + total_warps, ...: neighbouring queries cost about the same, so they are
+        // dealt out to different warps) in tiles of 32: lane l transforms query l (findMatchingPairs, voxel_grid.h:217-223),
+        // the 27-lane search runs once per query with the slot loads of query j+1 in flight while query j is scanned, lane j
+        // keeps the correspondence of query j; then the tile's normals are fetched in one round and all lanes evaluate
+        // their pair at x0 in parallel.
+        // large query sets: tile search, query i in lane (i & 31) of the warp that owns tile i / 32
         for (uint32_t base = gwarp * 32; tiled && base < a.m; base += total_warps * 32) {
             const uint32_t i = base + lane;
             const bool have = i < a.m;
@@ -545,23 +267,67 @@ __device__ inline void align_device(AlignArgs a, TileScratch* tile_scratch = nul
             const Terms t = pair_terms(ep0, pq, h.o, h.n);
             accumulate_warp<5>(row, t, h.valid, lane);
         }
-        for (uint32_t pass = 0; !tiled && pass < passes; pass++) {
-            const PairRegs pr = block_search(a.g, a.queries, a.m, pass, tf, max_d2, bs, a.trace, &trace_n, a.trace_block);
-            if (pass == 0) mine = pr;
-            Terms t;
-            if (threadIdx.x < kBlockQueries) {   // two warps hold the block's pairs, one per lane
-                const uint32_t i = block_query_index(pass, threadIdx.x);
-                if (i < a.m && pass > 0) {   // later passes are re-read from here by the evaluations
-                    a.pair_o[i] = make_float4(pr.o[0], pr.o[1], pr.o[2], pr.valid ? 1.f : 0.f);
-                    a.pair_n[i] = make_float4(pr.n[0], pr.n[1], pr.n[2], 0.f);
+        for (uint32_t base = 0; !tiled && base < my_queries; base += 32) {
+            const uint32_t mine = gwarp + (base + lane) * total_warps;
+            const bool have = base + lane < my_queries;
+            PointXYZ q{0.f, 0.f, 0.f, 0.f};
+            if (have) q = a.queries[mine];
+            const uint32_t in_tile = min(32u, my_queries - base);
+            float own[3];
+            transform_query(tf, q.x, q.y, q.z, own);
+            const int oi[3] = {clamp_axis(axis_index(own[0], a.g.voxel_size)), clamp_axis(axis_index(own[1], a.g.voxel_size)),
+                               clamp_axis(axis_index(own[2], a.g.voxel_size))};
+            bool my_valid = false;
+            float my_o[3] = {0.f, 0.f, 0.f}, my_n[3] = {0.f, 0.f, 0.f};
+            uint32_t my_at = 0;
+            Probe next = probe_issue_at(a.g, __shfl_sync(kFullMask, oi[0], 0), __shfl_sync(kFullMask, oi[1], 0), __shfl_sync(kFullMask, oi[2], 0), lofs);
+            for (uint32_t j = 0; j < in_tile; j++) {
+                uint32_t vid, cnt;
+                probe_resolve(a.g, next, vid, cnt);
+                const int jj = static_cast<int>(j);
+                const float cur[3] = {__shfl_sync(kFullMask, own[0], jj), __shfl_sync(kFullMask, own[1], jj), __shfl_sync(kFullMask, own[2], jj)};
+                if (j + 1 < in_tile)
+                    next = probe_issue_at(a.g, __shfl_sync(kFullMask, oi[0], jj + 1), __shfl_sync(kFullMask, oi[1], jj + 1),
+                                          __shfl_sync(kFullMask, oi[2], jj + 1), lofs);
+                const Hit hit = scan_candidates(a.g, cur, max_d2, lane, wl, vid, cnt);
+                if (lane == jj) {
+                    my_valid = hit.valid;
+                    my_at = hit.at;
+                    for (int k = 0; k < 3; k++) my_o[k] = hit.o[k];
                 }
-                if (pr.valid) t = pair_terms(ep0, pr.p, pr.o, pr.n);
             }
-            block_accumulate<kBlockQueries>(t, pr.valid, stage, cols);
+            if (my_valid) {
+                const float4 nv = __ldg(a.g.normals + my_at);
+                my_n[0] = nv.x; my_n[1] = nv.y; my_n[2] = nv.z;
+            }
+            if (have) {
+                a.pair_o[mine] = make_float4(my_o[0], my_o[1], my_o[2], my_valid ? 1.f : 0.f);
+                a.pair_n[mine] = make_float4(my_n[0], my_n[1], my_n[2], 0.f);
+            }
+            const float pq[3] = {q.x, q.y, q.z};
+            const Terms t = pair_terms(ep0, pq, my_o, my_n);
+            if (in_tile <= 4) accumulate_warp<2>(row, t, my_valid, lane);
+            else if (in_tile <= 8) accumulate_warp<3>(row, t, my_valid, lane);
+            else accumulate_warp<5>(row, t, my_valid, lane);
         }
-        if (tiled) rows_to_cols(rows, cols);
         LO_TRACE(1);
-        exchange_sum(cols, rows, a.partials, nblocks, buf, ++epoch, total);
+        block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
+        grid.sync();
+        LO_TRACE(2);
+        // this warp's first tile of pairs stays in registers for every LM evaluation of this outer iteration
+        const uint32_t i0 = gwarp * 32 + lane;
+        bool valid0 = false;
+        float pq0[3] = {0.f, 0.f, 0.f}, of0[3] = {0.f, 0.f, 0.f}, nf0[3] = {0.f, 0.f, 0.f};
+        if (i0 < a.m) {
+            const float4 o = __ldcg(a.pair_o + i0);
+            const float4 nv = __ldcg(a.pair_n + i0);
+            const PointXYZ q = a.queries[i0];
+            valid0 = o.w != 0.f;
+            pq0[0] = q.x; pq0[1] = q.y; pq0[2] = q.z;
+            of0[0] = o.x; of0[1] = o.y; of0[2] = o.z;
+            nf0[0] = nv.x; nf0[1] = nv.y; nf0[2] = nv.z;
+        }
+        reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, rows, total);
         LO_TRACE(3);
         buf ^= 1;
         if (threadIdx.x == 0) {
@@ -582,54 +348,43 @@ __device__ inline void align_device(AlignArgs a, TileScratch* tile_scratch = nul
             LO_TRACE(4);
             __syncthreads();
             if (!flag_s) break;
-            if (tiled) {
-                for (uint32_t base = gwarp * 32; base < a.m; base += total_warps * 32) {
-                    const uint32_t i = base + lane;
-                    bool valid = false;
-                    Terms t;
-                    if (i < a.m) {
-                        const float4 o = __ldcg(a.pair_o + i);
-                        valid = o.w != 0.f;
-                        if (valid) {
-                            const float4 nv = __ldcg(a.pair_n + i);
-                            const PointXYZ q = a.queries[i];
-                            const float pq[3] = {q.x, q.y, q.z}, of[3] = {o.x, o.y, o.z}, nf[3] = {nv.x, nv.y, nv.z};
-                            t = pair_terms(ep_s, pq, of, nf);
-                        }
-                    }
-                    if (!valid) {
-                        for (int k = 0; k < 6; k++) t.j[k] = 0.0;
-                        t.rc = 0.0;
-                        t.cost = 0.0;
-                    }
-                    accumulate_warp(row, t, valid, lane);
+            if (gwarp * 32 < a.m) {
+                Terms t;
+                if (valid0) {
+                    t = pair_terms(ep_s, pq0, of0, nf0);
+                } else {
+                    for (int k = 0; k < 6; k++) t.j[k] = 0.0;
+                    t.rc = 0.0;
+                    t.cost = 0.0;
                 }
-                rows_to_cols(rows, cols);
-            } else {
-                for (uint32_t pass = 0; pass < passes; pass++) {
-                    PairRegs pr = mine;
-                    if (pass > 0) {
-                        pr.valid = false;
-                        const uint32_t i = block_query_index(pass, threadIdx.x);
-                        if (threadIdx.x < kBlockQueries && i < a.m) {
-                            const float4 o = __ldcg(a.pair_o + i);
-                            pr.valid = o.w != 0.f;
-                            if (pr.valid) {
-                                const float4 nv = __ldcg(a.pair_n + i);
-                                const PointXYZ q = a.queries[i];
-                                pr.p[0] = q.x; pr.p[1] = q.y; pr.p[2] = q.z;
-                                pr.o[0] = o.x; pr.o[1] = o.y; pr.o[2] = o.z;
-                                pr.n[0] = nv.x; pr.n[1] = nv.y; pr.n[2] = nv.z;
-                            }
-                        }
+                accumulate_warp(row, t, valid0, lane);
+            }
+            for (uint32_t base = (gwarp + total_warps) * 32; base < a.m; base += total_warps * 32) {
+                const uint32_t i = base + lane;
+                bool valid = false;
+                Terms t;
+                if (i < a.m) {
+                    const float4 o = __ldcg(a.pair_o + i);
+                    valid = o.w != 0.f;
+                    if (valid) {
+                        const float4 nv = __ldcg(a.pair_n + i);
+                        const PointXYZ q = a.queries[i];
+                        const float pq[3] = {q.x, q.y, q.z}, of[3] = {o.x, o.y, o.z}, nf[3] = {nv.x, nv.y, nv.z};
+                        t = pair_terms(ep_s, pq, of, nf);
                     }
-                    Terms t;
-                    if (pr.valid) t = pair_terms(ep_s, pr.p, pr.o, pr.n);
-                    block_accumulate<kBlockQueries>(t, pr.valid, stage, cols);
                 }
+                if (!valid) {
+                    for (int k = 0; k < 6; k++) t.j[k] = 0.0;
+                    t.rc = 0.0;
+                    t.cost = 0.0;
+                }
+                accumulate_warp(row, t, valid, lane);
             }
             LO_TRACE(5);
-            exchange_sum(cols, rows, a.partials, nblocks, buf, ++epoch, total);
+            block_rows_to_global(rows, a.partials + (static_cast<size_t>(buf) * nblocks + blockIdx.x) * 32);
+            grid.sync();
+            LO_TRACE(6);
+            reduce_partials(a.partials + static_cast<size_t>(buf) * nblocks * 32, nblocks, rows, total);
             LO_TRACE(7);
             buf ^= 1;
             if (threadIdx.x == 0) {
@@ -659,7 +414,7 @@ __device__ inline void align_device(AlignArgs a, TileScratch* tile_scratch = nul
         __syncthreads();  // flag_s is rewritten by thread 0 at the top of the next solve
     }
     LO_TRACE(9);
-    if (a.trace && blockIdx.x == a.trace_block && threadIdx.x == 0) a.trace[1000] = trace_n;
+    if (a.trace && blockIdx.x == 0 && threadIdx.x == 0) a.trace[1000] = trace_n;
     if (threadIdx.x == 0) {  // cloud_matcher.cpp:175 Quaternionf::normalize()
         const float w = pose_s[3], x = pose_s[4], y = pose_s[5], z = pose_s[6];
         const float nrm = sqrtf((x * x + z * z) + (y * y + w * w));

@@ -107,7 +107,7 @@ extern "C" void lo_ctx_destroy(lo_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (DevBuf* b : {&ctx->in_a, &ctx->in_b, &ctx->out_a, &ctx->out_b, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tmp_d, &ctx->small, &ctx->align_rows})
+    for (DevBuf* b : {&ctx->in_a, &ctx->in_b, &ctx->out_a, &ctx->out_b, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tmp_d, &ctx->small})
         b->release();
     ctx->pin_in.release();
     ctx->pin_out.release();

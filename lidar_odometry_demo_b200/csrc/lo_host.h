@@ -75,8 +75,6 @@ struct lo_ctx {
     lo::DevBuf small;             // small result block (counters, normal equations, poses)
     lo::PinnedBuf pin_in, pin_out;
     int align_blocks = 0;         // co-resident blocks of the align kernel (computed once)
-    lo::DevBuf align_rows;        // align_kernel: per-block rows of the fused grid-wide sum (lo_align.cuh exchange_sum)
-    unsigned long long align_epoch = 0;   // launches of align_kernel so far: every launch gets its own epoch range
 };
 
 // Device counters of a grid (one uint32 array)

@@ -174,7 +174,8 @@ __global__ void normal_eq_finalize_kernel(const double* __restrict__ partials, i
 // CloudMatcher::align (src/cloud_matcher.cpp:105-178) as one persistent cooperative kernel (body: lo_align.cuh)
 __global__ void __launch_bounds__(kAlignThreads, 1) align_kernel(AlignArgs a) {
     extern __shared__ __align__(16) unsigned char tile_scratch[];
-    align_device(a, reinterpret_cast<TileScratch*>(tile_scratch));
+    cg::grid_group grid = cg::this_grid();
+    align_device(a, grid, reinterpret_cast<TileScratch*>(tile_scratch));
 }
 
 // enqueue align on the context's stream; every pointer is a device pointer
@@ -191,17 +192,13 @@ int align_enqueue(lo_grid* kf, const PointXYZ* d_queries, uint32_t m, const uint
         }
         ctx->align_blocks = per_sm * ctx->sm_count;
     }
-    // do not spin up more blocks than there is work for: the block-wide search wants a dozen queries per block
+    // do not spin up more blocks than there is work for: one warp per query in the search phase
     int blocks = ctx->align_blocks;
-    const int wanted = static_cast<int>((static_cast<uint64_t>(m) + 15) / 16);
+    const int wanted = static_cast<int>((static_cast<uint64_t>(m) * 32 + kAlignThreads - 1) / kAlignThreads);
     blocks = std::max(1, std::min(blocks, wanted));
     LO_TRY(ctx->tmp_a.ensure(std::max<size_t>(m, 1) * sizeof(float4)));
     LO_TRY(ctx->tmp_b.ensure(std::max<size_t>(m, 1) * sizeof(float4)));
-    const size_t row_bytes = static_cast<size_t>(2) * ctx->align_blocks * 32 * sizeof(double);
-    if (ctx->align_rows.cap < row_bytes) {   // rows of exchange_sum: their epoch words must never hold a stale match
-        LO_TRY(ctx->align_rows.ensure(row_bytes));
-        LO_CUDA(cudaMemsetAsync(ctx->align_rows.p, 0, ctx->align_rows.cap, ctx->stream));
-    }
+    LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(2) * ctx->align_blocks * 32 * sizeof(double)));
     AlignArgs args;
     args.g = kf->view();
     args.queries = d_queries;
@@ -209,8 +206,7 @@ int align_enqueue(lo_grid* kf, const PointXYZ* d_queries, uint32_t m, const uint
     args.m_dev = d_m;
     args.pair_o = ctx->tmp_a.as<float4>();
     args.pair_n = ctx->tmp_b.as<float4>();
-    args.partials = ctx->align_rows.as<double>();
-    args.epoch_base = (++ctx->align_epoch) << 16;
+    args.partials = ctx->tmp_c.as<double>();
     args.guess = d_guess7;
     args.out_pose = d_out7;
     args.stats = d_stats;

@@ -89,8 +89,6 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
         off += (bytes + 255) & ~static_cast<size_t>(255);
         return p;
     };
-    // first, at an offset that does not depend on n: the rows of exchange_sum are written by nothing else, ever
-    b.partials = reinterpret_cast<double*>(take(static_cast<size_t>(2) * kMaxPipeBlocks * 32 * 8));
     b.hist = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
     b.layout = reinterpret_cast<uint32_t*>(take(16));
     b.block_counts = reinterpret_cast<uint32_t*>(take(3 * kMaxPipeBlocks * 4));
@@ -117,6 +115,7 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.kf_base = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.pair_o = reinterpret_cast<float4*>(take(static_cast<size_t>(n) * 16));
     b.pair_n = reinterpret_cast<float4*>(take(static_cast<size_t>(n) * 16));
+    b.partials = reinterpret_cast<double*>(take(static_cast<size_t>(2) * kMaxPipeBlocks * 32 * 8));
     return off;
 }
 
@@ -271,15 +270,23 @@ __device__ inline void chunk_range(uint32_t total, uint32_t& begin, uint32_t& en
     end = min(total, begin + per);
 }
 
-// sum of counts[0..blockIdx.x) and of all gridDim.x counts; result valid in every thread
+// sum of counts[0..blockIdx.x) and of all gridDim.x counts; result valid in every thread. The (<= kMaxPipeBlocks) counts
+// are read by one warp with all its loads in flight at once: one round trip to L2, not one per 32 counts (the dependent
+// rounds cost ~4 k cycles per call, five calls per scan).
 __device__ inline void block_prefix(const uint32_t* __restrict__ counts, uint32_t& before, uint32_t& all) {
     __shared__ uint32_t sh[2];
     if (threadIdx.x < 32) {
+        uint32_t v[kMaxPipeBlocks / 32];
+#pragma unroll
+        for (uint32_t u = 0; u < kMaxPipeBlocks / 32; u++) {
+            const uint32_t k = threadIdx.x + 32 * u;
+            v[u] = k < gridDim.x ? __ldcg(counts + k) : 0u;
+        }
         uint32_t b = 0, a = 0;
-        for (uint32_t k = threadIdx.x; k < gridDim.x; k += 32) {
-            const uint32_t v = counts[k];
-            a += v;
-            if (k < blockIdx.x) b += v;
+#pragma unroll
+        for (uint32_t u = 0; u < kMaxPipeBlocks / 32; u++) {
+            a += v[u];
+            if (threadIdx.x + 32 * u < blockIdx.x) b += v[u];
         }
         for (int off = 16; off > 0; off >>= 1) {
             b += __shfl_xor_sync(0xFFFFFFFFu, b, off);
@@ -413,7 +420,9 @@ __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map a
 
 // P7. winners of the two down-samplers: update winners get their ideal robin_map bucket (histogrammed), matching
 // winners are counted per block for the ordered compaction of P8
-__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match) {
+// do_u: the update winners' part (robin_map buckets; only the key-frame insert needs it, so it runs after the pose is out);
+// do_m: the matching winners' part (the query set align needs)
+__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match, bool do_u, bool do_m) {
     uint32_t before, total;
     block_prefix(b.block_counts, before, total);   // total = n_planar
     const uint32_t buckets = robin_bucket_count(s->n_update), bin_shift = robin_bin_shift(buckets);
@@ -424,7 +433,7 @@ __device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match
         const uint32_t i = base + threadIdx.x;
         bool wm = false;
         if (i < end) {
-            const uint32_t su = b.slot_u[i];
+            const uint32_t su = do_u ? b.slot_u[i] : 0xFFFFFFFFu;
             uint32_t bucket = kNoBucket;
             if (su != 0xFFFFFFFFu && b.ds_u[su].ticket == i) {
                 long long ix, iy, iz;
@@ -433,15 +442,15 @@ __device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match
                 atomicAdd(&b.rb_hist[bucket], 1u);
                 atomicAdd(&b.rb_coarse[bucket >> bin_shift], 1u);
             }
-            b.ubucket[i] = bucket;
-            if (with_match) {
+            if (do_u) b.ubucket[i] = bucket;
+            if (with_match && do_m) {
                 const uint32_t sm = b.slot_m[i];
                 wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
             }
         }
         cm += __syncthreads_count(wm);
     }
-    if (threadIdx.x == 0) b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
+    if (threadIdx.x == 0 && do_m) b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
 }
 
 // exclusive prefix of v over the block's threads, and the block total
@@ -476,10 +485,10 @@ __device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
 // coarse bins, so every bin is scanned here by one block on its own (start of the bin = sum of the coarse counts before
 // it); P9 places the winners and orders every tie group by arrival; the insert reads them through the wrap rotation.
 __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
-                                  PointXYZ* __restrict__ query, int with_match) {
+                                  PointXYZ* __restrict__ query, int with_match, bool do_u, bool do_m) {
     uint32_t before, total, bm, nm;
-    block_prefix(b.block_counts, before, total);
-    if (with_match) {
+    if (with_match && do_m) {
+        block_prefix(b.block_counts, before, total);
         block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
         uint32_t begin, end;
         chunk_range(total, begin, end);
@@ -500,7 +509,7 @@ __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNorma
         }
     }
     const uint32_t n = s->n_update;
-    if (n == 0) return;
+    if (n == 0 || !do_u) return;
     const uint32_t C = robin_bucket_count(n);
     const uint32_t shift = robin_bin_shift(C), bins = C >> shift, per = 1u << shift;   // bins <= kRobinBins <= blockDim.x
     for (uint32_t bin = blockIdx.x; bin < bins; bin += gridDim.x) {
@@ -634,15 +643,15 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     phase_scatter(s, p.b, p.filtered, p.vs_u, p.vs_m, with_match, range_err);
     grid.sync();
     LO_SCAN_TRACE(106);
-    phase_select(s, p.b, with_match);
-    grid.sync();
-    LO_SCAN_TRACE(107);
-    phase_emit(s, p.b, p.filtered, p.query, with_match);
-    grid.sync();
-    LO_SCAN_TRACE(108);
-    phase_robin_place(p.b);
-    grid.sync();
-    LO_SCAN_TRACE(109);
+    // the query set align needs: winners of the matching down-sampler, in arrival order (the bootstrap scan has none)
+    if (with_match) {
+        phase_select(s, p.b, with_match, false, true);
+        grid.sync();
+        LO_SCAN_TRACE(107);
+        phase_emit(s, p.b, p.filtered, p.query, with_match, false, true);
+        grid.sync();
+        LO_SCAN_TRACE(108);
+    }
     __shared__ float next_s[7];
     __shared__ Pose current_s;
     __shared__ uint32_t unstable_s;
@@ -671,7 +680,6 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         a.pair_o = p.b.pair_o;
         a.pair_n = p.b.pair_n;
         a.partials = p.b.partials;
-        a.epoch_base = static_cast<unsigned long long>(p.seq) << 16;   // exchange_sum: epochs are unique across the scans of a handle
         a.guess = reinterpret_cast<const float*>(&s->guess);
         a.out_pose = reinterpret_cast<float*>(&s->next);
         a.stats = &s->align;
@@ -683,9 +691,9 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         // ~6 k queries stay on the per-query search. Same winners either way (lo_tile_search.cuh).
         if constexpr (kTiled) {
             extern __shared__ __align__(16) unsigned char tile_scratch[];
-            align_device(a, reinterpret_cast<TileScratch*>(tile_scratch));
+            align_device(a, grid, reinterpret_cast<TileScratch*>(tile_scratch));
         } else {
-            align_device(a);
+            align_device(a, grid);
         }
         if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_n = static_cast<int>(p.trace[1000]);
         // every block runs the gate on the (identical) result: no grid-wide hand-over; block 0 stores the state at the end
@@ -697,15 +705,25 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
             if (blockIdx.x == 0) publish_pose(current_s, unstable_s);
         }
         __syncthreads();
-        LO_SCAN_TRACE(120);
-        for (uint32_t sl = blockIdx.x * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += gridDim.x * blockDim.x)
-            grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
-        grid.sync();
-        LO_SCAN_TRACE(121);
         insert_pose = &current_s;        // transformWithNormals fused into the load (cpp:69)
     } else if (blockIdx.x == 0 && threadIdx.x == 0) {
         publish_pose(s->current, s->unstable);   // bootstrap scan: the pose does not move (cpp:40-44)
     }
+    // ---- behind the pose: everything only the key frame needs -------------------------------------------------
+    LO_SCAN_TRACE(120);
+    if (!first)
+        for (uint32_t sl = blockIdx.x * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += gridDim.x * blockDim.x)
+            grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
+    // keyframe_downsampler.getCloud() in robin_map order (cpp:38,42,69): winners -> bucket histogram | bucket starts | placement
+    phase_select(s, p.b, with_match, true, false);
+    grid.sync();
+    LO_SCAN_TRACE(121);
+    phase_emit(s, p.b, p.filtered, p.query, with_match, true, false);
+    grid.sync();
+    LO_SCAN_TRACE(125);
+    phase_robin_place(p.b);
+    grid.sync();
+    LO_SCAN_TRACE(126);
     // keyframe_.addCloud(update) (cpp:42 / cpp:70)
     // the update cloud is read in place: output position d of the robin_map order is sorted element (d - rot) mod n,
     // rot = how far the last cluster runs past the last bucket (positions >= C wrap to the front and are iterated first)
@@ -760,11 +778,7 @@ using namespace lo;
 int lo::fused_reserve(lo_odometry* h, uint32_t n) {
     PipeBufs b;
     n = std::max<uint32_t>(n, 1);
-    const size_t fused_bytes = carve(b, nullptr, n);
-    if (h->fused.cap < fused_bytes) {   // the rows of exchange_sum live in here: their epoch words must start out as "no epoch"
-        LO_TRY(h->fused.ensure(fused_bytes));
-        LO_CUDA(cudaMemsetAsync(h->fused.p, 0, h->fused.cap, h->ctx->stream));
-    }
+    LO_TRY(h->fused.ensure(carve(b, nullptr, n)));
     LO_TRY(h->deskewed.ensure(static_cast<size_t>(n) * sizeof(PointXYZIRT)));
     LO_TRY(h->filtered.ensure(static_cast<size_t>(n) * sizeof(PointNormal)));
     LO_TRY(h->query.ensure(static_cast<size_t>(n) * sizeof(PointXYZ)));
