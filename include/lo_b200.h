@@ -80,6 +80,11 @@ int lo_grid_add_cloud_dev(lo_grid* g, const void* d_points, size_t n, int has_no
  * that were filled by add_cloud calls only (no radius_cleanup) — the down-sampler use of lidar_odometry.cpp:37-50.
  * *n receives the number of points; LO_E_CAPACITY if cap is too small. out may be NULL to query *n. */
 int lo_grid_get_cloud(lo_grid* g, int mode, int order, void* out, size_t cap, size_t* n);
+/* The iteration order of the reference's container on its own (third-party/robin-map robin_hash.h, as src/voxel_grid.h:82-87
+ * fills it): order_out[d] = index of the key at iteration position d after n DISTINCT keys with the 22-bit hashes hash22[0..n)
+ * (IndicesHash, src/voxel_grid.h:31-38) were inserted in index order into an empty map. This is the block-local replay the
+ * per-scan kernel runs for keyframe_downsampler.getCloud() (src/lidar_odometry.cpp:38,69); n <= 16 384 (LO_E_CAPACITY). */
+int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, size_t n, uint32_t* order_out);
 /* radiusCleanup (:236-246): erase voxels whose FIRST stored point is farther than radius from center */
 int lo_grid_radius_cleanup(lo_grid* g, const float center[3], float radius);
 
@@ -274,7 +279,9 @@ typedef struct lo_scan_stats {
     int32_t outer_iterations;
     int32_t unstable;            /* 1 if the divergence gate fell back to the prediction */
     uint32_t keyframe_voxels;
-    uint32_t reserved;
+    uint32_t order_approximate;  /* 0: the update cloud entered the key frame in the exact tsl::robin_map iteration order (every
+                                    scan of up to 16 384 update points); 1: ties inside one ideal bucket were taken in
+                                    arrival order (larger scans, or a key set with > 2 048 consecutive occupied buckets) */
 } lo_scan_stats;
 
 /* LidarOdometry(const Params&) (lidar_odometry.cpp:14-20). All device memory a scan needs is allocated here, once: the

@@ -65,7 +65,7 @@ class KeyframeInfo(C.Structure):
 class ScanStats(C.Structure):
     _fields_ = [("n_points", C.c_uint32), ("n_planar", C.c_uint32), ("n_update", C.c_uint32), ("n_query", C.c_uint32),
                 ("outer_iterations", C.c_int32), ("unstable", C.c_int32), ("keyframe_voxels", C.c_uint32),
-                ("reserved", C.c_uint32)]
+                ("order_approximate", C.c_uint32)]
 
 
 _vp, _sz, _fl, _i = C.c_void_p, C.c_size_t, C.c_float, C.c_int
@@ -81,7 +81,7 @@ SIGNATURES = {
     "lo_classify_pair": (_i, [_vp, _vp, _sz, _vp, _sz, C.POINTER(_sz), _vp, _sz, C.POINTER(_sz)]), "lo_grid_size": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz)]),
     "lo_grid_add_cloud": (_i, [_vp, _vp, _sz, _i]), "lo_grid_add_cloud_dev": (_i, [_vp, _vp, _sz, _i]),
     "lo_grid_get_cloud": (_i, [_vp, _i, _i, _vp, _sz, C.POINTER(_sz)]),
-    "lo_grid_radius_cleanup": (_i, [_vp, _vp, _fl]),
+    "lo_grid_radius_cleanup": (_i, [_vp, _vp, _fl]), "lo_robin_iteration_order": (_i, [_vp, _vp, _sz, _vp]),
     "lo_grid_snapshot": (_i, [_vp, _vp, _sz, C.POINTER(_sz)]), "lo_grid_restore": (_i, [_vp, _vp, _sz]),
     "lo_odometry_snapshot": (_i, [_vp, _vp, _sz, C.POINTER(_sz)]), "lo_odometry_restore": (_i, [_vp, _vp, _sz]),
     "lo_grid_find_matching_pairs": (_i, [_vp, _vp, _sz, _vp, _fl, _vp, _vp, C.POINTER(_sz)]),
@@ -182,6 +182,13 @@ class Context:
     @property
     def kernel_launches(self):
         return int(self.lib.lo_ctx_kernel_launches(self.h))
+
+    def robin_iteration_order(self, hash22):
+        """Iteration order of the reference's tsl::robin_map after inserting distinct keys with these hashes in index order."""
+        h = np.ascontiguousarray(hash22, dtype=np.uint32)
+        out = np.empty(len(h), np.uint32)
+        _check(self.lib.lo_robin_iteration_order(self.h, _p(h), len(h), _p(out)))
+        return out
 
     def voxel_keys(self, voxel_size, cloud):
         cloud = np.ascontiguousarray(cloud, dtype=XYZ)

@@ -57,7 +57,8 @@ struct ScanReadback {
     uint32_t pose_seq;    // scan number, written after a system-scope fence once everything above is final
     uint32_t kf_counters[GC_COUNT];
     uint32_t seq;         // scan number, written last (after a system-scope fence)
-    uint32_t pad[3];
+    uint32_t order_approximate;   // 1: the update cloud went into the key frame in the counting-sort order, not the replayed one
+    uint32_t pad[2];
 };
 
 }  // namespace lo

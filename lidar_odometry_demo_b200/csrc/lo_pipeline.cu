@@ -36,6 +36,7 @@
 #include "lo_align.cuh"
 #include "lo_grid.cuh"
 #include "lo_odometry.cuh"
+#include "lo_robin_block.cuh"
 #include "lo_stages.cuh"
 
 namespace lo {
@@ -63,6 +64,8 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     uint32_t* slot_u;                      // [n] slot of filtered point i in ds_u
     uint32_t* slot_m;                      // [n]
     uint32_t* ubucket;                     // [n] ideal robin_map bucket of filtered point i if it is an update winner, else ~0
+    uint32_t* uarr;                        // [n] update winners in arrival order (index into filtered) = the reference's insertion order
+    uint32_t* uhash;                       // [n] their 22-bit reference hashes
     uint32_t* usorted;                     // [n] update winners in robin_map order (index into filtered)
     uint32_t* umember;                     // [n] bucket members before a tie group is ordered
     uint32_t* rb_hist;                     // [rb_cap] winners per ideal bucket, then exclusive start of each bucket
@@ -70,6 +73,7 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     uint32_t* rb_done;                     // [rb_cap] members of a tie group that have been placed
     uint32_t* rb_coarse;                   // [kRobinBins] update winners per coarse bin of buckets
     int* rb_shift;                         // [1] max over sorted elements of (bucket - position)
+    uint32_t* robin_refused;               // [1] the block-local replay refused this scan's key set (a run of > 2048 occupied buckets)
     uint32_t* kf_slot;                     // [n] key-frame insert: slot of update point i
     uint32_t* kf_base;                     // [n] key-frame insert: first free entry of its voxel
     float4* pair_o;                        // [n] align: plane origin per query (w = valid)
@@ -101,6 +105,8 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.slot_u = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.slot_m = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.ubucket = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.uarr = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.uhash = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.usorted = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.umember = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     uint32_t rb = 2;
@@ -110,6 +116,7 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.rb_fill = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
     b.rb_done = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
     b.rb_shift = reinterpret_cast<int*>(take(16));
+    b.robin_refused = reinterpret_cast<uint32_t*>(take(16));
     b.rb_coarse = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
     b.kf_slot = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.kf_base = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
@@ -420,37 +427,47 @@ __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map a
 
 // P7. winners of the two down-samplers: update winners get their ideal robin_map bucket (histogrammed), matching
 // winners are counted per block for the ordered compaction of P8
-// do_u: the update winners' part (robin_map buckets; only the key-frame insert needs it, so it runs after the pose is out);
-// do_m: the matching winners' part (the query set align needs)
-__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match, bool do_u, bool do_m) {
+// do_hist: the update winners get their ideal robin_map bucket and are histogrammed (the counting-sort order, used where the
+// exact block-local replay does not apply); do_count: the winners of both down-samplers are counted per block for the
+// ordered compactions of P8 (queries for align; update winners in arrival order for the replay)
+__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match, bool do_hist, bool do_count) {
     uint32_t before, total;
     block_prefix(b.block_counts, before, total);   // total = n_planar
     const uint32_t buckets = robin_bucket_count(s->n_update), bin_shift = robin_bin_shift(buckets);
     uint32_t begin, end;
     chunk_range(total, begin, end);
-    uint32_t cm = 0;
+    uint32_t cm = 0, cu = 0;
     for (uint32_t base = begin; base < end; base += blockDim.x) {
         const uint32_t i = base + threadIdx.x;
-        bool wm = false;
+        bool wm = false, wu = false;
         if (i < end) {
-            const uint32_t su = do_u ? b.slot_u[i] : 0xFFFFFFFFu;
-            uint32_t bucket = kNoBucket;
-            if (su != 0xFFFFFFFFu && b.ds_u[su].ticket == i) {
-                long long ix, iy, iz;
-                unpack_key(b.ds_u[su].key, ix, iy, iz);
-                bucket = reference_hash22(ix, iy, iz) & (buckets - 1);
-                atomicAdd(&b.rb_hist[bucket], 1u);
-                atomicAdd(&b.rb_coarse[bucket >> bin_shift], 1u);
+            const uint32_t su = b.slot_u[i];
+            wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+            if (do_hist) {
+                uint32_t bucket = kNoBucket;
+                if (wu) {
+                    long long ix, iy, iz;
+                    unpack_key(b.ds_u[su].key, ix, iy, iz);
+                    bucket = reference_hash22(ix, iy, iz) & (buckets - 1);
+                    atomicAdd(&b.rb_hist[bucket], 1u);
+                    atomicAdd(&b.rb_coarse[bucket >> bin_shift], 1u);
+                }
+                b.ubucket[i] = bucket;
             }
-            if (do_u) b.ubucket[i] = bucket;
-            if (with_match && do_m) {
+            if (with_match && do_count) {
                 const uint32_t sm = b.slot_m[i];
                 wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
             }
         }
-        cm += __syncthreads_count(wm);
+        if (do_count) {
+            cm += __syncthreads_count(wm);
+            cu += __syncthreads_count(wu);
+        }
     }
-    if (threadIdx.x == 0 && do_m) b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
+    if (threadIdx.x == 0 && do_count) {
+        b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
+        b.block_counts[1 * kMaxPipeBlocks + blockIdx.x] = cu;
+    }
 }
 
 // exclusive prefix of v over the block's threads, and the block total
@@ -486,26 +503,40 @@ __device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
 // it); P9 places the winners and orders every tie group by arrival; the insert reads them through the wrap rotation.
 __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
                                   PointXYZ* __restrict__ query, int with_match, bool do_u, bool do_m) {
-    uint32_t before, total, bm, nm;
-    if (with_match && do_m) {
+    uint32_t before, total, bm, nm, bu, nu;
+    if (do_m) {   // ordered compactions: the query cloud (if there is a key frame to match) and the update winners with their hashes
         block_prefix(b.block_counts, before, total);
         block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
+        block_prefix(b.block_counts + 1 * kMaxPipeBlocks, bu, nu);
         uint32_t begin, end;
         chunk_range(total, begin, end);
         for (uint32_t base = begin; base < end; base += blockDim.x) {
             const uint32_t i = base + threadIdx.x;
-            bool wm = false;
+            bool wm = false, wu = false;
+            uint32_t su = 0xFFFFFFFFu;
             if (i < end) {
-                const uint32_t sm = b.slot_m[i];
-                wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
+                su = b.slot_u[i];
+                wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+                if (with_match) {
+                    const uint32_t sm = b.slot_m[i];
+                    wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
+                }
             }
-            uint32_t tm;
+            uint32_t tm, tu;
             const uint32_t rm = block_rank(wm, tm);
+            const uint32_t ru = block_rank(wu, tu);
             if (wm) {
                 const float4 p = *reinterpret_cast<const float4*>(filtered + i);
                 reinterpret_cast<float4*>(query)[bm + rm] = make_float4(p.x, p.y, p.z, 1.f);
             }
+            if (wu) {
+                long long ix, iy, iz;
+                unpack_key(b.ds_u[su].key, ix, iy, iz);
+                b.uarr[bu + ru] = i;
+                b.uhash[bu + ru] = reference_hash22(ix, iy, iz);
+            }
             bm += tm;
+            bu += tu;
         }
     }
     const uint32_t n = s->n_update;
@@ -643,15 +674,14 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     phase_scatter(s, p.b, p.filtered, p.vs_u, p.vs_m, with_match, range_err);
     grid.sync();
     LO_SCAN_TRACE(106);
-    // the query set align needs: winners of the matching down-sampler, in arrival order (the bootstrap scan has none)
-    if (with_match) {
-        phase_select(s, p.b, with_match, false, true);
-        grid.sync();
-        LO_SCAN_TRACE(107);
-        phase_emit(s, p.b, p.filtered, p.query, with_match, false, true);
-        grid.sync();
-        LO_SCAN_TRACE(108);
-    }
+    // winners of the two down-samplers, in arrival order: the query set align needs (none on the bootstrap scan), and the
+    // update set with its hashes = the reference map's insertion sequence, for the robin_map order below
+    phase_select(s, p.b, with_match, false, true);
+    grid.sync();
+    LO_SCAN_TRACE(107);
+    phase_emit(s, p.b, p.filtered, p.query, with_match, false, true);
+    grid.sync();
+    LO_SCAN_TRACE(108);
     __shared__ float next_s[7];
     __shared__ Pose current_s;
     __shared__ uint32_t unstable_s;
@@ -690,8 +720,8 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         // large query sets (a 128-beam scan has ~10^5 queries: more than 8 per warp) take the tile search; a VLP16 scan's
         // ~6 k queries stay on the per-query search. Same winners either way (lo_tile_search.cuh).
         if constexpr (kTiled) {
-            extern __shared__ __align__(16) unsigned char tile_scratch[];
-            align_device(a, grid, reinterpret_cast<TileScratch*>(tile_scratch));
+            extern __shared__ __align__(16) unsigned char dyn_smem[];
+            align_device(a, grid, reinterpret_cast<TileScratch*>(dyn_smem));
         } else {
             align_device(a, grid);
         }
@@ -711,29 +741,48 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     }
     // ---- behind the pose: everything only the key frame needs -------------------------------------------------
     LO_SCAN_TRACE(120);
-    if (!first)
+    // keyframe_downsampler.getCloud() (cpp:38,42,69) in the EXACT iteration order of the reference's tsl::robin_map: block 0
+    // replays the map's history in shared memory (lo_robin_block.cuh) while the other blocks run radiusCleanup (cpp:67).
+    const uint32_t nu = min(p.n, s->n_update);
+    bool exact_order = false;
+    if constexpr (!kTiled) exact_order = nu <= kRobinBlockMax && gridDim.x > 1;
+    if (exact_order) {
+        if (blockIdx.x == 0) {
+            extern __shared__ __align__(16) unsigned char dyn_smem[];
+            const bool ok = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);
+            if (threadIdx.x == 0) *p.b.robin_refused = ok ? 0u : 1u;
+        } else if (!first) {
+            for (uint32_t sl = (blockIdx.x - 1) * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += (gridDim.x - 1) * blockDim.x)
+                grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
+        }
+        grid.sync();
+        LO_SCAN_TRACE(121);
+        if (__ldcg(p.b.robin_refused)) exact_order = false;   // a degenerate key set: the counting-sort order below takes over
+    } else if (!first) {
         for (uint32_t sl = blockIdx.x * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += gridDim.x * blockDim.x)
             grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
-    // keyframe_downsampler.getCloud() in robin_map order (cpp:38,42,69): winners -> bucket histogram | bucket starts | placement
-    phase_select(s, p.b, with_match, true, false);
-    grid.sync();
-    LO_SCAN_TRACE(121);
-    phase_emit(s, p.b, p.filtered, p.query, with_match, true, false);
-    grid.sync();
-    LO_SCAN_TRACE(125);
-    phase_robin_place(p.b);
-    grid.sync();
-    LO_SCAN_TRACE(126);
-    // keyframe_.addCloud(update) (cpp:42 / cpp:70)
-    // the update cloud is read in place: output position d of the robin_map order is sorted element (d - rot) mod n,
-    // rot = how far the last cluster runs past the last bucket (positions >= C wrap to the front and are iterated first)
-    const uint32_t nu = min(p.n, s->n_update);
-    uint32_t gather_shift = 0;
-    if (nu) {
-        const long long over = static_cast<long long>(nu) + *p.b.rb_shift - static_cast<long long>(robin_bucket_count(nu));
-        const uint32_t rot = over > 0 ? static_cast<uint32_t>(over % nu) : 0u;
-        gather_shift = (nu - rot) % nu;
     }
+    uint32_t gather_shift = 0;
+    if (!exact_order) {
+        // Counting sort by ideal bucket with the wrap rotation (large scans; refused key sets): exact between different
+        // ideal buckets, groups of equal ideal bucket in arrival order. Output position d of the robin_map order is sorted
+        // element (d - rot) mod n, rot = how far the last cluster runs past the last bucket.
+        phase_select(s, p.b, with_match, true, false);
+        grid.sync();
+        LO_SCAN_TRACE(127);
+        phase_emit(s, p.b, p.filtered, p.query, with_match, true, false);
+        grid.sync();
+        LO_SCAN_TRACE(125);
+        phase_robin_place(p.b);
+        grid.sync();
+        LO_SCAN_TRACE(126);
+        if (nu) {
+            const long long over = static_cast<long long>(nu) + *p.b.rb_shift - static_cast<long long>(robin_bucket_count(nu));
+            const uint32_t rot = over > 0 ? static_cast<uint32_t>(over % nu) : 0u;
+            gather_shift = (nu - rot) % nu;
+        }
+    }
+    // keyframe_.addCloud(update) (cpp:42 / cpp:70); the update cloud is read in place through the order
     const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
         grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
@@ -756,6 +805,7 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         }
         ScanReadback* out = p.readback;
         for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
+        out->order_approximate = exact_order ? 0u : 1u;
         p.minmax[0] = 0xFFFFFFFFu;
         p.minmax[1] = 0u;
         __threadfence_system();
@@ -795,8 +845,9 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     if (blocks_per_sm == 0) {
         int large_per_sm = 0;
         LO_CUDA(cudaFuncSetAttribute(scan_kernel_large, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kAlignTileScratchBytes)));
+        LO_CUDA(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
         LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&large_per_sm, scan_kernel_large, kPipeThreads, kAlignTileScratchBytes));
-        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, 0));
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, kRobinBlockSmemBytes));
         blocks_per_sm = std::min(blocks_per_sm, large_per_sm);
         if (blocks_per_sm < 1) {
             set_error("the per-scan kernel does not fit on an SM");
@@ -841,7 +892,7 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     void* kargs[] = {&p};
     const cudaError_t e =
         n <= kSmallScanPoints
-            ? cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream)
+            ? cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, kRobinBlockSmemBytes, ctx->stream)
             : cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel_large), dim3(blocks), dim3(kPipeThreads), kargs,
                                           kAlignTileScratchBytes, ctx->stream);
     if (e != cudaSuccess) {   // nothing was queued: the scan number and the tickets stay where they were

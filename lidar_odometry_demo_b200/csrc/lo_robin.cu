@@ -19,6 +19,7 @@
 #include <cub/cub.cuh>
 
 #include "lo_host.h"
+#include "lo_robin_block.cuh"
 
 namespace lo {
 
@@ -209,8 +210,52 @@ int robin_export_bounded(lo_grid* g, int mode, void* d_out, uint32_t* d_count, u
     return LO_OK;
 }
 
+// the block-local epoch replay of lo_robin_block.cuh (what the per-scan kernel runs) on its own
+__global__ void __launch_bounds__(512, 1) robin_order_block_kernel(const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n,
+                                                                   uint32_t* __restrict__ out, uint32_t* __restrict__ refused) {
+    extern __shared__ __align__(16) unsigned char robin_smem[];
+    const bool ok = robin_order_block(uh, ids, n, robin_smem, out);
+    if (threadIdx.x == 0) *refused = ok ? 0u : 1u;
+}
+
 int robin_export_dev(lo_grid* g, int mode, void* d_out, uint32_t* d_count) {
     return robin_export_bounded(g, mode, d_out, d_count, g->h_counters[GC_VOXELS]);
 }
 
 }  // namespace lo
+
+using namespace lo;
+
+// order_out[d] = index (into hash22) of the key at iteration position d of a tsl::robin_map<..., IndicesHash> into which n
+// DISTINCT keys with these hashes were inserted in index order (src/voxel_grid.h:82-87 on an empty map)
+extern "C" int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, size_t n, uint32_t* order_out) {
+    if (!ctx || (!hash22 && n) || (!order_out && n)) return LO_E_ARG;
+    if (n > kRobinBlockMax) {
+        set_error("lo_robin_iteration_order takes at most %u keys (got %zu)", kRobinBlockMax, n);
+        return LO_E_CAPACITY;
+    }
+    if (n == 0) return LO_OK;
+    LO_CUDA(cudaSetDevice(ctx->device));
+    LO_TRY(ctx->tmp_a.ensure(n * sizeof(uint32_t)));
+    LO_TRY(ctx->tmp_b.ensure(n * sizeof(uint32_t)));
+    LO_TRY(ctx->tmp_c.ensure(n * sizeof(uint32_t)));
+    std::vector<uint32_t> iota(n);
+    for (size_t k = 0; k < n; k++) iota[k] = static_cast<uint32_t>(k);
+    LO_CUDA(cudaMemcpyAsync(ctx->tmp_a.p, hash22, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(ctx->tmp_b.p, iota.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    LO_CUDA(cudaFuncSetAttribute(robin_order_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
+    uint32_t* d_refused = ctx->small.as<uint32_t>() + 96;
+    robin_order_block_kernel<<<1, 512, kRobinBlockSmemBytes, ctx->stream>>>(ctx->tmp_a.as<uint32_t>(), ctx->tmp_b.as<uint32_t>(), static_cast<uint32_t>(n),
+                                                                             ctx->tmp_c.as<uint32_t>(), d_refused);
+    LO_LAUNCHED(ctx);
+    uint32_t refused = 0;
+    LO_CUDA(cudaMemcpyAsync(order_out, ctx->tmp_c.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaMemcpyAsync(&refused, d_refused, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LO_CUDA(cudaStreamSynchronize(ctx->stream));   // iota must outlive the copy
+    if (refused) {
+        set_error("lo_robin_iteration_order: a run of more than %u occupied buckets (degenerate hashes); the block-local replay refuses it — "
+                  "VoxelGrid::getCloud* (lo_grid_get_cloud, order 1) replays any key set", kRobinBlockMaxCluster);
+        return LO_E_RANGE;
+    }
+    return LO_OK;
+}

@@ -8,7 +8,7 @@ import pytest
 
 import lidar_odometry_demo_b200 as lo
 import oracle
-from util import PN, planar_scene
+from util import PN, planar_scene, sort_rows
 
 pytestmark = pytest.mark.gpu
 F = ("x", "y", "z", "nx", "ny", "nz")
@@ -109,3 +109,90 @@ def test_scan_downsamplers(ctx, real_map, port, stream12):
             o.add_cloud(planar)
             assert g.getCloud(reference_order=True).tobytes() == o.get_cloud().tobytes()
             assert g.getCloudWithoutNormals(reference_order=True).tobytes() == o.get_cloud_xyz().tobytes()
+
+
+# ---- the block-local epoch replay (csrc/lo_robin_block.cuh: what the per-scan kernel runs) on its own ------------------------
+def _real_order(real_map, keys, rng):
+    """Iteration order of the real container for these voxel keys inserted in this order: index into `keys` per position."""
+    cloud = cloud_of(keys, rng)
+    o = real_map.grid(1.0, 1)
+    o.add_cloud(cloud)
+    got = o.get_cloud()
+    lut = {(float(p["x"]), float(p["y"]), float(p["z"])): k for k, p in enumerate(cloud)}
+    return np.array([lut[(float(p["x"]), float(p["y"]), float(p["z"]))] for p in got], np.uint32)
+
+
+def _check_block_replay(ctx, real_map, keys, rng):
+    h = hash22(keys[:, 0], keys[:, 1], keys[:, 2]).astype(np.uint32)
+    got = ctx.robin_iteration_order(h)
+    want = _real_order(real_map, keys, rng)
+    assert np.array_equal(got, want), f"n = {len(keys)}: first difference at position {int(np.flatnonzero(got != want)[0])}"
+
+
+def test_block_replay_random_sizes_across_every_epoch_boundary(ctx, real_map):
+    rng = np.random.default_rng(21)
+    keys, _ = candidate_keys(30)
+    sizes = [1, 2, 3, 4, 5, 8, 9, 15, 16, 17, 31, 32, 33, 63, 64, 65, 127, 128, 129, 255, 256, 257, 511, 512, 513, 1000, 1024, 1025, 2048, 2049,
+             4095, 4096, 4097, 8191, 8192, 8193, 12345, 14000, 16383, 16384]
+    for n in sizes:
+        _check_block_replay(ctx, real_map, keys[rng.choice(len(keys), n, replace=False)], rng)
+
+
+def test_block_replay_forced_wrap_and_growth_collisions(ctx, real_map):
+    rng = np.random.default_rng(22)
+    keys, h = candidate_keys(40)
+    for n, window in ((6, 2), (40, 8), (200, 12), (200, 64), (1000, 30), (1900, 200)):
+        C = 2
+        while C < 2 * n:
+            C <<= 1
+        pool = np.flatnonzero((h & (C - 1)) >= C - window)
+        assert len(pool) >= n
+        _check_block_replay(ctx, real_map, keys[rng.choice(pool, n, replace=False)], rng)
+    # a degenerate key set (9 000 keys in 600 buckets: one run of 9 000 cells, beyond tsl's probe-distance limit) is refused,
+    # not answered wrongly; the sequential replay behind VoxelGrid::getCloud* takes it (test_forced_last_bucket_cluster_and_wrap)
+    pool = np.flatnonzero((h & 32767) >= 32768 - 600)
+    sel = keys[rng.choice(pool, 9000, replace=False)]
+    with pytest.raises(lo.LoError) as err:
+        ctx.robin_iteration_order(hash22(sel[:, 0], sel[:, 1], sel[:, 2]).astype(np.uint32))
+    assert err.value.code == lo.LO_E_RANGE
+    for n, low_bits, residues in ((64, 5, (31, 30)), (500, 6, (63, 0, 1)), (2000, 8, (255, 254, 7)), (6000, 9, (511, 0, 1, 2, 300))):
+        pool = np.flatnonzero(np.isin(h & ((1 << low_bits) - 1), residues))
+        if len(pool) < n:
+            continue
+        _check_block_replay(ctx, real_map, keys[rng.choice(pool, n, replace=False)], rng)
+
+
+def test_block_replay_scan_update_sets(ctx, real_map, port, stream12):
+    """The real use: the 0.1 m down-sampler of a scan's planar cloud (12-15 k voxels)."""
+    for k in (1, 5, 9):
+        planar = planar_scene(port, stream12[0], k)
+        keys_all, h_all = ctx.voxel_keys(0.1, np.ascontiguousarray(planar[["x", "y", "z", "pad0"]]).view(lo.XYZ) if False else _xyz_of(planar))
+        _, first = np.unique(keys_all, axis=0, return_index=True)
+        first.sort()                                  # voxels in order of first arrival = insertion order of the reference
+        got = ctx.robin_iteration_order(h_all[first])
+        o = real_map.grid(0.1, 1)
+        o.add_cloud(planar)
+        want = o.get_cloud()
+        sel = planar[first[got]]
+        assert len(sel) == len(want) and all(np.array_equal(sel[f].view(np.uint32), want[f].view(np.uint32)) for f in ("x", "y", "z"))
+
+
+def _xyz_of(pn):
+    out = np.zeros(len(pn), lo.XYZ)
+    out["x"], out["y"], out["z"], out["pad"] = pn["x"], pn["y"], pn["z"], 1.0
+    return out
+
+
+def test_per_scan_kernel_inserts_in_the_replayed_order(ctx, real_map, stream12):
+    """The fused per-scan kernel (csrc/lo_pipeline.cu) feeds keyframe_.addCloud(update) (lidar_odometry.cpp:42,70) in the
+    replayed order: after every scan the key frame holds the same points in the same per-voxel slots as the real container
+    pipeline, the pose is the same to the bit pattern of the tolerance, and the stats say the order was the exact one."""
+    od, oc = lo.LidarOdometry(ctx), real_map.odometry()
+    for k, s in enumerate(stream12[0]):
+        od.processCloud(s)
+        oc.process(s)
+        st = od.stats()
+        assert st.order_approximate == 0, k
+        a, b = od.getKeyFrameCloudWithNormals(), oc.keyframe_pn()
+        assert len(a) == len(b), k
+        assert np.array_equal(sort_rows(a), sort_rows(b)), f"key frames differ after scan {k}"

@@ -1,6 +1,7 @@
 #!/bin/bash
 # One warm scan_kernel launch under `ncu --set full` with source correlation; summaries into gpurun_out/ (the report itself only if small).
 mkdir -p gpurun_out
+export PYTHONPATH="$(pwd)${PYTHONPATH:+:$PYTHONPATH}"
 cat > /tmp/drive_scans.py <<'PY'
 import lidar_odometry_demo_b200 as lo
 from bench import make_stream
