@@ -274,14 +274,21 @@ typedef struct lo_params {               /* LidarOdometry::Params (lidar_odometr
 void lo_params_default(lo_params* p);                      /* GetROSDeclaration defaults (lidar_odometry.h:36-48) */
 int lo_params_from_yaml(const char* path, lo_params* p);  /* reads config/params.yaml's lidar_odometry block */
 
+#define LO_ORDER_SORTED 0
+#define LO_ORDER_REPLAYED 1
+#define LO_ORDER_APPROXIMATE 2
 typedef struct lo_scan_stats {
     uint32_t n_points, n_planar, n_update, n_query;  /* N, P, U, M of SURVEY.md section 3.1 */
     int32_t outer_iterations;
     int32_t unstable;            /* 1 if the divergence gate fell back to the prediction */
     uint32_t keyframe_voxels;
-    uint32_t order_approximate;  /* 0: the update cloud entered the key frame in the exact tsl::robin_map iteration order (every
-                                    scan of up to 16 384 update points); 1: ties inside one ideal bucket were taken in
-                                    arrival order (larger scans, or a key set with > 2 048 consecutive occupied buckets) */
+    uint32_t update_order;       /* how the order in which the update cloud entered the key frame (tsl::robin_map iteration order,
+                                    lidar_odometry.cpp:38,42,69) was obtained. LO_ORDER_SORTED: counting sort by ideal bucket; no
+                                    group of equal ideal bucket had two points in one key-frame voxel, so the key frame is
+                                    exactly what the reference's order gives. LO_ORDER_REPLAYED: such a pair existed and the
+                                    map's insertion history was replayed: the exact order. LO_ORDER_APPROXIMATE: such a pair
+                                    existed but the replay did not apply (more than 16 384 update points, or more than 2 048
+                                    consecutive occupied buckets): groups of equal ideal bucket went in in arrival order */
 } lo_scan_stats;
 
 /* LidarOdometry(const Params&) (lidar_odometry.cpp:14-20). All device memory a scan needs is allocated here, once: the

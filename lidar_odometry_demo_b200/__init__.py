@@ -62,10 +62,13 @@ class KeyframeInfo(C.Structure):
         return {k: int(getattr(self, k)) for k, _ in self._fields_}
 
 
+LO_ORDER_SORTED, LO_ORDER_REPLAYED, LO_ORDER_APPROXIMATE = 0, 1, 2   # lo_scan_stats.update_order
+
+
 class ScanStats(C.Structure):
     _fields_ = [("n_points", C.c_uint32), ("n_planar", C.c_uint32), ("n_update", C.c_uint32), ("n_query", C.c_uint32),
                 ("outer_iterations", C.c_int32), ("unstable", C.c_int32), ("keyframe_voxels", C.c_uint32),
-                ("order_approximate", C.c_uint32)]
+                ("update_order", C.c_uint32)]
 
 
 _vp, _sz, _fl, _i = C.c_void_p, C.c_size_t, C.c_float, C.c_int

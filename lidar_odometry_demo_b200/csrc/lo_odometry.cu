@@ -159,7 +159,7 @@ static int finish_scan(lo_odometry* h, uint32_t n_points) {
     h->keyframe->cleaned = true;
     const int st = adopt_pose(h, *h->h_stage_readback, n_points);
     const int st2 = adopt_counters(h, h->h_stage_readback->kf_counters, false);
-    h->stats.order_approximate = 0;   // the staged pipeline replays the whole insertion history (lo_robin.cu)
+    h->stats.update_order = kOrderReplayed;   // the staged pipeline replays the whole insertion history (lo_robin.cu)
     return st != LO_OK ? st : st2;
 }
 
@@ -199,7 +199,7 @@ static int adopt_finished(lo_odometry* h, uint32_t upto, bool block) {
         h->pending_points -= h->queued_n[slot];
         if (h->adopt_seq == h->scan_seq) fused_trace_dump(h);
         const int s2 = adopt_counters(h, h->h_readback[slot].kf_counters, h->queued_rebuilds[slot] != h->keyframe->rebuild_count);
-        h->stats.order_approximate = h->h_readback[slot].order_approximate;   // known once the kernel's tail has run
+        h->stats.update_order = h->h_readback[slot].update_order;   // known once the kernel's tail has run
         if (st == LO_OK) st = s2;
     }
     return st;

@@ -48,6 +48,9 @@ __device__ inline void euler_angles_012(const float r[9], float ang[3]) {
 // on `pose_seq` — the reference's processCloud has nothing else to hand back — while the kernel's tail (cpp:67-70) runs on
 // behind them; whatever needs the key frame waits for `seq`. The stage-by-stage pipeline fills a device copy that is
 // fetched with one D2H.
+// lo_scan_stats.update_order (include/lo_b200.h)
+constexpr uint32_t kOrderSorted = 0, kOrderReplayed = 1, kOrderApproximate = 2;
+
 struct ScanReadback {
     float pose[7];
     uint32_t n_planar, n_update, n_query, unstable;
@@ -57,7 +60,7 @@ struct ScanReadback {
     uint32_t pose_seq;    // scan number, written after a system-scope fence once everything above is final
     uint32_t kf_counters[GC_COUNT];
     uint32_t seq;         // scan number, written last (after a system-scope fence)
-    uint32_t order_approximate;   // 1: the update cloud went into the key frame in the counting-sort order, not the replayed one
+    uint32_t update_order;   // kOrder*: how the update cloud's order was obtained (lo_scan_stats.update_order)
     uint32_t pad[2];
 };
 

@@ -73,7 +73,8 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     uint32_t* rb_done;                     // [rb_cap] members of a tie group that have been placed
     uint32_t* rb_coarse;                   // [kRobinBins] update winners per coarse bin of buckets
     int* rb_shift;                         // [1] max over sorted elements of (bucket - position)
-    uint32_t* robin_refused;               // [1] the block-local replay refused this scan's key set (a run of > 2048 occupied buckets)
+    uint32_t* robin_flags;                 // [0] a tie group with two members in one key-frame voxel was seen; [2] the rest of the
+                                           //     insert is left to scan_replay_kernel (1: with the pose, 2: bootstrap scan)
     uint32_t* kf_slot;                     // [n] key-frame insert: slot of update point i
     uint32_t* kf_base;                     // [n] key-frame insert: first free entry of its voxel
     float4* pair_o;                        // [n] align: plane origin per query (w = valid)
@@ -116,7 +117,7 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.rb_fill = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
     b.rb_done = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(rb) * 4));
     b.rb_shift = reinterpret_cast<int*>(take(16));
-    b.robin_refused = reinterpret_cast<uint32_t*>(take(16));
+    b.robin_flags = reinterpret_cast<uint32_t*>(take(16));
     b.rb_coarse = reinterpret_cast<uint32_t*>(take(kRobinBins * 4));
     b.kf_slot = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.kf_base = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
@@ -160,7 +161,10 @@ __device__ inline void phase_prep(OdomDev* s, const PointXYZIRT* __restrict__ in
     }
     if (tid < 256) b.hist[tid] = 0;
     if (tid < kRobinBins) b.rb_coarse[tid] = 0;
-    if (tid == 0) *b.rb_shift = INT_MIN;
+    if (tid == 0) {
+        *b.rb_shift = INT_MIN;
+        b.robin_flags[0] = b.robin_flags[1] = b.robin_flags[2] = 0u;
+    }
     for (uint32_t c = tid; c < b.rb_cap; c += nthreads) {
         b.rb_hist[c] = 0;
         b.rb_done[c] = 0;
@@ -594,6 +598,18 @@ __device__ inline void phase_robin_place(PipeBufs b) {
     if ((threadIdx.x & 31) == 0 && shift != INT_MIN) atomicMax(b.rb_shift, shift);
 }
 
+// the key-frame voxel an update point goes to: the arithmetic of grid_locate_item (load_point with the pose fused in, then
+// the reference's float division, voxel_grid.h:60-64); kKeyEmpty for a point the insert skips
+__device__ inline unsigned long long update_voxel_key(const PointNormal* __restrict__ filtered, uint32_t i, const Pose* pose, float voxel_size) {
+    const PointSource one{reinterpret_cast<const float*>(filtered), 12u, 1};
+    float q[3], nrm[3];
+    load_point(one, i, pose, q, nrm);
+    const long long ix = axis_index(q[0], voxel_size), iy = axis_index(q[1], voxel_size), iz = axis_index(q[2], voxel_size);
+    const bool finite = isfinite(q[0]) && isfinite(q[1]) && isfinite(q[2]);
+    if (!finite || !axis_in_range(ix) || !axis_in_range(iy) || !axis_in_range(iz)) return kKeyEmpty;
+    return pack_key(ix, iy, iz);
+}
+
 // lidar_odometry.cpp:53-65: Euler-angle divergence gate; returns the pose that becomes current_transform_
 __device__ inline Pose gate_pose(const Pose& nw, const Pose& cur, const Pose& guess, float threshold, uint32_t& unstable) {
     Pose a = identity_pose(), c = identity_pose();   // new.rotation * current.rotation.inverse()
@@ -632,8 +648,21 @@ struct ScanArgs {
     uint32_t seq;                // this scan's number, published in readback->seq when everything else is written
     uint32_t n;
     float lo2, hi2, vs_u, vs_m, cleanup_range, gate_threshold;
+    uint32_t force_replay;       // developer switch (LO_B200_REPLAY_ALWAYS): run the block replay on every scan it can take
     long long* trace;
 };
+
+// second half of the read-back block (one thread, when the key-frame insert is through); re-arms the next scan's time min/max
+__device__ inline void scan_publish_tail(const ScanArgs& p, uint32_t update_order) {
+    grid_fix_counters(p.kf_counters);
+    ScanReadback* out = p.readback;
+    for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
+    out->update_order = update_order;
+    p.minmax[0] = 0xFFFFFFFFu;
+    p.minmax[1] = 0u;
+    __threadfence_system();
+    *reinterpret_cast<volatile uint32_t*>(&out->seq) = p.seq;
+}
 
 // kTiled: align may use the tile search (scans with more than ~19 k queries); the VLP16-sized instantiation is compiled
 // without it so that its code and register allocation stay what they were tuned to.
@@ -741,53 +770,81 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     }
     // ---- behind the pose: everything only the key frame needs -------------------------------------------------
     LO_SCAN_TRACE(120);
-    // keyframe_downsampler.getCloud() (cpp:38,42,69) in the EXACT iteration order of the reference's tsl::robin_map: block 0
-    // replays the map's history in shared memory (lo_robin_block.cuh) while the other blocks run radiusCleanup (cpp:67).
+    // keyframe_downsampler.getCloud() (cpp:38,42,69): the update set in the iteration order of the reference's tsl::robin_map.
+    // (1) Counting sort by ideal bucket with the wrap rotation: exact between different ideal buckets; a tie group (equal
+    // ideal bucket) comes out in arrival order, while the map's order inside it depends on its whole history. Output
+    // position d of the order is sorted element (d - rot) mod n, rot = how far the last cluster runs past the last bucket.
+    // radiusCleanup (cpp:67) shares the first phase.
     const uint32_t nu = min(p.n, s->n_update);
-    bool exact_order = false;
-    if constexpr (!kTiled) exact_order = nu <= kRobinBlockMax && gridDim.x > 1;
-    if (exact_order) {
-        if (blockIdx.x == 0) {
-            extern __shared__ __align__(16) unsigned char dyn_smem[];
-            const bool ok = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);
-            if (threadIdx.x == 0) *p.b.robin_refused = ok ? 0u : 1u;
-        } else if (!first) {
-            for (uint32_t sl = (blockIdx.x - 1) * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += (gridDim.x - 1) * blockDim.x)
-                grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
-        }
-        grid.sync();
-        LO_SCAN_TRACE(121);
-        if (__ldcg(p.b.robin_refused)) exact_order = false;   // a degenerate key set: the counting-sort order below takes over
-    } else if (!first) {
+    if (!first) {
         for (uint32_t sl = blockIdx.x * blockDim.x + threadIdx.x; sl < p.kf_capacity; sl += gridDim.x * blockDim.x)
             grid_cleanup_slot(sl, p.kf, current_s.t, p.cleanup_range, p.kf_counters, p.kf_free_list);   // cpp:67
     }
+    phase_select(s, p.b, with_match, true, false);
+    grid.sync();
+    LO_SCAN_TRACE(121);
+    phase_emit(s, p.b, p.filtered, p.query, with_match, true, false);
+    grid.sync();
+    LO_SCAN_TRACE(125);
+    phase_robin_place(p.b);
+    grid.sync();
+    LO_SCAN_TRACE(126);
     uint32_t gather_shift = 0;
-    if (!exact_order) {
-        // Counting sort by ideal bucket with the wrap rotation (large scans; refused key sets): exact between different
-        // ideal buckets, groups of equal ideal bucket in arrival order. Output position d of the robin_map order is sorted
-        // element (d - rot) mod n, rot = how far the last cluster runs past the last bucket.
-        phase_select(s, p.b, with_match, true, false);
-        grid.sync();
-        LO_SCAN_TRACE(127);
-        phase_emit(s, p.b, p.filtered, p.query, with_match, true, false);
-        grid.sync();
-        LO_SCAN_TRACE(125);
-        phase_robin_place(p.b);
-        grid.sync();
-        LO_SCAN_TRACE(126);
-        if (nu) {
-            const long long over = static_cast<long long>(nu) + *p.b.rb_shift - static_cast<long long>(robin_bucket_count(nu));
-            const uint32_t rot = over > 0 ? static_cast<uint32_t>(over % nu) : 0u;
-            gather_shift = (nu - rot) % nu;
-        }
+    if (nu) {
+        const long long over = static_cast<long long>(nu) + *p.b.rb_shift - static_cast<long long>(robin_bucket_count(nu));
+        const uint32_t rot = over > 0 ? static_cast<uint32_t>(over % nu) : 0u;
+        gather_shift = (nu - rot) % nu;
     }
-    // keyframe_.addCloud(update) (cpp:42 / cpp:70); the update cloud is read in place through the order
-    const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
-        grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
+    // (2) keyframe_.addCloud(update) (cpp:42 / cpp:70), first pass: the key-frame voxel of every update point; the update cloud
+    // is read in place through the order. The order inside a tie group reaches the key frame only where two of its members
+    // fall into the SAME key-frame voxel (it decides their slots there, and which is dropped once the voxel is full,
+    // voxel_grid.h:82-91): the pass looks for such a pair. None (about 39 scans in 40 of the VLP16 stream): the key frame
+    // comes out exactly as from the reference's order.
+    uint32_t update_order = kOrderSorted;
+    bool can_replay = false;
+    if constexpr (!kTiled) can_replay = nu <= kRobinBlockMax && gridDim.x > 1;
+    {
+        const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
+        bool pair_found = false;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x) {
+            grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
+            uint32_t k = i + gather_shift;
+            if (k >= nu) k -= nu;
+            const uint32_t me = p.b.usorted[k], bucket = p.b.ubucket[me];
+            if (k + 1 < nu && p.b.ubucket[p.b.usorted[k + 1]] == bucket) {   // not the last of its tie group
+                const unsigned long long mine = update_voxel_key(p.filtered, me, insert_pose, p.kf.voxel_size);
+                for (uint32_t k2 = k + 1; k2 < nu; k2++) {
+                    const uint32_t other = p.b.usorted[k2];
+                    if (p.b.ubucket[other] != bucket) break;
+                    pair_found = pair_found || (mine != kKeyEmpty && update_voxel_key(p.filtered, other, insert_pose, p.kf.voxel_size) == mine);
+                }
+            }
+        }
+        if (pair_found) p.b.robin_flags[0] = 1u;
+    }
     grid.sync();
     LO_SCAN_TRACE(122);
+    // (3) such a pair exists: the rest of the insert is left to scan_replay_kernel, queued right behind this kernel: one block
+    // that replays the map's history in shared memory (lo_robin_block.cuh: 176 KB — as dynamic shared memory of THIS kernel
+    // it would leave 28 KB of L1 for its spills, +11 % on every scan) and finishes the insert in the exact order. A scan
+    // too large for the replay keeps the counting-sort order and says so in its stats.
+    if (__ldcg(p.b.robin_flags) || (p.force_replay && can_replay)) {
+        if (can_replay) {
+            if (blockIdx.x == 0 && threadIdx.x == 0) {
+                if (!first) {   // the gate's outcome becomes the state of the next scan; the replay kernel inserts with it
+                    s->current = current_s;
+                    s->unstable = unstable_s;
+                    s->center[0] = current_s.t[0]; s->center[1] = current_s.t[1]; s->center[2] = current_s.t[2];
+                }
+                p.b.robin_flags[2] = first ? 2u : 1u;
+                if (p.trace) p.trace[1000] = trace_n;
+            }
+            return;
+        }
+        update_order = kOrderApproximate;
+    }
+    const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
+
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nu; i += gridDim.x * blockDim.x)
         grid_chain_item(i, p.ticket_base, p.kf, p.b.kf_slot, p.b.kf_base);
     grid.sync();
@@ -796,20 +853,13 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
         grid_write_item(i, src, p.ticket_base, insert_pose, p.kf, p.kf_counters, p.b.kf_slot, p.b.kf_base);
     grid.sync();
     LO_SCAN_TRACE(124);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {   // second half of the read-back block; re-arm the next scan's time min/max
-        grid_fix_counters(p.kf_counters);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         if (!first) {                            // the gate's outcome becomes the state of the next scan
             s->current = current_s;
             s->unstable = unstable_s;
             s->center[0] = current_s.t[0]; s->center[1] = current_s.t[1]; s->center[2] = current_s.t[2];
         }
-        ScanReadback* out = p.readback;
-        for (int k = 0; k < GC_COUNT; k++) out->kf_counters[k] = p.kf_counters[k];
-        out->order_approximate = exact_order ? 0u : 1u;
-        p.minmax[0] = 0xFFFFFFFFu;
-        p.minmax[1] = 0u;
-        __threadfence_system();
-        *reinterpret_cast<volatile uint32_t*>(&out->seq) = p.seq;
+        scan_publish_tail(p, update_order);
         if (p.trace) p.trace[1000] = trace_n;
     }
 #undef LO_SCAN_TRACE
@@ -818,6 +868,41 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
 __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) { scan_body<false>(p); }
 __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel_large(ScanArgs p) { scan_body<true>(p); }
 constexpr uint32_t kSmallScanPoints = 32768;   // scans up to this size (a VLP16 revolution is ~30 k) run scan_kernel
+
+// Queued behind every scan_kernel; returns at once unless that kernel left the insert to it (a tie group with two members
+// in one key-frame voxel: about one VLP16 scan in 40). One block: the exact tsl::robin_map iteration order of the update
+// set (lo_robin_block.cuh), then keyframe_.addCloud(update) (lidar_odometry.cpp:42,70) in that order — the three passes of
+// the insert separated by block barriers — and the second half of the read-back block.
+__global__ void __launch_bounds__(kPipeThreads, 1) scan_replay_kernel(ScanArgs p) {
+    const uint32_t deferred = p.b.robin_flags[2];
+    if (!deferred) return;
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    OdomDev* s = p.s;
+    const uint32_t nu = min(p.n, s->n_update);
+    const bool exact = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);   // refused: usorted is untouched
+    __shared__ Pose pose_s;
+    if (threadIdx.x == 0) pose_s = s->current;
+    __syncthreads();
+    const Pose* insert_pose = deferred == 2u ? nullptr : &pose_s;
+    uint32_t gather_shift = 0;
+    if (!exact && nu) {   // a run of more than 2 048 occupied buckets: the counting-sort order and its rotation stand
+        const long long over = static_cast<long long>(nu) + *p.b.rb_shift - static_cast<long long>(robin_bucket_count(nu));
+        const uint32_t rot = over > 0 ? static_cast<uint32_t>(over % nu) : 0u;
+        gather_shift = (nu - rot) % nu;
+    }
+    const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
+    if (exact) {   // the first pass again, in the new order: it finds the voxels scan_kernel created
+        for (uint32_t i = threadIdx.x; i < nu; i += blockDim.x)
+            grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
+        __syncthreads();
+    }
+    for (uint32_t i = threadIdx.x; i < nu; i += blockDim.x) grid_chain_item(i, p.ticket_base, p.kf, p.b.kf_slot, p.b.kf_base);
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < nu; i += blockDim.x)
+        grid_write_item(i, src, p.ticket_base, insert_pose, p.kf, p.kf_counters, p.b.kf_slot, p.b.kf_base);
+    __syncthreads();
+    if (threadIdx.x == 0) scan_publish_tail(p, exact ? kOrderReplayed : kOrderApproximate);
+}
 
 }  // namespace lo
 
@@ -845,9 +930,9 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     if (blocks_per_sm == 0) {
         int large_per_sm = 0;
         LO_CUDA(cudaFuncSetAttribute(scan_kernel_large, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kAlignTileScratchBytes)));
-        LO_CUDA(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
+        LO_CUDA(cudaFuncSetAttribute(scan_replay_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
         LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&large_per_sm, scan_kernel_large, kPipeThreads, kAlignTileScratchBytes));
-        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, kRobinBlockSmemBytes));
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, 0));
         blocks_per_sm = std::min(blocks_per_sm, large_per_sm);
         if (blocks_per_sm < 1) {
             set_error("the per-scan kernel does not fit on an SM");
@@ -883,6 +968,8 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     p.vs_m = h->params.keyframe_matching_voxel_size;
     p.cleanup_range = h->params.keyframe_cleanup_range;
     p.gate_threshold = h->params.angular_divergence_threshold;
+    static const bool replay_always = getenv("LO_B200_REPLAY_ALWAYS") != nullptr;
+    p.force_replay = replay_always ? 1u : 0u;
     static const bool want_trace = getenv("LO_SCAN_TRACE") != nullptr;   // developer aid, see fused_trace_dump
     p.trace = nullptr;
     if (want_trace) {
@@ -892,7 +979,7 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     void* kargs[] = {&p};
     const cudaError_t e =
         n <= kSmallScanPoints
-            ? cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, kRobinBlockSmemBytes, ctx->stream)
+            ? cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel), dim3(blocks), dim3(kPipeThreads), kargs, 0, ctx->stream)
             : cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_kernel_large), dim3(blocks), dim3(kPipeThreads), kargs,
                                           kAlignTileScratchBytes, ctx->stream);
     if (e != cudaSuccess) {   // nothing was queued: the scan number and the tickets stay where they were
@@ -902,6 +989,10 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     }
     h->scan_seq = p.seq;
     ctx->launches++;
+    if (n <= kSmallScanPoints) {   // returns at once unless scan_kernel left the insert to it (see there)
+        scan_replay_kernel<<<1, kPipeThreads, kRobinBlockSmemBytes, ctx->stream>>>(p);
+        LO_LAUNCHED(ctx);
+    }
     return LO_OK;
 }
 

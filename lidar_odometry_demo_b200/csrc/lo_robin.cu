@@ -19,6 +19,9 @@
 #include <cub/cub.cuh>
 
 #include "lo_host.h"
+#include <cstdio>
+#include <cstdlib>
+
 #include "lo_robin_block.cuh"
 
 namespace lo {
@@ -212,9 +215,9 @@ int robin_export_bounded(lo_grid* g, int mode, void* d_out, uint32_t* d_count, u
 
 // the block-local epoch replay of lo_robin_block.cuh (what the per-scan kernel runs) on its own
 __global__ void __launch_bounds__(512, 1) robin_order_block_kernel(const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n,
-                                                                   uint32_t* __restrict__ out, uint32_t* __restrict__ refused) {
+                                                                   uint32_t* __restrict__ out, uint32_t* __restrict__ refused, long long* prof) {
     extern __shared__ __align__(16) unsigned char robin_smem[];
-    const bool ok = robin_order_block(uh, ids, n, robin_smem, out);
+    const bool ok = robin_order_block(uh, ids, n, robin_smem, out, prof);
     if (threadIdx.x == 0) *refused = ok ? 0u : 1u;
 }
 
@@ -245,9 +248,28 @@ extern "C" int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, siz
     LO_CUDA(cudaMemcpyAsync(ctx->tmp_b.p, iota.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     LO_CUDA(cudaFuncSetAttribute(robin_order_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
     uint32_t* d_refused = ctx->small.as<uint32_t>() + 96;
+    static const bool profile = getenv("LO_ROBIN_PROF") != nullptr;   // developer switch: cycles per phase of the replay on stderr
+    long long* d_prof = nullptr;
+    if (profile) {
+        LO_CUDA(cudaMalloc(&d_prof, 64 * sizeof(long long)));
+        LO_CUDA(cudaMemsetAsync(d_prof, 0, 64 * sizeof(long long), ctx->stream));
+    }
     robin_order_block_kernel<<<1, 512, kRobinBlockSmemBytes, ctx->stream>>>(ctx->tmp_a.as<uint32_t>(), ctx->tmp_b.as<uint32_t>(), static_cast<uint32_t>(n),
-                                                                             ctx->tmp_c.as<uint32_t>(), d_refused);
+                                                                             ctx->tmp_c.as<uint32_t>(), d_refused, d_prof);
     LO_LAUNCHED(ctx);
+    if (profile) {
+        long long h_prof[64];
+        LO_CUDA(cudaMemcpyAsync(h_prof, d_prof, sizeof(h_prof), cudaMemcpyDeviceToHost, ctx->stream));
+        LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        LO_CUDA(cudaFree(d_prof));
+        static const char* names[14] = {"", "E1 clear", "E2 histogram", "E3 scan", "E4 wrap", "E5 place", "A labels", "R2 lengths", "R3 rank",
+                                        "P park", "W walk", "-", "-", "E7 order"};
+        fprintf(stderr, "robin replay n = %zu:", n);
+        for (int k = 1; k <= 13; k++) fprintf(stderr, " %s %lld |", names[k], h_prof[k]);
+        fprintf(stderr, "\n  per epoch:");
+        for (int k = 32; k < 48; k++) fprintf(stderr, " %lld", h_prof[k]);
+        fprintf(stderr, "\n");
+    }
     uint32_t refused = 0;
     LO_CUDA(cudaMemcpyAsync(order_out, ctx->tmp_c.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     LO_CUDA(cudaMemcpyAsync(&refused, d_refused, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));

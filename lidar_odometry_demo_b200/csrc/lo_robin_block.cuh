@@ -15,10 +15,19 @@
 // runs of occupied cells) are known up front, nothing ever enters or leaves a final cluster's cells, and the history of a
 // cluster involves its own members only. So per epoch: counting sort of the sequence by ideal bucket, cluster heads from a
 // prefix maximum (element t of the sorted order sits at t + max_{u<=t}(b_u - u); a new cluster starts where that maximum
-// rises), then one thread per cluster replays the literal robin-hood insertion of its members, in sequence order, on the
-// cluster's handful of cells. The iteration order of the epoch's table (the clusters' cells in position order; the w cells
-// that ran past the last bucket come first) is the next epoch's re-insertion sequence, and the last one is the answer.
-// Identical to the sequential replay of lo_robin.cu, which tests/test_gpu_robin.py pins to the real container.
+// rises), and then the history of every cluster WITHOUT replaying it cell by cell:
+//   * robin_hash.h:1283-1317 swaps only with a strictly richer resident, and the cells of a run are sorted by ideal bucket,
+//     so the insertion of x (ideal cell a) does exactly this: x goes to the end of its own group (the elements with ideal
+//     cell a), and every following group of the run up to the first empty cell e has its first element carried to its
+//     end (a rotation by one; the group moves one cell up). e is the first empty cell >= a — plain linear probing.
+//   * hence, per cluster: (1) the members in sequence order (rank by counting, all members in parallel); (2) e of every
+//     insertion, one thread per cluster with an occupancy bitmap in registers; (3) every member on its own: start at the
+//     end of its group, then walk the LATER insertions (a', e') of the cluster: one of its own group -> the group grew;
+//     a' < a < e' -> the group was rotated: index 0 goes to the end, the others move down. Its final cell is the group's
+//     first cell + that index. O(cluster length) independent loads per member instead of a serial replay per cluster.
+// The iteration order of the epoch's table (the clusters' cells in position order; the w cells that ran past the last
+// bucket come first) is the next epoch's re-insertion sequence, and the last one is the answer. Identical to the
+// sequential replay of lo_robin.cu, which tests/test_gpu_robin.py pins to the real container.
 #pragma once
 
 #include <limits.h>
@@ -28,18 +37,20 @@ namespace lo {
 
 constexpr uint32_t kRobinBlockMax = 16384;          // elements the shared-memory replay takes (a VLP16 update set is 12-15 k)
 constexpr uint32_t kRobinBlockBuckets = 2 * kRobinBlockMax;
-// A cluster longer than this is refused (the function returns false): one thread replays a cluster, so a long one would
-// crawl, and past 8192 cells tsl's probe-distance limit (robin_hash.h:327) adds growth steps this replay does not model.
+// A cluster longer than this is refused (the function returns false): step (2) is serial per cluster (and quadratic beyond
+// 64 cells), and past 8192 cells tsl's probe-distance limit (robin_hash.h:327) adds growth steps this replay does not model.
 // Hash-random keys at load <= 0.5 give clusters of tens of cells; the sequential replay of lo_robin.cu takes anything.
 constexpr uint32_t kRobinBlockMaxCluster = 2048;
 // uint16 arrays: start[C] | seq[n] | stash[n] | cells[n] | prev[n / 2]
 constexpr size_t kRobinBlockSmemBytes = 2 * (kRobinBlockBuckets + 3 * kRobinBlockMax + kRobinBlockMax / 2);
 
 struct RobinBlockSmem {
-    uint16_t* start;   // [C]  counts -> exclusive starts (bit 15: the bucket heads a cluster) -> ends after the placement
-    uint16_t* seq;     // [n]  sequence indices grouped by bucket, then each cluster's in sequence order; E7: scratch
-    uint16_t* stash;   // [n]  ideal bucket of sequence element s
-    uint16_t* cells;   // [n]  the occupied cells in position order from the first non-wrapped one: sequence index of the resident
+    uint16_t* start;   // [C]  counts -> exclusive starts (bit 15: the bucket heads a cluster) -> ends after the placement;
+                       //      dead after the labels: [0, n) = ideal cell of a cluster's k-th insertion, [n, 2n) = the cell it filled
+    uint16_t* seq;     // [n]  sequence indices grouped by bucket (sorted position t); E7: scratch
+    uint16_t* stash;   // [n]  ideal bucket of sequence element s; dead after R3: the occupied cells in position order from the
+                       //      first non-wrapped one: sequence index of the resident
+    uint16_t* cells;   // [n]  cluster label (sorted position of the cluster's first element; there: bit 15 | members)
     uint16_t* prev;    // [n/2] previous epoch's iteration order (element ids)
 };
 __device__ inline RobinBlockSmem robin_block_carve(unsigned char* base) {
@@ -52,10 +63,12 @@ __device__ inline RobinBlockSmem robin_block_carve(unsigned char* base) {
     return s;
 }
 
-// exclusive prefix sum and exclusive prefix maximum of one value per thread, and the block totals; blockDim.x <= 1024
-__device__ inline void robin_block_scan(uint32_t v, int g, uint32_t& v_before, int& g_before, uint32_t& v_all, int& g_all) {
-    __shared__ uint32_t ws[32];
-    __shared__ int wg[32];
+// exclusive prefix sum and exclusive prefix maximum of one value per thread, and the block totals; blockDim.x <= 1024.
+// One block barrier per call: every warp scans the per-warp totals itself; `slot` alternates between consecutive calls
+// (two sets of partials, so a warp still reading one call's partials is not overrun by the next call).
+__device__ inline void robin_block_scan(uint32_t v, int g, uint32_t& v_before, int& g_before, uint32_t& v_all, int& g_all, int slot) {
+    __shared__ uint32_t ws[2][32];
+    __shared__ int wg[2][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
     uint32_t vi = v;
     int gi = g;
@@ -68,50 +81,73 @@ __device__ inline void robin_block_scan(uint32_t v, int g, uint32_t& v_before, i
         }
     }
     if (lane == 31) {
-        ws[warp] = vi;
-        wg[warp] = gi;
+        ws[slot][warp] = vi;
+        wg[slot][warp] = gi;
     }
     __syncthreads();
-    uint32_t vb = 0, va = 0;
-    int gb = INT_MIN, ga = INT_MIN;
-    for (int w = 0; w < nwarps; w++) {
-        if (w < warp) {
-            vb += ws[w];
-            gb = max(gb, wg[w]);
+    uint32_t pv = lane < nwarps ? ws[slot][lane] : 0u;   // inclusive scan of the warp totals, in every warp
+    int pg = lane < nwarps ? wg[slot][lane] : INT_MIN;
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t uv = __shfl_up_sync(0xFFFFFFFFu, pv, off);
+        const int ug = __shfl_up_sync(0xFFFFFFFFu, pg, off);
+        if (lane >= off) {
+            pv += uv;
+            pg = max(pg, ug);
         }
-        va += ws[w];
-        ga = max(ga, wg[w]);
     }
+    v_all = __shfl_sync(0xFFFFFFFFu, pv, 31);
+    g_all = __shfl_sync(0xFFFFFFFFu, pg, 31);
+    const uint32_t vb = __shfl_sync(0xFFFFFFFFu, pv, max(warp - 1, 0));
+    const int gb = __shfl_sync(0xFFFFFFFFu, pg, max(warp - 1, 0));
     const uint32_t v_excl_in_warp = __shfl_up_sync(0xFFFFFFFFu, vi, 1);
     const int g_excl_in_warp = __shfl_up_sync(0xFFFFFFFFu, gi, 1);
-    v_before = vb + (lane ? v_excl_in_warp : 0u);
-    g_before = lane ? max(gb, g_excl_in_warp) : gb;
-    v_all = va;
-    g_all = ga;
-    __syncthreads();
+    const uint32_t warp_v = warp ? vb : 0u;
+    const int warp_g = warp ? gb : INT_MIN;
+    v_before = warp_v + (lane ? v_excl_in_warp : 0u);
+    g_before = lane ? max(warp_g, g_excl_in_warp) : warp_g;
+}
+
+// elements (16 bit) per thread for a contiguous-chunk pass: enough to cover `count` with `nthreads` threads, an even number
+// whose half is odd, so that the threads of a warp start in different shared-memory banks
+__device__ __forceinline__ uint32_t robin_block_chunk(uint32_t count, uint32_t nthreads) {
+    return 2u * (((count + 2u * nthreads - 1u) / (2u * nthreads)) | 1u);
 }
 
 // uh[k]: the reference's 22-bit hash of the k-th key in insertion (arrival) order, k < n <= kRobinBlockMax (global memory).
-// ids[k]: what to emit for element k. out[d] = ids[element at iteration position d]. All threads of ONE block call.
-// Returns false (in every thread; `out` is then unspecified) if a cluster exceeded kRobinBlockMaxCluster.
+// ids[k]: what to emit for element k. out[d] = ids[element at iteration position d]. All threads of ONE block of >= 512
+// threads call. Returns false (in every thread; `out` is then unspecified) if a cluster exceeded kRobinBlockMaxCluster.
 __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n, unsigned char* smem,
-                                         uint32_t* __restrict__ out) {
+                                         uint32_t* __restrict__ out, long long* prof = nullptr) {
+    // prof (developer aid, LO_ROBIN_PROF=1 with lo_robin_iteration_order): [phase] cycles summed over epochs, [32 + j] per epoch
+    long long prof_last = prof ? clock64() : 0;
+    auto mark = [&](int slot) {
+        if (prof && threadIdx.x == 0) {
+            const long long c = clock64();
+            prof[slot] += c - prof_last;
+            prof_last = c;
+        }
+    };
     const RobinBlockSmem sm = robin_block_carve(smem);
-    __shared__ uint32_t wrap_s, origin_s;
+    __shared__ uint32_t wrap_s;
     __shared__ int refused_s;
-    if (threadIdx.x == 0) refused_s = 0;
+    if (threadIdx.x == 0) refused_s = blockDim.x < 512 ? 1 : 0;
     __syncthreads();
+    if (refused_s) return false;
     const uint32_t tid = threadIdx.x, nthreads = blockDim.x;
-    constexpr uint16_t kEmpty = 0xFFFFu, kHead = 0x8000u, kVal = 0x7FFFu;
+    constexpr uint16_t kHead = 0x8000u, kVal = 0x7FFFu;
+    constexpr int kMaxOwn = kRobinBlockMax / 512;   // members per thread
+    uint16_t l_r[kMaxOwn];   // rank of my k-th member inside its cluster (the only state a thread carries between phases)
     uint32_t lo = 0;   // elements present before this epoch's arrivals = length of `prev`
     for (uint32_t j = 0; lo < n; j++) {
         const uint32_t C = 2u << j, mask = C - 1;
         const uint32_t hi = j == 0 ? 1u : min(n, 1u << j);   // arrivals of this epoch: element ids lo .. hi - 1
         const uint32_t ne = hi;                               // sequence S = prev[0 .. lo) ++ [lo .. hi): S[s] = s for s >= lo
         uint32_t* packed = reinterpret_cast<uint32_t*>(sm.start);
+        auto at = [&](uint32_t x) { return x >= ne ? x - ne : x; };   // sorted positions are cyclic (the cluster that wraps)
         // E1: clear the counts
-        for (uint32_t w = tid; w < (C + 1) / 2; w += nthreads) packed[w] = 0;
+        for (uint32_t w = tid; w < C / 2; w += nthreads) packed[w] = 0;
         __syncthreads();
+        mark(1);
         // E2: histogram of the ideal buckets (two 16-bit counters per word; a count is at most ne < 2^15)
         for (uint32_t s = tid; s < ne; s += nthreads) {
             const uint32_t e = s < lo ? sm.prev[s] : s;
@@ -120,26 +156,23 @@ __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const 
             atomicAdd(packed + (b >> 1), (b & 1u) ? 65536u : 1u);
         }
         __syncthreads();
-        // E3: counts -> exclusive starts, cluster heads, overflow past the last bucket. Thread t owns buckets [t per, (t+1) per).
-        const uint32_t per = (C + nthreads - 1) / nthreads;
+        mark(2);
+        // E3: counts -> exclusive starts, cluster heads, overflow past the last bucket. Thread t owns `per` consecutive buckets.
+        const uint32_t per = robin_block_chunk(C, nthreads);
         const uint32_t b_lo = min(C, tid * per), b_hi = min(C, b_lo + per);
         uint32_t sum = 0;
-        for (uint32_t b = b_lo; b < b_hi; b++) sum += sm.start[b];
+        int m = INT_MIN;   // max over my non-empty buckets of b - (elements of my earlier buckets)
+        for (uint32_t b = b_lo; b < b_hi; b++) {
+            const uint32_t c = sm.start[b];
+            if (c) m = max(m, static_cast<int>(b) - static_cast<int>(sum));
+            sum += c;
+        }
         uint32_t base, unused_all;
         int unused_g, unused_ga;
-        robin_block_scan(sum, INT_MIN, base, unused_g, unused_all, unused_ga);
-        int gmax = INT_MIN;   // g_b = b - start_b over my non-empty buckets
-        {
-            uint32_t run = base;
-            for (uint32_t b = b_lo; b < b_hi; b++) {
-                const uint32_t c = sm.start[b];
-                if (c) gmax = max(gmax, static_cast<int>(b) - static_cast<int>(run));
-                run += c;
-            }
-        }
+        robin_block_scan(sum, INT_MIN, base, unused_g, unused_all, unused_ga, 0);
         uint32_t unused_vb, unused_va;
-        int g_before, g_all;
-        robin_block_scan(0u, gmax, unused_vb, g_before, unused_va, g_all);
+        int g_before, g_all;   // g_b = b - start_b: where bucket b's first element would sit relative to its sorted index
+        robin_block_scan(0u, m == INT_MIN ? INT_MIN : m - static_cast<int>(base), unused_vb, g_before, unused_va, g_all, 1);
         {
             uint32_t run = base;
             int G = g_before;
@@ -160,6 +193,7 @@ __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const 
             wrap_s = over > 0 ? static_cast<uint32_t>(over) : 0u;
         }
         __syncthreads();
+        mark(3);
         // E4: the cluster that wraps swallows the front buckets it reaches: everything before the first bucket o with g_o > w
         if (tid == 0) {
             uint32_t o = 0;
@@ -171,9 +205,9 @@ __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const 
                     sm.start[o] = static_cast<uint16_t>(s0);   // no longer a head
                 }
             }
-            origin_s = o;
         }
         __syncthreads();
+        mark(4);
         // E5: placement (any order inside a bucket); start[b] ends up as the END of bucket b, the head bit stays
         for (uint32_t s = tid; s < ne; s += nthreads) {
             const uint32_t b = sm.stash[s];
@@ -182,117 +216,140 @@ __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const 
             sm.seq[t] = static_cast<uint16_t>(s);
         }
         __syncthreads();
-        const uint32_t w = wrap_s, origin = origin_s;
-        auto bucket_begin = [&](uint32_t b) { return b ? static_cast<uint32_t>(sm.start[b - 1] & kVal) : 0u; };
-        auto bucket_end = [&](uint32_t b) { return static_cast<uint32_t>(sm.start[b] & kVal); };
-        // E6a: every cluster head labels its members with the cluster's first sorted index (in `cells`, free until E6c)
-        for (uint32_t b0 = b_lo; b0 < b_hi; b0++) {
-            if (!(sm.start[b0] & kHead)) continue;
-            const uint32_t t0 = bucket_begin(b0);
-            uint32_t b = b0;
-            bool wrapped = false;
-            while (true) {
-                for (uint32_t t = bucket_begin(b); t < bucket_end(b); t++) sm.cells[t] = static_cast<uint16_t>(t0);
-                b++;
-                if (b == C) {
-                    if (!w) break;     // nothing ran past the last bucket
-                    b = 0;             // the wrapping cluster goes on through the front buckets up to `origin`
-                    wrapped = true;
+        const uint32_t w = wrap_s;
+        mark(5);
+        // A: label every sorted position with its cluster = the sorted position of the cluster's first element (the first
+        // element of a head bucket): a prefix maximum over contiguous chunks. Positions before the first head belong to the
+        // cluster that wraps = the last head.
+        {
+            const uint32_t q = robin_block_chunk(ne, nthreads);
+            const uint32_t t_lo = min(ne, tid * q), t_hi = min(ne, t_lo + q);
+            unsigned long long firsts = 0;
+            int last_first = INT_MIN;
+            for (uint32_t t = t_lo; t < t_hi; t++) {
+                const uint32_t b = sm.stash[sm.seq[t]];
+                if ((sm.start[b] & kHead) && t == (b ? static_cast<uint32_t>(sm.start[b - 1] & kVal) : 0u)) {
+                    firsts |= 1ull << (t - t_lo);
+                    last_first = static_cast<int>(t);
                 }
-                if (wrapped ? (b >= origin || b == b0) : (sm.start[b] & kHead) != 0) break;
+            }
+            uint32_t unused_b, unused_a;
+            int before, overall;
+            robin_block_scan(0u, last_first, unused_b, before, unused_a, overall, 0);
+            int label = before == INT_MIN ? overall : before;
+            for (uint32_t t = t_lo; t < t_hi; t++) {
+                if ((firsts >> (t - t_lo)) & 1ull) label = static_cast<int>(t);
+                sm.cells[t] = static_cast<uint16_t>(label);
             }
         }
         __syncthreads();
-        // E6b: every member finds its rank by sequence index inside its cluster (all members in parallel; clusters are short)
-        constexpr int kMaxOwn = (kRobinBlockMax + 255) / 256;   // members per thread at >= 256 threads
-        uint16_t own_rank[kMaxOwn];
-        {
-            int k = 0;
-            for (uint32_t t = tid; t < ne; t += nthreads, k++) {
-                const uint32_t t0 = sm.cells[t], mine = sm.seq[t];
-                uint32_t r = 0, u = t0;
-                for (uint32_t steps = 0; steps < ne; steps++) {
-                    if (sm.cells[u] != t0) break;
-                    r += sm.seq[u] < mine ? 1u : 0u;
-                    u = u + 1 == ne ? 0u : u + 1;
-                }
-                own_rank[k] = static_cast<uint16_t>(r);
-            }
-        }
-        __syncthreads();
-        {
-            int k = 0;
-            uint16_t own_seq[kMaxOwn];
-            for (uint32_t t = tid; t < ne; t += nthreads, k++) own_seq[k] = sm.seq[t];
-            __syncthreads();
-            k = 0;
-            for (uint32_t t = tid; t < ne; t += nthreads, k++) {
-                uint32_t at = static_cast<uint32_t>(sm.cells[t]) + own_rank[k];
-                if (at >= ne) at -= ne;
-                sm.seq[at] = own_seq[k];   // a permutation inside the cluster: its members in sequence (= insertion) order
-            }
-        }
-        __syncthreads();
-        // E6c: one thread per cluster replays robin_hash's insertion (robin_hash.h:1226-1317) on the cluster's own cells.
-        // Cell i of the cluster is table position (b0 + i) mod C and lives at cells[(t0 + i) mod ne]. The lengths are taken
-        // first, while the labels are intact everywhere (a neighbour's cells may hold anything once it has started).
-        constexpr int kMaxHeads = (kRobinBlockBuckets + 255) / 256;   // buckets per thread at >= 256 threads
-        uint16_t own_len[kMaxHeads];
-        {
-            int k = 0;
-            for (uint32_t b0 = b_lo; b0 < b_hi; b0++, k++) {
-                own_len[k] = 0;
-                if (!(sm.start[b0] & kHead)) continue;
-                const uint32_t t0 = bucket_begin(b0);
-                uint32_t L = 0;
-                for (uint32_t u = t0; L < ne && sm.cells[u] == t0; L++) u = u + 1 == ne ? 0u : u + 1;
-                own_len[k] = static_cast<uint16_t>(L);
-                if (L > kRobinBlockMaxCluster) refused_s = 1;
-            }
+        mark(6);
+        // `start` is dead from here: [0, n) = ideal cell of the cluster's k-th insertion, [n, 2n) = the empty cell it filled,
+        // both at sorted position (t0 + k) mod ne (cell i of a cluster = table position (b0 + i) mod C = sorted position
+        // (t0 + i) mod ne, so the cluster's cells and its insertions share one index range)
+        uint16_t* const atime = sm.start;
+        uint16_t* const etime = sm.start + kRobinBlockMax;
+        // R2: cluster lengths: every cluster's first element closes the cluster before it; the length replaces the (redundant)
+        // label of that cluster's first element: cells[t0] = kHead | length. Readers accept either form of a first element.
+        for (uint32_t t = tid; t < ne; t += nthreads) {
+            const uint32_t v = sm.cells[t];
+            if (!(v & kHead) && v != t) continue;
+            const uint32_t pv = sm.cells[t ? t - 1 : ne - 1], t_last = t ? t - 1 : ne - 1;
+            const uint32_t t_prev = (pv & kHead) ? t_last : pv;
+            const uint32_t len = t_prev == t ? ne : (t > t_prev ? t - t_prev : t + ne - t_prev);
+            sm.cells[t_prev] = static_cast<uint16_t>(kHead | len);
+            if (len > kRobinBlockMaxCluster) refused_s = 1;
         }
         __syncthreads();
         if (refused_s) return false;
+        mark(7);
+        auto cluster_of = [&](uint32_t t, uint32_t& t0, uint32_t& L) {
+            const uint32_t v = sm.cells[t];
+            t0 = (v & kHead) ? t : v;
+            L = (v & kHead) ? (v & kVal) : (sm.cells[t0] & kVal);
+        };
+        // R3: rank of every member among its cluster's members by sequence index = its place in the cluster's insertion
+        // history; its ideal cell goes to that place
         {
             int k = 0;
-            for (uint32_t b0 = b_lo; b0 < b_hi; b0++, k++) {
-                const uint32_t L = own_len[k];
-                if (!L) continue;
-                const uint32_t t0 = bucket_begin(b0);
-                auto at = [&](uint32_t i) { const uint32_t u = t0 + i; return u >= ne ? u - ne : u; };
-                if (L == 1) {
-                    sm.cells[t0] = sm.seq[t0];
-                    continue;
+            for (uint32_t t = tid; t < ne; t += nthreads, k++) {
+                uint32_t t0, L;
+                cluster_of(t, t0, L);
+                const uint32_t mine = sm.seq[t];
+                const uint32_t a = (static_cast<uint32_t>(sm.stash[mine]) - sm.stash[sm.seq[t0]]) & mask;
+                uint32_t r = 0;
+#pragma unroll 1   // lanes of a warp walk clusters of different lengths: a tight loop, not unrolled variants of it
+                for (uint32_t i = 0; i < L; i++) r += sm.seq[at(t0 + i)] < mine ? 1u : 0u;
+                l_r[k] = static_cast<uint16_t>(r);
+                atime[at(t0 + r)] = static_cast<uint16_t>(a);
+            }
+        }
+        __syncthreads();
+        mark(8);
+        // P: the empty cell every insertion filled = the first empty cell at or after its ideal cell (robin_hash.h:1226-1317
+        // probes on from there, whatever it swaps on the way). Serial per cluster, by the thread of its first element.
+        for (uint32_t t0 = tid; t0 < ne; t0 += nthreads) {
+            const uint32_t v = sm.cells[t0];
+            if (!(v & kHead)) continue;
+            const uint32_t L = v & kVal;
+            if (L <= 64) {
+                unsigned long long occupied = 0;
+#pragma unroll 1
+                for (uint32_t k = 0; k < L; k++) {
+                    const uint32_t u = at(t0 + k), a = atime[u];
+                    const uint32_t e = a + static_cast<uint32_t>(__ffsll(static_cast<long long>(~occupied >> a))) - 1u;
+                    occupied |= 1ull << e;
+                    etime[u] = static_cast<uint16_t>(e);
                 }
-                for (uint32_t i = 0; i < L; i++) sm.cells[at(i)] = kEmpty;
-                for (uint32_t m = 0; m < L; m++) {
-                    uint32_t carry = sm.seq[at(m)];
-                    uint32_t i = (static_cast<uint32_t>(sm.stash[carry]) - b0) & mask;   // ideal cell, inside the cluster by construction
-                    uint32_t dist = 0;
-                    while (i < L) {
-                        const uint32_t cur = sm.cells[at(i)];
-                        if (cur == kEmpty) {
-                            sm.cells[at(i)] = static_cast<uint16_t>(carry);
-                            break;
-                        }
-                        const uint32_t cur_dist = (i - ((static_cast<uint32_t>(sm.stash[cur]) - b0) & mask)) & mask;
-                        if (dist > cur_dist) {   // a strictly richer resident gives way and is carried on
-                            sm.cells[at(i)] = static_cast<uint16_t>(carry);
-                            carry = cur;
-                            dist = cur_dist;
-                        }
-                        i++;
-                        dist++;
-                    }
+            } else {   // a long cluster: occupancy of cell i in bit 15 of atime[t0 + i]
+#pragma unroll 1
+                for (uint32_t k = 0; k < L; k++) {
+                    const uint32_t u = at(t0 + k);
+                    uint32_t e = atime[u] & kVal;
+                    while (atime[at(t0 + e)] & kHead) e++;
+                    atime[at(t0 + e)] |= kHead;
+                    etime[u] = static_cast<uint16_t>(e);
                 }
             }
         }
         __syncthreads();
+        mark(9);
+        // W: every member follows its own group through the cluster's history. Before its own insertion it counts the
+        // earlier arrivals of its group (it is appended behind them); after it, a later arrival of the group makes the group
+        // longer, and an insertion (a2, e2) with a2 < a < e2 carries the group's first element to its end. The group's first
+        // cell is the number of members with a smaller ideal cell. The result goes to `stash` (dead since R3).
+        {
+            int k = 0;
+            for (uint32_t t = tid; t < ne; t += nthreads, k++) {
+                uint32_t t0, L;
+                cluster_of(t, t0, L);
+                const uint32_t r = l_r[k], a = atime[at(t0 + r)] & kVal;
+                uint32_t before = 0, idx = 0;
+#pragma unroll 1
+                for (uint32_t i = 0; i < r; i++) {
+                    const uint32_t a2 = atime[at(t0 + i)] & kVal;
+                    before += a2 < a ? 1u : 0u;
+                    idx += a2 == a ? 1u : 0u;
+                }
+                uint32_t size = idx + 1u;
+#pragma unroll 1
+                for (uint32_t i = r + 1u; i < L; i++) {
+                    const uint32_t u = at(t0 + i), a2 = atime[u] & kVal, e2 = etime[u];
+                    before += a2 < a ? 1u : 0u;
+                    if (a2 == a) size++;
+                    else if (a2 < a && a < e2) idx = idx ? idx - 1u : size - 1u;
+                }
+                sm.stash[at(t0 + before + idx)] = static_cast<uint16_t>(sm.seq[t]);
+            }
+        }
+        __syncthreads();
+        mark(10);
         // E7: the table's iteration order: cell order, the w wrapped cells first
         const bool last = hi == n;
         for (uint32_t t = tid; t < ne; t += nthreads) {
             uint32_t d = t + w;
             if (d >= ne) d -= ne;
-            const uint32_t s = sm.cells[t];
+            const uint32_t s = sm.stash[t];
             const uint32_t e = s < lo ? sm.prev[s] : s;
             if (last) out[d] = __ldg(ids + e);
             else sm.seq[d] = static_cast<uint16_t>(e);
@@ -301,6 +358,13 @@ __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const 
         if (!last) {
             for (uint32_t d = tid; d < ne; d += nthreads) sm.prev[d] = sm.seq[d];   // ne <= n / 2 whenever another epoch follows
             __syncthreads();
+        }
+        mark(13);
+        if (prof && threadIdx.x == 0) {
+            long long all = 0;
+            for (int k = 1; k <= 13; k++) all += prof[k];
+            prof[32 + j] = all - prof[31];
+            prof[31] = all;
         }
         lo = hi;
     }

@@ -183,16 +183,53 @@ def _xyz_of(pn):
     return out
 
 
-def test_per_scan_kernel_inserts_in_the_replayed_order(ctx, real_map, stream12):
-    """The fused per-scan kernel (csrc/lo_pipeline.cu) feeds keyframe_.addCloud(update) (lidar_odometry.cpp:42,70) in the
-    replayed order: after every scan the key frame holds the same points in the same per-voxel slots as the real container
-    pipeline, the pose is the same to the bit pattern of the tolerance, and the stats say the order was the exact one."""
+def _run_against_real_container(ctx, real_map, scans):
     od, oc = lo.LidarOdometry(ctx), real_map.odometry()
-    for k, s in enumerate(stream12[0]):
+    orders = []
+    for k, s in enumerate(scans):
         od.processCloud(s)
         oc.process(s)
         st = od.stats()
-        assert st.order_approximate == 0, k
+        orders.append(st.update_order)
         a, b = od.getKeyFrameCloudWithNormals(), oc.keyframe_pn()
         assert len(a) == len(b), k
         assert np.array_equal(sort_rows(a), sort_rows(b)), f"key frames differ after scan {k}"
+    return orders
+
+
+def test_per_scan_kernel_update_order(ctx, real_map, stream12):
+    """The fused per-scan kernel (csrc/lo_pipeline.cu) feeds keyframe_.addCloud(update) (lidar_odometry.cpp:42,70) in the
+    counting-sort order where that provably gives the reference's key frame, and in the replayed order otherwise: after every
+    scan the key frame holds the same points as the pipeline over the real container, and no scan reports an approximation."""
+    orders = _run_against_real_container(ctx, real_map, stream12[0])
+    assert all(o in (lo.LO_ORDER_SORTED, lo.LO_ORDER_REPLAYED) for o in orders), orders
+
+
+def test_per_scan_kernel_replay_forced():
+    """The same with the block replay forced on every scan (LO_B200_REPLAY_ALWAYS is read when the first scan is queued, so
+    this test owns a fresh library state only if it runs in its own process: the switch is latched per process)."""
+    import subprocess
+    import sys
+    import os
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, 'tests')\n"
+        "import lidar_odometry_demo_b200 as lo, oracle\n"
+        "from lidar_odometry_demo_b200 import synthetic as S\n"
+        "from util import sort_rows\n"
+        "orc = oracle.load('reference' if oracle.available('reference') else 'port')\n"
+        "scans, _, _ = S.vlp16_stream(8)\n"
+        "ctx = lo.Context(0)\n"
+        "od, oc = lo.LidarOdometry(ctx), orc.odometry()\n"
+        "for k, s in enumerate(scans):\n"
+        "    od.processCloud(s); oc.process(s)\n"
+        "    assert od.stats().update_order == lo.LO_ORDER_REPLAYED, (k, od.stats().update_order)\n"
+        "    a, b = od.getKeyFrameCloudWithNormals(), oc.keyframe_pn()\n"
+        "    assert len(a) == len(b) and np.array_equal(sort_rows(a), sort_rows(b)), k\n"
+        "    d = np.abs(od.getCurrentPose().astype(np.float64) - oc.pose().astype(np.float64)).max()\n"
+        "    assert d < 1e-5, (k, d)\n"
+        "print('replayed', len(scans))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, LO_B200_REPLAY_ALWAYS="1"), cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "replayed 8" in r.stdout
