@@ -445,13 +445,16 @@ def run_ours(args):
     if steady is not None:
         od_chk = lo.LidarOdometry(ctx)
         ss_worst = [0.0, 0.0]
+        orders = [0, 0, 0]   # lo_scan_stats.update_order: counting sort sufficed / exact replay / approximate
 
         def check(k, pose_cpu):
             od_chk.processCloud(steady[k])
             a, b = pose_err(od_chk.getCurrentPose(), pose_cpu)
             ss_worst[0], ss_worst[1] = max(ss_worst[0], a), max(ss_worst[1], b)
+            orders[od_chk.stats().update_order] += 1
         cpu_ss = cpu_steady_state(K, steady, check)
-        parity["steady_stream"] = {"max_pose_err_m": ss_worst[0], "max_pose_err_rad": ss_worst[1], "scans_checked": len(steady)}
+        parity["steady_stream"] = {"max_pose_err_m": ss_worst[0], "max_pose_err_rad": ss_worst[1], "scans_checked": len(steady),
+                                   "update_order": {"counting_sort_exact": orders[0], "replayed": orders[1], "approximate": orders[2]}}
 
     n = world
     line = {

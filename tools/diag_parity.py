@@ -18,15 +18,17 @@ orc = oracle.load(kind)
 ctx = lo.Context(0)
 od, oc = lo.LidarOdometry(ctx), orc.odometry()
 shown = 0
+orders = [0, 0, 0]
 for k, s in enumerate(scans):
     od.processCloud(s)
     c, extra = oc.process(s)
     a, b = od.getCurrentPose().astype(np.float64), oc.pose().astype(np.float64)
     dt = float(np.linalg.norm(a[:3] - b[:3]))
     st = od.stats()
+    orders[st.update_order] += 1
     bad = dt > 1e-7 or (st.n_planar, st.n_update, st.n_query) != (c[1], c[2], c[3])
     if bad and shown < 12:
         shown += 1
         print(f"scan {k}: |dt| {dt:.3e}; GPU P/U/M {st.n_planar}/{st.n_update}/{st.n_query} outer {st.outer_iterations} unstable {st.unstable} kf {st.keyframe_voxels}; "
               f"oracle {c[1]}/{c[2]}/{c[3]} extra {extra}; gpu {a[:3]} oracle {b[:3]}", flush=True)
-print("done; oracle", kind)
+print("done; oracle", kind, "; update order: counting sort / replayed / approximate =", orders)

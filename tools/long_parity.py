@@ -24,6 +24,7 @@ ctx = lo.Context(0)   # after the stream was generated: the generator forks work
 od, oc = lo.LidarOdometry(ctx), orc.odometry()
 worst_t = worst_r = 0.0
 count_mismatch = unstable = 0
+orders = [0, 0, 0]
 t_gpu = t_cpu = 0.0
 for k, s in enumerate(scans):
     t1 = time.perf_counter()
@@ -42,11 +43,13 @@ for k, s in enumerate(scans):
     if (st.n_planar, st.n_update, st.n_query) != (c[1], c[2], c[3]):
         count_mismatch += 1
     unstable += int(st.unstable)
+    orders[st.update_order] += 1
     if k % 50 == 49 or k == n - 1:
         print(f"scan {k:4d}: |dt| {dt:.2e} m |dr| {dr:.2e} rad (worst so far {worst_t:.2e} / {worst_r:.2e}); P/U/M {st.n_planar}/{st.n_update}/"
               f"{st.n_query} vs {c[1]}/{c[2]}/{c[3]}; key-frame voxels {st.keyframe_voxels}; x = {a[0]:.3f} m", flush=True)
 print(json.dumps({"workload": f"config 2, {n} scans", "oracle": kind, "max_pose_err_m": worst_t, "max_pose_err_rad": worst_r,
-                  "scans_with_count_mismatch": count_mismatch, "unstable_scans": unstable, "final_pose_gpu": [float(v) for v in a],
+                  "scans_with_count_mismatch": count_mismatch,
+                  "update_order": {"counting_sort_exact": orders[0], "replayed": orders[1], "approximate": orders[2]}, "unstable_scans": unstable, "final_pose_gpu": [float(v) for v in a],
                   "final_pose_oracle": [float(v) for v in b], "gpu_wall_s": t_gpu, "cpu_wall_s": t_cpu, "speedup_wall_clock_blocking_pageable": t_cpu / t_gpu,
                   "keyframe": od.keyframeInfo().as_dict(),
                   "tolerance": "1e-4 m / 1e-4 rad per scan (north_star)"}))
