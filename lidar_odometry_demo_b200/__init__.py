@@ -14,7 +14,7 @@ import numpy as np
 from .synthetic import PN, XYZ, XYZIRT  # noqa: F401  (wire dtypes)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblo_b200.so")
+LIB_PATH = os.environ.get("LO_B200_LIB") or os.path.join(_HERE, "liblo_b200.so")   # the override: A/B runs of another build
 
 QUEUE_DEPTH = 8   # LO_ODOMETRY_QUEUE_DEPTH
 LO_OK, LO_E_CUDA, LO_E_ARG, LO_E_CAPACITY, LO_E_RANGE, LO_E_IO, LO_E_BUSY = 0, -1, -2, -3, -4, -5, -6

@@ -46,6 +46,7 @@ __global__ void find_pairs_kernel(GridView g, const PointXYZ* __restrict__ queri
 // query, lane j keeps the correspondence of query j, then all 32 lanes evaluate their residual/Jacobian in
 // parallel and the warp reduces the 28 sums by shuffles into its shared-memory row.
 constexpr int kNnThreads = 256;
+constexpr int kNnBlocksPerSm = 4;   // resident blocks per SM of the tile kernel (64 registers)
 __global__ void __launch_bounds__(kNnThreads, 4) nn_residual_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
                                                                   QueryTransform tf, EvalPoint ep, float max_d2,
                                                                   double* __restrict__ partials) {
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(kNnThreads, 4) nn_residual_kernel(GridView g, 
 // The same contract with the tile search of lo_tile_search.cuh (own voxel first, neighbours pruned exactly by the best
 // distance so far): a warp takes 32 consecutive queries, lane l owns query l from the transform to the residual.
 // rows[29] / rows[30] count the stored points / occupied voxels actually visited.
-__global__ void __launch_bounds__(kNnThreads, 4) nn_residual_tile_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
+__global__ void __launch_bounds__(kNnThreads, kNnBlocksPerSm) nn_residual_tile_kernel(GridView g, const PointXYZ* __restrict__ queries, uint32_t m,
                                                                        QueryTransform tf, EvalPoint ep, float max_d2,
                                                                        double* __restrict__ partials) {
     __shared__ double rows[(kNnThreads / 32) * kRow];
@@ -300,7 +301,7 @@ extern "C" int lo_nn_residual_dev(lo_grid* g, const void* d_xyz16, size_t m, con
     const EvalPoint ep = make_eval_point(x7d);
     const uint32_t tiles = static_cast<uint32_t>((m + 31) / 32);
     // at most one resident wave (4 blocks of 8 warps per SM); each warp takes an equal share of the queries
-    const int max_blocks = ctx->sm_count * 4;
+    const int max_blocks = ctx->sm_count * kNnBlocksPerSm;
     const int blocks = std::max(1, std::min<int>(max_blocks, static_cast<int>((tiles + kNnThreads / 32 - 1) / (kNnThreads / 32))));
     LO_TRY(ctx->tmp_c.ensure(static_cast<size_t>(blocks) * 32 * sizeof(double)));
     lo_normal_eq* d_out = reinterpret_cast<lo_normal_eq*>(ctx->small.as<char>() + 1024);
@@ -366,7 +367,7 @@ extern "C" int lo_nn_residual_static_dev(lo_grid* g, const void* d_xyz16, size_t
     const QueryTransform tf = make_query_transform(pose_from7(pose7));
     const EvalPoint ep = make_eval_point(x7d);
     const uint32_t tiles = static_cast<uint32_t>((m + 31) / 32);
-    const int max_blocks = std::min(ctx->sm_count * 4, kStaticNnMaxBlocks);   // the same launch shape as lo_nn_residual_dev on any GPU of <= 256 SMs
+    const int max_blocks = std::min(ctx->sm_count * kNnBlocksPerSm, kStaticNnMaxBlocks);   // the same launch shape as lo_nn_residual_dev on any GPU of <= 256 SMs
     const int blocks = std::max(1, std::min<int>(max_blocks, static_cast<int>((tiles + kNnThreads / 32 - 1) / (kNnThreads / 32))));
     if (g->width > kTileMaxWidth)
         nn_residual_kernel<<<blocks, kNnThreads, 0, ctx->stream>>>(g->view(), static_cast<const PointXYZ*>(d_xyz16), static_cast<uint32_t>(m),

@@ -363,24 +363,32 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
 
 // Upload of a scan that sits in ordinary (pageable) host memory, as processCloud's caller has it: the scan is copied
 // through the handle's pinned staging buffer in pieces, each piece's DMA running under the memcpy of the next one.
-// (cudaMemcpyAsync on pageable memory stages too, but serially and with a synchronising tail.)
+// (cudaMemcpyAsync on pageable memory stages too, but serially and with a synchronising tail.) The DMA runs on the copy
+// stream: the previous process call returned when its pose was final, so its kernel may still be in its tail
+// (radiusCleanup + key-frame insert, a fifth of the kernel) — which reads the filtered cloud, never the raw scan (last read
+// by the deskew phase) — and the upload goes on underneath it instead of queueing behind it.
 static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
     lo_ctx* ctx = h->ctx;
     const size_t bytes = n * sizeof(PointXYZIRT);
     LO_TRY(h->scan.ensure(std::max<size_t>(bytes, sizeof(PointXYZIRT))));
     if (!n) return LO_OK;
-    static const int mode = [] { const char* e = getenv("LO_B200_UPLOAD"); return e ? atoi(e) : 0; }();   // developer switch: 1 = plain cudaMemcpyAsync
-    if (mode == 1) {
+    static const int mode = [] { const char* e = getenv("LO_B200_UPLOAD"); return e ? atoi(e) : 0; }();   // developer switch: 1 = plain
+    if (mode == 1) {                                                                                    // cudaMemcpyAsync, 2 = main stream
         LO_CUDA(cudaMemcpyAsync(h->scan.p, xyzirt32, bytes, cudaMemcpyHostToDevice, ctx->stream));
         return LO_OK;
     }
+    cudaStream_t copy = mode == 2 ? ctx->stream : h->copy_stream;
     // the previous scan's DMA out of the staging buffer ended before that call returned (its kernel was waited for)
     LO_TRY(h->stage.ensure(bytes));
     constexpr size_t kPiece = 256 * 1024;
     for (size_t off = 0; off < bytes; off += kPiece) {
         const size_t len = std::min(kPiece, bytes - off);
         std::memcpy(h->stage.as<char>() + off, static_cast<const char*>(xyzirt32) + off, len);
-        LO_CUDA(cudaMemcpyAsync(h->scan.as<char>() + off, h->stage.as<char>() + off, len, cudaMemcpyHostToDevice, ctx->stream));
+        LO_CUDA(cudaMemcpyAsync(h->scan.as<char>() + off, h->stage.as<char>() + off, len, cudaMemcpyHostToDevice, copy));
+    }
+    if (copy != ctx->stream) {
+        LO_CUDA(cudaEventRecord(h->copy_done, copy));
+        LO_CUDA(cudaStreamWaitEvent(ctx->stream, h->copy_done, 0));
     }
     return LO_OK;
 }

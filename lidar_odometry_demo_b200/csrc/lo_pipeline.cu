@@ -869,20 +869,25 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel(ScanArgs p) { sca
 __global__ void __launch_bounds__(kPipeThreads, 1) scan_kernel_large(ScanArgs p) { scan_body<true>(p); }
 constexpr uint32_t kSmallScanPoints = 32768;   // scans up to this size (a VLP16 revolution is ~30 k) run scan_kernel
 
-// Queued behind every scan_kernel; returns at once unless that kernel left the insert to it (a tie group with two members
-// in one key-frame voxel: about one VLP16 scan in 40). One block: the exact tsl::robin_map iteration order of the update
-// set (lo_robin_block.cuh), then keyframe_.addCloud(update) (lidar_odometry.cpp:42,70) in that order — the three passes of
-// the insert separated by block barriers — and the second half of the read-back block.
+// Queued behind every scan_kernel (same cooperative grid); returns at once unless that kernel left the insert to it (a tie
+// group with two members in one key-frame voxel: about one VLP16 scan in 25). Block 0 computes the exact tsl::robin_map
+// iteration order of the update set in its shared memory (lo_robin_block.cuh), then all blocks run
+// keyframe_.addCloud(update) (lidar_odometry.cpp:42,70) in that order and block 0 writes the second half of the read-back.
 __global__ void __launch_bounds__(kPipeThreads, 1) scan_replay_kernel(ScanArgs p) {
     const uint32_t deferred = p.b.robin_flags[2];
     if (!deferred) return;
+    cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     OdomDev* s = p.s;
     const uint32_t nu = min(p.n, s->n_update);
-    const bool exact = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);   // refused: usorted is untouched
+    if (blockIdx.x == 0) {
+        const bool ok = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);   // refused: usorted is untouched
+        if (threadIdx.x == 0) p.b.robin_flags[1] = ok ? 0u : 1u;
+    }
     __shared__ Pose pose_s;
     if (threadIdx.x == 0) pose_s = s->current;
-    __syncthreads();
+    grid.sync();
+    const bool exact = __ldcg(p.b.robin_flags + 1) == 0u;
     const Pose* insert_pose = deferred == 2u ? nullptr : &pose_s;
     uint32_t gather_shift = 0;
     if (!exact && nu) {   // a run of more than 2 048 occupied buckets: the counting-sort order and its rotation stand
@@ -891,17 +896,17 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_replay_kernel(ScanArgs p
         gather_shift = (nu - rot) % nu;
     }
     const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
     if (exact) {   // the first pass again, in the new order: it finds the voxels scan_kernel created
-        for (uint32_t i = threadIdx.x; i < nu; i += blockDim.x)
-            grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
-        __syncthreads();
+        for (uint32_t i = tid; i < nu; i += nthreads) grid_locate_item(i, src, insert_pose, p.kf, p.kf_counters, p.kf_free_list, p.b.kf_slot);
+        grid.sync();
     }
-    for (uint32_t i = threadIdx.x; i < nu; i += blockDim.x) grid_chain_item(i, p.ticket_base, p.kf, p.b.kf_slot, p.b.kf_base);
-    __syncthreads();
-    for (uint32_t i = threadIdx.x; i < nu; i += blockDim.x)
+    for (uint32_t i = tid; i < nu; i += nthreads) grid_chain_item(i, p.ticket_base, p.kf, p.b.kf_slot, p.b.kf_base);
+    grid.sync();
+    for (uint32_t i = tid; i < nu; i += nthreads)
         grid_write_item(i, src, p.ticket_base, insert_pose, p.kf, p.kf_counters, p.b.kf_slot, p.b.kf_base);
-    __syncthreads();
-    if (threadIdx.x == 0) scan_publish_tail(p, exact ? kOrderReplayed : kOrderApproximate);
+    grid.sync();
+    if (tid == 0) scan_publish_tail(p, exact ? kOrderReplayed : kOrderApproximate);
 }
 
 }  // namespace lo
@@ -933,7 +938,9 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
         LO_CUDA(cudaFuncSetAttribute(scan_replay_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
         LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&large_per_sm, scan_kernel_large, kPipeThreads, kAlignTileScratchBytes));
         LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, scan_kernel, kPipeThreads, 0));
-        blocks_per_sm = std::min(blocks_per_sm, large_per_sm);
+        int replay_per_sm = 0;
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&replay_per_sm, scan_replay_kernel, kPipeThreads, kRobinBlockSmemBytes));
+        blocks_per_sm = std::min(std::min(blocks_per_sm, large_per_sm), replay_per_sm);
         if (blocks_per_sm < 1) {
             set_error("the per-scan kernel does not fit on an SM");
             return LO_E_CUDA;
@@ -990,8 +997,13 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     h->scan_seq = p.seq;
     ctx->launches++;
     if (n <= kSmallScanPoints) {   // returns at once unless scan_kernel left the insert to it (see there)
-        scan_replay_kernel<<<1, kPipeThreads, kRobinBlockSmemBytes, ctx->stream>>>(p);
-        LO_LAUNCHED(ctx);
+        const cudaError_t e2 = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_replay_kernel), dim3(blocks), dim3(kPipeThreads), kargs,
+                                                           kRobinBlockSmemBytes, ctx->stream);
+        if (e2 != cudaSuccess) {
+            set_error("launching the replay kernel (%d cooperative blocks of %d threads) failed: %s", blocks, kPipeThreads, cudaGetErrorString(e2));
+            return LO_E_CUDA;
+        }
+        ctx->launches++;
     }
     return LO_OK;
 }
