@@ -468,6 +468,7 @@ def run_ours(args):
                 "e2e": "lo_odometry_process (blocking, processCloud-shaped) on pageable host scans + lo_odometry_pose; time.perf_counter around "
                        "every call, L2 flushed and device drained between calls (not timed); K / sum of the call times"},
         "e2e": {"value": n * K / e2e_time, "unit": UNIT, "h2d_bytes_per_step": int(np.mean(sizes[W:]) * 32), "d2h_bytes_per_step": 64,
+                "host_threads": od.hostThreads(),   # the caller + the helper threads of the staging copy (pageable -> pinned)
                 "ms_per_call_p50": 1e3 * float(np.median(e2e_dt)), "ms_per_call_max": 1e3 * float(e2e_dt.max()),
                 "back_to_back": {"value": K / b2b_loop, "note": "rank 0: the same K blocking calls in one loop without L2 flushes, one wall-clock "
                                                                  "interval around the loop"},

@@ -334,6 +334,10 @@ typedef struct lo_keyframe_info {
     uint64_t table_rebuilds, payload_growths;   /* stream-ordered re-allocations since creation (0 in a sized run) */
 } lo_keyframe_info;
 int lo_odometry_keyframe_info(lo_odometry* h, lo_keyframe_info* out);
+/* Host threads lo_odometry_process uses for a scan in pageable memory: the caller plus the helpers of the staging copy into
+ * pinned memory (csrc/lo_copy_pool.h; up to 3, env LO_B200_COPY_THREADS overrides, 0 = none). The helpers spin for 1 ms after
+ * a copy and sleep otherwise. No counterpart in the reference (its processCloud takes the cloud where it lies). */
+int lo_odometry_host_threads(const lo_odometry* h);
 int lo_odometry_stats(lo_odometry* h, lo_scan_stats* out);
 /* getKeyFrameCloud (full=0, sparse) / getFullKeyFrameCloud (full=1): xyz16 */
 int lo_odometry_keyframe(lo_odometry* h, int full, float* xyz16_out, size_t cap, size_t* n);

@@ -118,6 +118,7 @@ SIGNATURES = {
     "lo_odometry_submit": (_i, [_vp, _vp, _sz]), "lo_odometry_submit_dev": (_i, [_vp, _vp, _sz]), "lo_odometry_wait": (_i, [_vp]),
     "lo_odometry_process_planar": (_i, [_vp, _vp, _sz]), "lo_odometry_pose": (_i, [_vp, _vp]),
     "lo_odometry_keyframe_info": (_i, [_vp, _vp]),
+    "lo_odometry_host_threads": (_i, [_vp]),
     "lo_odometry_stats": (_i, [_vp, _vp]),
     "lo_odometry_keyframe": (_i, [_vp, _i, _vp, _sz, C.POINTER(_sz)]),
     "lo_odometry_keyframe_pn": (_i, [_vp, _vp, _sz, C.POINTER(_sz)]),
@@ -559,6 +560,10 @@ class LidarOdometry:
         s = ScanStats()
         _check(self.lib.lo_odometry_stats(self.h, C.byref(s)))
         return s
+
+    def hostThreads(self):
+        """Host threads the blocking processCloud uses for a pageable scan (caller + staging-copy helpers)."""
+        return int(self.lib.lo_odometry_host_threads(self.h))
 
     def keyframeInfo(self):
         k = KeyframeInfo()

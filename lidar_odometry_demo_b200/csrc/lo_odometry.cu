@@ -6,6 +6,9 @@
 #include <atomic>
 #include <cstring>
 
+#include <chrono>
+
+#include "lo_copy_pool.h"
 #include "lo_odometry.cuh"
 
 namespace lo {
@@ -318,6 +321,7 @@ extern "C" void lo_odometry_destroy(lo_odometry* h) {
         cudaStreamDestroy(h->copy_stream);
     }
     if (h->copy_done) cudaEventDestroy(h->copy_done);
+    delete h->copy_pool;
     for (DevBuf* b : {&h->scan, &h->scan_next, &h->deskewed, &h->filtered, &h->update, &h->query}) b->release();
     h->stage.release();
     for (DevBuf& b : h->scan_q) b.release();
@@ -367,6 +371,16 @@ extern "C" int lo_odometry_process_dev(lo_odometry* h, const void* d_xyzirt32, s
 // stream: the previous process call returned when its pose was final, so its kernel may still be in its tail
 // (radiusCleanup + key-frame insert, a fifth of the kernel) — which reads the filtered cloud, never the raw scan (last read
 // by the deskew phase) — and the upload goes on underneath it instead of queueing behind it.
+// helper threads of the staging copy: LO_B200_COPY_THREADS, else up to 3, leaving every GPU of the box (one process per GPU
+// is the normal deployment) half of its share of the cores
+static int copy_helpers() {
+    if (const char* e = getenv("LO_B200_COPY_THREADS")) return std::max(0, std::min(15, atoi(e)));
+    int gpus = 1;
+    if (cudaGetDeviceCount(&gpus) != cudaSuccess || gpus < 1) gpus = 1;
+    const int cores = static_cast<int>(std::thread::hardware_concurrency());
+    return std::max(0, std::min(3, cores / (2 * gpus) - 1));
+}
+
 static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
     lo_ctx* ctx = h->ctx;
     const size_t bytes = n * sizeof(PointXYZIRT);
@@ -380,10 +394,11 @@ static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
     cudaStream_t copy = mode == 2 ? ctx->stream : h->copy_stream;
     // the previous scan's DMA out of the staging buffer ended before that call returned (its kernel was waited for)
     LO_TRY(h->stage.ensure(bytes));
+    if (!h->copy_pool) h->copy_pool = new CopyPool(copy_helpers());
     constexpr size_t kPiece = 256 * 1024;
     for (size_t off = 0; off < bytes; off += kPiece) {
         const size_t len = std::min(kPiece, bytes - off);
-        std::memcpy(h->stage.as<char>() + off, static_cast<const char*>(xyzirt32) + off, len);
+        h->copy_pool->copy(h->stage.as<char>() + off, static_cast<const char*>(xyzirt32) + off, len);
         LO_CUDA(cudaMemcpyAsync(h->scan.as<char>() + off, h->stage.as<char>() + off, len, cudaMemcpyHostToDevice, copy));
     }
     if (copy != ctx->stream) {
@@ -391,6 +406,11 @@ static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
         LO_CUDA(cudaStreamWaitEvent(ctx->stream, h->copy_done, 0));
     }
     return LO_OK;
+}
+
+extern "C" int lo_odometry_host_threads(const lo_odometry* h) {
+    if (!h) return 0;
+    return 1 + (h->copy_pool ? h->copy_pool->helpers() : copy_helpers());
 }
 
 extern "C" int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t n) {
@@ -401,8 +421,33 @@ extern "C" int lo_odometry_process(lo_odometry* h, const void* xyzirt32, size_t 
         set_error("scans submitted with lo_odometry_submit are still in flight: call lo_odometry_wait first");
         return LO_E_BUSY;
     }
+    static const bool timing = getenv("LO_B200_TIMING") != nullptr;   // developer switch: host microseconds per part of the call, on stderr
+    if (!timing) {
+        LO_TRY(upload_scan(h, xyzirt32, n));
+        return lo_odometry_process_dev(h, h->scan.p, n);
+    }
+    static double t_upload = 0, t_submit = 0, t_wait = 0;
+    static long calls = 0;
+    auto now = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
     LO_TRY(upload_scan(h, xyzirt32, n));
-    return lo_odometry_process_dev(h, h->scan.p, n);
+    const double t1 = now();
+    int st = LO_OK;
+    if (n <= fused_max_points()) {
+        st = submit_fused(h, h->scan.as<PointXYZIRT>(), static_cast<uint32_t>(n));
+        const double t2 = now();
+        if (st == LO_OK) st = wait_oldest(h);
+        const double t3 = now();
+        t_upload += t1 - t0; t_submit += t2 - t1; t_wait += t3 - t2;
+        if (++calls % 100 == 0) {
+            fprintf(stderr, "lo_odometry_process: per call over the last 100: upload (staging memcpy + DMA enqueue) %.1f us, submit %.1f us, wait for the pose %.1f us\n",
+                    t_upload / 100, t_submit / 100, t_wait / 100);
+            t_upload = t_submit = t_wait = 0;
+        }
+    } else {
+        st = lo_odometry_process_dev(h, h->scan.p, n);
+    }
+    return st;
 }
 
 extern "C" int lo_odometry_process_next(lo_odometry* h, const void* xyzirt32, size_t n, const void* next_xyzirt32, size_t next_n) {

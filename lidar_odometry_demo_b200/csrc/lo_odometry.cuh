@@ -70,6 +70,8 @@ namespace lo {
 constexpr uint32_t kQueueDepth = LO_ODOMETRY_QUEUE_DEPTH;   // scans in flight through lo_odometry_submit*: rings of result blocks and staging buffers
 }
 
+namespace lo { class CopyPool; }
+
 struct lo_odometry {
     lo_ctx* ctx = nullptr;
     lo_params params;
@@ -88,6 +90,7 @@ struct lo_odometry {
     uint64_t queued_rebuilds[lo::kQueueDepth] = {};   // per slot: key-frame table rebuilds before the scan was queued
     size_t pending_points = 0;               // points of the scans whose key-frame counters are not on the host yet
     lo::PinnedBuf stage;                     // lo_odometry_process: pinned staging of a pageable host scan
+    lo::CopyPool* copy_pool = nullptr;       // ... and the helper threads of that copy (created with the first such scan)
     lo::DevBuf scan_q[lo::kQueueDepth];      // lo_odometry_submit: device copies of the queued host scans
     cudaEvent_t scan_q_done[lo::kQueueDepth] = {};
     lo::DevBuf scan, deskewed, filtered, update, query;
