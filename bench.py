@@ -227,7 +227,8 @@ def run_ours(args):
     W, K = args.warmup, args.steps
     # streams first: the generator forks worker processes, which must happen before CUDA is initialised here
     scans = make_stream(W + K, rank, gen_workers(world))
-    steady = make_stream(steady_len(K), 0, gen_workers(world)) if rank == 0 and want_steady() else None
+    # the steady-state leg belongs to the N = 1 record (its arms synchronise with barrier(): rank 0 alone must not enter them)
+    steady = make_stream(steady_len(K), 0, gen_workers(world)) if world == 1 and want_steady() else None
 
     import torch
     import lidar_odometry_demo_b200 as lo
