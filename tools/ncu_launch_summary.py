@@ -21,9 +21,11 @@ grand = sum(total.values()) or 1.0
 with open(out, "w") as f:
     f.write("# ncu --metrics gpu__time_duration.sum --clock-control none  python bench.py --steps 5 --warmup 3\n"
             "# per-launch times under ncu are cold-cache and serialised; what must agree with bench.py is the SHARE of the step.\n"
-            "# One timed step = one lo::scan_kernel launch (gpu_launches = steps + table rebuilds). The other kernels belong to\n"
-            "# bench.py's untimed sections: L2 flush fills (at::FillFunctor), the roofline section (align_kernel, nn_residual*_kernel,\n"
-            "# grid_* inserts of the 12 M-point map), odometry construction.\n")
+            "# One timed step = one lo::scan_kernel launch + the lo::scan_replay_kernel queued behind it, which returns at once unless\n"
+            "# the scan needs the exact robin_map replay (about 1 scan in 25; those launches take ~0.4 ms and make up its share here).\n"
+            "# gpu_launches = 2 x steps (+ table rebuilds: none). The other kernels belong to bench.py's untimed sections: L2 flush\n"
+            "# fills (at::FillFunctor), the roofline section (align_kernel, nn_residual*_kernel, grid_* inserts of the 12 M-point map),\n"
+            "# odometry construction.\n")
     f.write(f"{'launches':>8s} {'total_ns':>14s} {'share':>7s}  kernel\n")
     for name in sorted(total, key=total.get, reverse=True):
         f.write(f"{count[name]:8d} {total[name]:14.1f} {100 * total[name] / grand:6.1f}%  {name}\n")
