@@ -51,6 +51,7 @@ if __name__ == "__main__":
     d_scans = [torch.from_numpy(s.view(np.uint8).reshape(-1)).cuda() for s in scans]
     torch.cuda.synchronize()
     worst, ms, t_cpu = (0.0, 0.0), [], 0.0
+    orders = [0, 0, 0]
     for k, sc in enumerate(scans):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -59,6 +60,7 @@ if __name__ == "__main__":
         torch.cuda.synchronize()
         ms.append(e0.elapsed_time(e1))
         st = od.stats()
+        orders[st.update_order] += 1
         if oc is not None:
             t1 = time.perf_counter()
             counts, _ = oc.process(sc)
@@ -71,6 +73,7 @@ if __name__ == "__main__":
             assert (st.n_planar, st.n_update, st.n_query) == (counts[1], counts[2], counts[3]), (k, st.n_planar, st.n_update, st.n_query, counts)
         print(k, f"{ms[-1]:.3f} ms", st.n_planar, st.n_update, st.n_query, st.outer_iterations, st.keyframe_voxels, file=sys.stderr)
     print(json.dumps({"workload": "config 3: 128 x 2048 returns per scan, voxels 0.1 / 0.05 / 0.05", "scans": n, "points_per_scan": len(scans[0]),
+                      "update_order": {"counting_sort_exact": orders[0], "replayed": orders[1], "approximate": orders[2]},
                       "ms_per_scan_after_first": float(np.mean(ms[1:])), "scans_per_s": 1e3 / float(np.mean(ms[1:])),
                       "cpu_oracle_scans_per_s": (n / t_cpu) if oc is not None else None,
                       "max_pose_err_m": worst[0], "max_pose_err_rad": worst[1], "kernel_launches": int(ctx.kernel_launches),
