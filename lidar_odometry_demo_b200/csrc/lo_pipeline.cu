@@ -434,7 +434,7 @@ __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map a
 // do_hist: the update winners get their ideal robin_map bucket and are histogrammed (the counting-sort order, used where the
 // exact block-local replay does not apply); do_count: the winners of both down-samplers are counted per block for the
 // ordered compactions of P8 (queries for align; update winners in arrival order for the replay)
-__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match, bool do_hist, bool do_count) {
+__device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match, bool do_hist, bool do_count, bool count_update = false) {
     uint32_t before, total;
     block_prefix(b.block_counts, before, total);   // total = n_planar
     const uint32_t buckets = robin_bucket_count(s->n_update), bin_shift = robin_bin_shift(buckets);
@@ -445,9 +445,12 @@ __device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match
         const uint32_t i = base + threadIdx.x;
         bool wm = false, wu = false;
         if (i < end) {
-            const uint32_t su = b.slot_u[i];
-            wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+            if (do_hist || count_update) {
+                const uint32_t su = b.slot_u[i];
+                wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+            }
             if (do_hist) {
+                const uint32_t su = b.slot_u[i];
                 uint32_t bucket = kNoBucket;
                 if (wu) {
                     long long ix, iy, iz;
@@ -463,15 +466,11 @@ __device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match
                 wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
             }
         }
-        if (do_count) {
-            cm += __syncthreads_count(wm);
-            cu += __syncthreads_count(wu);
-        }
+        if (do_count) cm += __syncthreads_count(wm);
+        if (count_update) cu += __syncthreads_count(wu);
     }
-    if (threadIdx.x == 0 && do_count) {
-        b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
-        b.block_counts[1 * kMaxPipeBlocks + blockIdx.x] = cu;
-    }
+    if (threadIdx.x == 0 && do_count) b.block_counts[2 * kMaxPipeBlocks + blockIdx.x] = cm;
+    if (threadIdx.x == 0 && count_update) b.block_counts[1 * kMaxPipeBlocks + blockIdx.x] = cu;
 }
 
 // exclusive prefix of v over the block's threads, and the block total
@@ -506,12 +505,13 @@ __device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
 // coarse bins, so every bin is scanned here by one block on its own (start of the bin = sum of the coarse counts before
 // it); P9 places the winners and orders every tie group by arrival; the insert reads them through the wrap rotation.
 __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
-                                  PointXYZ* __restrict__ query, int with_match, bool do_u, bool do_m) {
-    uint32_t before, total, bm, nm, bu, nu;
-    if (do_m) {   // ordered compactions: the query cloud (if there is a key frame to match) and the update winners with their hashes
+                                  PointXYZ* __restrict__ query, int with_match, bool do_u, bool do_m, bool arrival_update = false) {
+    uint32_t before, total, bm = 0, nm = 0, bu = 0, nu = 0;
+    if (do_m || arrival_update) {   // ordered compactions: the query cloud (if there is a key frame to match); the update winners with
+                                    // their hashes in arrival order (the reference map's insertion sequence, for the replay)
         block_prefix(b.block_counts, before, total);
-        block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
-        block_prefix(b.block_counts + 1 * kMaxPipeBlocks, bu, nu);
+        if (do_m) block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
+        if (arrival_update) block_prefix(b.block_counts + 1 * kMaxPipeBlocks, bu, nu);
         uint32_t begin, end;
         chunk_range(total, begin, end);
         for (uint32_t base = begin; base < end; base += blockDim.x) {
@@ -519,16 +519,18 @@ __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNorma
             bool wm = false, wu = false;
             uint32_t su = 0xFFFFFFFFu;
             if (i < end) {
-                su = b.slot_u[i];
-                wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
-                if (with_match) {
+                if (arrival_update) {
+                    su = b.slot_u[i];
+                    wu = su != 0xFFFFFFFFu && b.ds_u[su].ticket == i;
+                }
+                if (with_match && do_m) {
                     const uint32_t sm = b.slot_m[i];
                     wm = sm != 0xFFFFFFFFu && b.ds_m[sm].ticket == i;
                 }
             }
-            uint32_t tm, tu;
-            const uint32_t rm = block_rank(wm, tm);
-            const uint32_t ru = block_rank(wu, tu);
+            uint32_t tm = 0, tu = 0, rm = 0, ru = 0;
+            if (do_m) rm = block_rank(wm, tm);
+            if (arrival_update) ru = block_rank(wu, tu);
             if (wm) {
                 const float4 p = *reinterpret_cast<const float4*>(filtered + i);
                 reinterpret_cast<float4*>(query)[bm + rm] = make_float4(p.x, p.y, p.z, 1.f);
@@ -703,14 +705,15 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     phase_scatter(s, p.b, p.filtered, p.vs_u, p.vs_m, with_match, range_err);
     grid.sync();
     LO_SCAN_TRACE(106);
-    // winners of the two down-samplers, in arrival order: the query set align needs (none on the bootstrap scan), and the
-    // update set with its hashes = the reference map's insertion sequence, for the robin_map order below
-    phase_select(s, p.b, with_match, false, true);
-    grid.sync();
-    LO_SCAN_TRACE(107);
-    phase_emit(s, p.b, p.filtered, p.query, with_match, false, true);
-    grid.sync();
-    LO_SCAN_TRACE(108);
+    // the query set align needs: winners of the matching down-sampler, in arrival order (the bootstrap scan has none)
+    if (with_match) {
+        phase_select(s, p.b, with_match, false, true);
+        grid.sync();
+        LO_SCAN_TRACE(107);
+        phase_emit(s, p.b, p.filtered, p.query, with_match, false, true);
+        grid.sync();
+        LO_SCAN_TRACE(108);
+    }
     __shared__ float next_s[7];
     __shared__ Pose current_s;
     __shared__ uint32_t unstable_s;
@@ -880,6 +883,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_replay_kernel(ScanArgs p
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     OdomDev* s = p.s;
     const uint32_t nu = min(p.n, s->n_update);
+    // the update winners with their hashes in arrival order = the reference map's insertion sequence
+    phase_select(s, p.b, 0, false, false, true);
+    grid.sync();
+    phase_emit(s, p.b, p.filtered, p.query, 0, false, false, true);
+    grid.sync();
     if (blockIdx.x == 0) {
         const bool ok = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);   // refused: usorted is untouched
         if (threadIdx.x == 0) p.b.robin_flags[1] = ok ? 0u : 1u;
