@@ -89,3 +89,21 @@ def test_set_max_points_only_changes_the_cap(ctx, port):
     g2 = lo.VoxelGrid(ctx, 0.5, 2)
     g2.restore(snap)
     assert g2.numPoints() == g.numPoints()
+
+
+def test_staging_copy_helper_threads(ctx, stream12, monkeypatch):
+    """lo_odometry_process on pageable scans: the staging copy with 0, 1 and 5 helper threads (LO_B200_COPY_THREADS is read when
+    a handle's pool is created, i.e. at its first pageable scan) ends on the same poses; lo_odometry_host_threads reports
+    caller + helpers."""
+    poses = []
+    for helpers in (0, 1, 5):
+        monkeypatch.setenv("LO_B200_COPY_THREADS", str(helpers))
+        od = lo.LidarOdometry(ctx)
+        for s in stream12[0][:5]:
+            od.processCloud(s)          # numpy memory: pageable
+        assert od.hostThreads() == 1 + helpers
+        poses.append(od.getCurrentPose().copy())
+        del od
+    assert np.array_equal(poses[0].view(np.uint32), poses[1].view(np.uint32)) and np.array_equal(poses[0].view(np.uint32), poses[2].view(np.uint32))
+    monkeypatch.delenv("LO_B200_COPY_THREADS")
+    assert 1 <= lo.LidarOdometry(ctx).hostThreads() <= 4
