@@ -364,7 +364,14 @@ __device__ inline uint32_t ds_insert(DsSlot* __restrict__ slots, uint32_t mask, 
         return 0xFFFFFFFFu;
     }
     const unsigned long long key = pack_key(ix, iy, iz);
-    uint32_t h = probe_hash(key) & mask;
+    // Not probe_hash: that one gives the 8 voxels of a brick 8 consecutive slots, which pays for the key frame's 27-neighbour
+    // search; a down-sampler is only inserted into, and bricks that collide make runs of occupied slots (its inserts took
+    // 7-10 k cycles per 512 points; neighbouring points of a ring are neighbouring voxels). murmur3's 64-bit finaliser.
+    unsigned long long mix = key;
+    mix ^= mix >> 33; mix *= 0xFF51AFD7ED558CCDull;
+    mix ^= mix >> 33; mix *= 0xC4CEB9FE1A85EC53ull;
+    mix ^= mix >> 33;
+    uint32_t h = static_cast<uint32_t>(mix) & mask;
     while (true) {
         unsigned long long k = slots[h].key;
         if (k == kKeyEmpty) {
@@ -435,8 +442,7 @@ __device__ inline uint32_t robin_bucket_count(uint32_t n) {  // tsl::robin_map a
 // exact block-local replay does not apply); do_count: the winners of both down-samplers are counted per block for the
 // ordered compactions of P8 (queries for align; update winners in arrival order for the replay)
 __device__ inline void phase_select(const OdomDev* s, PipeBufs b, int with_match, bool do_hist, bool do_count, bool count_update = false) {
-    uint32_t before, total;
-    block_prefix(b.block_counts, before, total);   // total = n_planar
+    const uint32_t total = __ldcg(&s->n_planar);   // written by block 0 in P6, at least one grid-wide step ago (L2: the line may sit stale in L1)
     const uint32_t buckets = robin_bucket_count(s->n_update), bin_shift = robin_bin_shift(buckets);
     uint32_t begin, end;
     chunk_range(total, begin, end);
@@ -506,10 +512,10 @@ __device__ inline uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
 // it); P9 places the winners and orders every tie group by arrival; the insert reads them through the wrap rotation.
 __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNormal* __restrict__ filtered,
                                   PointXYZ* __restrict__ query, int with_match, bool do_u, bool do_m, bool arrival_update = false) {
-    uint32_t before, total, bm = 0, nm = 0, bu = 0, nu = 0;
+    uint32_t bm = 0, nm = 0, bu = 0, nu = 0;
     if (do_m || arrival_update) {   // ordered compactions: the query cloud (if there is a key frame to match); the update winners with
                                     // their hashes in arrival order (the reference map's insertion sequence, for the replay)
-        block_prefix(b.block_counts, before, total);
+        const uint32_t total = __ldcg(&s->n_planar);
         if (do_m) block_prefix(b.block_counts + 2 * kMaxPipeBlocks, bm, nm);
         if (arrival_update) block_prefix(b.block_counts + 1 * kMaxPipeBlocks, bu, nu);
         uint32_t begin, end;
@@ -571,9 +577,8 @@ __device__ inline void phase_emit(const OdomDev* s, PipeBufs b, const PointNorma
 // P9. every update winner goes to its bucket's segment; the member that completes a tie group orders it by arrival
 // (= index in the filtered cloud). Sorted element k sits at bucket position k + max_{j<=k}(b_j - j): rb_shift collects
 // the maximum, which gives the wrap of the last cluster.
-__device__ inline void phase_robin_place(PipeBufs b) {
-    uint32_t before, total;
-    block_prefix(b.block_counts, before, total);   // total = n_planar
+__device__ inline void phase_robin_place(const OdomDev* s, PipeBufs b) {
+    const uint32_t total = __ldcg(&s->n_planar);
     int shift = INT_MIN;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const uint32_t bk = b.ubucket[i];
@@ -789,7 +794,7 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     phase_emit(s, p.b, p.filtered, p.query, with_match, true, false);
     grid.sync();
     LO_SCAN_TRACE(125);
-    phase_robin_place(p.b);
+    phase_robin_place(s, p.b);
     grid.sync();
     LO_SCAN_TRACE(126);
     uint32_t gather_shift = 0;
