@@ -203,6 +203,8 @@ def test_per_scan_kernel_update_order(ctx, real_map, stream12):
     scan the key frame holds the same points as the pipeline over the real container, and no scan reports an approximation."""
     orders = _run_against_real_container(ctx, real_map, stream12[0])
     assert all(o in (lo.LO_ORDER_SORTED, lo.LO_ORDER_REPLAYED) for o in orders), orders
+    # scan 8 of this stream has a tie group with two points in one key-frame voxel: the pair check must find it (tools/list_replayed.py)
+    assert orders[8] == lo.LO_ORDER_REPLAYED and orders.count(lo.LO_ORDER_SORTED) >= 8, orders
 
 
 def test_per_scan_kernel_replay_forced():
