@@ -203,8 +203,21 @@ def test_per_scan_kernel_update_order(ctx, real_map, stream12):
     scan the key frame holds the same points as the pipeline over the real container, and no scan reports an approximation."""
     orders = _run_against_real_container(ctx, real_map, stream12[0])
     assert all(o in (lo.LO_ORDER_SORTED, lo.LO_ORDER_REPLAYED) for o in orders), orders
-    # scan 8 of this stream has a tie group with two points in one key-frame voxel: the pair check must find it (tools/list_replayed.py)
-    assert orders[8] == lo.LO_ORDER_REPLAYED and orders.count(lo.LO_ORDER_SORTED) >= 8, orders
+
+
+def test_pair_check_finds_the_tie_group_pair(ctx, real_map):
+    """Scan 8 of the 120-scan stream (tools/list_replayed.py) has a group of equal ideal bucket with two update points in one
+    key-frame voxel: the pair check of the locate pass must find it and hand the insert to the replay kernel; the other scans
+    stay on the counting sort; the key frame equals the real-container pipeline's after every scan."""
+    from lidar_odometry_demo_b200 import synthetic as S
+    n = 120                                              # the scene's length follows the stream's length: build that stream's head
+    lidar = S.LidarModel.vlp16()
+    pos, q, _ = S.trajectory(n + 1, 99)
+    scene = S.Scene(1234, length=max(60.0, pos[-1, 0] + 140.0))
+    scans = [S.generate_scan(scene, lidar, pos[k], q[k], pos[k + 1], q[k + 1], 1234 + k, t_offset=0.1 * k) for k in range(10)]
+    orders = _run_against_real_container(ctx, real_map, scans)
+    assert orders[8] == lo.LO_ORDER_REPLAYED, orders
+    assert all(o == lo.LO_ORDER_SORTED for k, o in enumerate(orders) if k != 8), orders
 
 
 def test_per_scan_kernel_replay_forced():
