@@ -395,11 +395,25 @@ static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
     // the previous scan's DMA out of the staging buffer ended before that call returned (its kernel was waited for)
     LO_TRY(h->stage.ensure(bytes));
     if (!h->copy_pool) h->copy_pool = new CopyPool(copy_helpers());
+    // the helpers copy chunk after chunk; this thread hands every completed piece of the prefix to the DMA engine at once and
+    // copies chunks itself while there is nothing to hand over
+    CopyPool& pool = *h->copy_pool;
+    pool.begin(h->stage.p, xyzirt32, bytes);
     constexpr size_t kPiece = 256 * 1024;
-    for (size_t off = 0; off < bytes; off += kPiece) {
-        const size_t len = std::min(kPiece, bytes - off);
-        h->copy_pool->copy(h->stage.as<char>() + off, static_cast<const char*>(xyzirt32) + off, len);
-        LO_CUDA(cudaMemcpyAsync(h->scan.as<char>() + off, h->stage.as<char>() + off, len, cudaMemcpyHostToDevice, copy));
+    size_t sent = 0;
+    while (sent < bytes) {
+        const size_t ready = pool.ready_bytes();
+        if (ready - sent >= kPiece || (ready == bytes && ready > sent)) {
+            const cudaError_t e = cudaMemcpyAsync(h->scan.as<char>() + sent, h->stage.as<char>() + sent, ready - sent, cudaMemcpyHostToDevice, copy);
+            if (e != cudaSuccess) {
+                pool.finish();   // the job must be complete before the pool sees the next one
+                set_error("uploading the scan failed: %s", cudaGetErrorString(e));
+                return LO_E_CUDA;
+            }
+            sent = ready;
+        } else if (!pool.help_one()) {
+            CopyPool::cpu_relax();
+        }
     }
     if (copy != ctx->stream) {
         LO_CUDA(cudaEventRecord(h->copy_done, copy));

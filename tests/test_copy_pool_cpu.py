@@ -12,4 +12,4 @@ def test_copy_pool(tmp_path):
                    check=True, capture_output=True, text=True)
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert r.stdout.startswith("ok 2000 copies")
+    assert r.stdout.startswith("ok 3000 copies")
