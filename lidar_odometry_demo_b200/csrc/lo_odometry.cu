@@ -399,11 +399,11 @@ static int upload_scan(lo_odometry* h, const void* xyzirt32, size_t n) {
     // copies chunks itself while there is nothing to hand over
     CopyPool& pool = *h->copy_pool;
     pool.begin(h->stage.p, xyzirt32, bytes);
-    constexpr size_t kPiece = 256 * 1024;
+    constexpr size_t kPiece = 256 * 1024, kFirstPiece = 64 * 1024;   // the DMA (~40 us for a VLP16 scan) is the longer leg: start it early
     size_t sent = 0;
     while (sent < bytes) {
         const size_t ready = pool.ready_bytes();
-        if (ready - sent >= kPiece || (ready == bytes && ready > sent)) {
+        if (ready - sent >= (sent ? kPiece : kFirstPiece) || (ready == bytes && ready > sent)) {
             const cudaError_t e = cudaMemcpyAsync(h->scan.as<char>() + sent, h->stage.as<char>() + sent, ready - sent, cudaMemcpyHostToDevice, copy);
             if (e != cudaSuccess) {
                 pool.finish();   // the job must be complete before the pool sees the next one
