@@ -22,7 +22,7 @@
 #include <cstdio>
 #include <cstdlib>
 
-#include "lo_robin_block.cuh"
+#include "lo_robin_grid.cuh"
 
 namespace lo {
 
@@ -221,6 +221,17 @@ __global__ void __launch_bounds__(512, 1) robin_order_block_kernel(const uint32_
     if (threadIdx.x == 0) *refused = ok ? 0u : 1u;
 }
 
+// the same for any n up to kRobinGridMax: block replay of the first 2^14 elements, the later epochs on the whole cooperative grid
+__global__ void __launch_bounds__(512, 1) robin_order_grid_kernel(const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n,
+                                                                  uint32_t* scratch, uint32_t* __restrict__ out, uint32_t* __restrict__ refused,
+                                                                  int force_grid) {
+    extern __shared__ __align__(16) unsigned char robin_smem[];
+    cg::grid_group grid = cg::this_grid();
+    const RobinGridBufs B = robin_grid_carve(scratch, n);
+    const bool ok = robin_order_any(grid, uh, ids, n, robin_smem, B, out, force_grid != 0);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *refused = ok ? 0u : 1u;
+}
+
 int robin_export_dev(lo_grid* g, int mode, void* d_out, uint32_t* d_count) {
     return robin_export_bounded(g, mode, d_out, d_count, g->h_counters[GC_VOXELS]);
 }
@@ -233,8 +244,8 @@ using namespace lo;
 // DISTINCT keys with these hashes were inserted in index order (src/voxel_grid.h:82-87 on an empty map)
 extern "C" int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, size_t n, uint32_t* order_out) {
     if (!ctx || (!hash22 && n) || (!order_out && n)) return LO_E_ARG;
-    if (n > kRobinBlockMax) {
-        set_error("lo_robin_iteration_order takes at most %u keys (got %zu)", kRobinBlockMax, n);
+    if (n > kRobinGridMax) {
+        set_error("lo_robin_iteration_order takes at most %u keys (got %zu)", kRobinGridMax, n);
         return LO_E_CAPACITY;
     }
     if (n == 0) return LO_OK;
@@ -248,6 +259,39 @@ extern "C" int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, siz
     LO_CUDA(cudaMemcpyAsync(ctx->tmp_b.p, iota.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     LO_CUDA(cudaFuncSetAttribute(robin_order_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
     uint32_t* d_refused = ctx->small.as<uint32_t>() + 96;
+    const char* force = getenv("LO_ROBIN_GRID");   // developer switch: 1 = every epoch on the grid, whatever n
+    const int force_grid = force && force[0] == '1' ? 1 : 0;
+    if (n > kRobinBlockMax || force_grid) {
+        uint32_t nn = static_cast<uint32_t>(n);
+        LO_TRY(ctx->tmp_d.ensure(robin_grid_words(nn) * sizeof(uint32_t)));
+        LO_CUDA(cudaFuncSetAttribute(robin_order_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
+        int per_sm = 0;
+        LO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, robin_order_grid_kernel, 512, kRobinBlockSmemBytes));
+        if (per_sm < 1) {
+            set_error("the grid replay kernel does not fit on an SM");
+            return LO_E_CUDA;
+        }
+        const int blocks = std::min<int>(ctx->sm_count, static_cast<int>(kRobinGridMaxBlocks));
+        const uint32_t* d_uh = ctx->tmp_a.as<uint32_t>();
+        const uint32_t* d_ids = ctx->tmp_b.as<uint32_t>();
+        uint32_t* d_scratch = ctx->tmp_d.as<uint32_t>();
+        uint32_t* d_out = ctx->tmp_c.as<uint32_t>();
+        int fg = force_grid;
+        void* kargs[] = {&d_uh, &d_ids, &nn, &d_scratch, &d_out, &d_refused, &fg};
+        LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(robin_order_grid_kernel), dim3(blocks), dim3(512), kargs, kRobinBlockSmemBytes,
+                                            ctx->stream));
+        ctx->launches++;
+        uint32_t refused_g = 0;
+        LO_CUDA(cudaMemcpyAsync(order_out, ctx->tmp_c.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        LO_CUDA(cudaMemcpyAsync(&refused_g, d_refused, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        LO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (refused_g) {
+            set_error("lo_robin_iteration_order: a run of more than %u occupied buckets (degenerate hashes); the epoch replay refuses it — "
+                      "VoxelGrid::getCloud* (lo_grid_get_cloud, order 1) replays any key set", kRobinBlockMaxCluster);
+            return LO_E_RANGE;
+        }
+        return LO_OK;
+    }
     static const bool profile = getenv("LO_ROBIN_PROF") != nullptr;   // developer switch: cycles per phase of the replay on stderr
     long long* d_prof = nullptr;
     if (profile) {

@@ -114,7 +114,7 @@ __device__ __forceinline__ uint32_t robin_block_chunk(uint32_t count, uint32_t n
 }
 
 // uh[k]: the reference's 22-bit hash of the k-th key in insertion (arrival) order, k < n <= kRobinBlockMax (global memory).
-// ids[k]: what to emit for element k. out[d] = ids[element at iteration position d]. All threads of ONE block of >= 512
+// ids[k]: what to emit for element k (nullptr: k itself). out[d] = ids[element at iteration position d]. All threads of ONE block of >= 512
 // threads call. Returns false (in every thread; `out` is then unspecified) if a cluster exceeded kRobinBlockMaxCluster.
 __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n, unsigned char* smem,
                                          uint32_t* __restrict__ out, long long* prof = nullptr) {
@@ -351,7 +351,7 @@ __device__ inline bool robin_order_block(const uint32_t* __restrict__ uh, const 
             if (d >= ne) d -= ne;
             const uint32_t s = sm.stash[t];
             const uint32_t e = s < lo ? sm.prev[s] : s;
-            if (last) out[d] = __ldg(ids + e);
+            if (last) out[d] = ids ? __ldg(ids + e) : e;
             else sm.seq[d] = static_cast<uint16_t>(e);
         }
         __syncthreads();

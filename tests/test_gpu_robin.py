@@ -162,6 +162,41 @@ def test_block_replay_forced_wrap_and_growth_collisions(ctx, real_map):
         _check_block_replay(ctx, real_map, keys[rng.choice(pool, n, replace=False)], rng)
 
 
+def test_grid_replay_every_epoch_on_the_grid(ctx, real_map, monkeypatch):
+    """csrc/lo_robin_grid.cuh with every epoch on the cooperative grid (LO_ROBIN_GRID=1), on sizes the block replay also takes:
+    random sets across epoch boundaries, forced wrap, collisions at every growth step."""
+    monkeypatch.setenv("LO_ROBIN_GRID", "1")
+    rng = np.random.default_rng(31)
+    keys, h = candidate_keys(30)
+    for n in (1, 2, 3, 5, 16, 17, 33, 64, 65, 257, 1000, 1025, 4097, 9000, 16384):
+        _check_block_replay(ctx, real_map, keys[rng.choice(len(keys), n, replace=False)], rng)
+    keys, h = candidate_keys(40)
+    for n, window in ((6, 2), (200, 12), (1000, 30), (1900, 200)):
+        C = 2
+        while C < 2 * n:
+            C <<= 1
+        pool = np.flatnonzero((h & (C - 1)) >= C - window)
+        _check_block_replay(ctx, real_map, keys[rng.choice(pool, n, replace=False)], rng)
+    for n, low_bits, residues in ((500, 6, (63, 0, 1)), (4000, 9, (511, 0, 1, 2, 300))):
+        pool = np.flatnonzero(np.isin(h & ((1 << low_bits) - 1), residues))
+        _check_block_replay(ctx, real_map, keys[rng.choice(pool, n, replace=False)], rng)
+
+
+def test_grid_replay_large_key_sets(ctx, real_map):
+    """Key sets beyond one block's shared memory (the update set of a 128-beam scan has ~180 k voxels): block 0 replays the
+    first 2^14 elements, the grid the epochs after that. Position by position against the real container."""
+    rng = np.random.default_rng(32)
+    keys, h = candidate_keys(48)           # 884 736 candidate voxels
+    for n in (16385, 20000, 32768, 32769, 70000, 180000, 300000):
+        _check_block_replay(ctx, real_map, keys[rng.choice(len(keys), n, replace=False)], rng)
+    # collisions at every growth step and a wrapping cluster at this size
+    pool = np.flatnonzero(np.isin(h & 1023, (1023, 0, 1, 2, 3, 4, 500, 501)))
+    _check_block_replay(ctx, real_map, keys[rng.choice(pool, 6500, replace=False)], rng)
+    n = 40000
+    pool = np.flatnonzero((h & 131071) >= 131072 - 60000)
+    _check_block_replay(ctx, real_map, keys[rng.choice(pool, n, replace=False)], rng)
+
+
 def test_block_replay_scan_update_sets(ctx, real_map, port, stream12):
     """The real use: the 0.1 m down-sampler of a scan's planar cloud (12-15 k voxels)."""
     for k in (1, 5, 9):
