@@ -36,7 +36,7 @@
 #include "lo_align.cuh"
 #include "lo_grid.cuh"
 #include "lo_odometry.cuh"
-#include "lo_robin_block.cuh"
+#include "lo_robin_grid.cuh"
 #include "lo_stages.cuh"
 
 namespace lo {
@@ -66,6 +66,7 @@ struct PipeBufs {                          // carved out of lo_odometry::fused
     uint32_t* ubucket;                     // [n] ideal robin_map bucket of filtered point i if it is an update winner, else ~0
     uint32_t* uarr;                        // [n] update winners in arrival order (index into filtered) = the reference's insertion order
     uint32_t* uhash;                       // [n] their 22-bit reference hashes
+    uint32_t* robin_grid;                  // [robin_grid_words(n)] scratch of the grid-wide replay (update sets of more than 2^14 points)
     uint32_t* usorted;                     // [n] update winners in robin_map order (index into filtered)
     uint32_t* umember;                     // [n] bucket members before a tie group is ordered
     uint32_t* rb_hist;                     // [rb_cap] winners per ideal bucket, then exclusive start of each bucket
@@ -108,6 +109,7 @@ static size_t carve(PipeBufs& b, char* base, uint32_t n) {
     b.ubucket = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.uarr = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.uhash = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
+    b.robin_grid = reinterpret_cast<uint32_t*>(take(robin_grid_words(n) * 4));
     b.usorted = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     b.umember = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(n) * 4));
     uint32_t rb = 2;
@@ -809,8 +811,7 @@ __device__ __forceinline__ void scan_body(const ScanArgs& p) {
     // voxel_grid.h:82-91): the pass looks for such a pair. None (about 39 scans in 40 of the VLP16 stream): the key frame
     // comes out exactly as from the reference's order.
     uint32_t update_order = kOrderSorted;
-    bool can_replay = false;
-    if constexpr (!kTiled) can_replay = nu <= kRobinBlockMax && gridDim.x > 1;
+    const bool can_replay = gridDim.x > 1;   // one block alone could not wait for itself in the replay kernel's hand-over
     {
         const PointSource src{reinterpret_cast<const float*>(p.filtered), 12u, 1, p.b.usorted, nu, gather_shift};
         bool pair_found = false;
@@ -893,14 +894,12 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_replay_kernel(ScanArgs p
     grid.sync();
     phase_emit(s, p.b, p.filtered, p.query, 0, false, false, true);
     grid.sync();
-    if (blockIdx.x == 0) {
-        const bool ok = robin_order_block(p.b.uhash, p.b.uarr, nu, dyn_smem, p.b.usorted);   // refused: usorted is untouched
-        if (threadIdx.x == 0) p.b.robin_flags[1] = ok ? 0u : 1u;
-    }
     __shared__ Pose pose_s;
     if (threadIdx.x == 0) pose_s = s->current;
-    grid.sync();
-    const bool exact = __ldcg(p.b.robin_flags + 1) == 0u;
+    // up to 2^14 update points: block 0 alone, in shared memory; more (a 128-beam scan): the later epochs on the whole grid
+    const RobinGridBufs rg = robin_grid_carve(p.b.robin_grid, max(p.n, 1u));
+    const bool exact = robin_order_any(grid, p.b.uhash, p.b.uarr, nu, dyn_smem, rg, p.b.usorted, false);   // refused: usorted is untouched
+    __syncthreads();
     const Pose* insert_pose = deferred == 2u ? nullptr : &pose_s;
     uint32_t gather_shift = 0;
     if (!exact && nu) {   // a run of more than 2 048 occupied buckets: the counting-sort order and its rotation stand
@@ -1009,7 +1008,7 @@ int lo::fused_process_enqueue(lo_odometry* h, const PointXYZIRT* d_scan, uint32_
     }
     h->scan_seq = p.seq;
     ctx->launches++;
-    if (n <= kSmallScanPoints) {   // returns at once unless scan_kernel left the insert to it (see there)
+    {   // returns at once unless the scan kernel left the insert to it (see there)
         const cudaError_t e2 = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(scan_replay_kernel), dim3(blocks), dim3(kPipeThreads), kargs,
                                                            kRobinBlockSmemBytes, ctx->stream);
         if (e2 != cudaSuccess) {

@@ -42,7 +42,7 @@ if __name__ == "__main__":
     oc = None
     if "--no-oracle" not in sys.argv:
         import oracle
-        orc = oracle.load("port")
+        orc = oracle.load("reference" if oracle.available("reference") else "port")
         op = orc.default_params()
         op.keyframe_voxel_size, op.keyframe_update_voxel_size, op.keyframe_matching_voxel_size = 0.1, 0.05, 0.05
         op.keyframe_max_points_cnt = 20
@@ -52,6 +52,9 @@ if __name__ == "__main__":
     torch.cuda.synchronize()
     worst, ms, t_cpu = (0.0, 0.0), [], 0.0
     orders = [0, 0, 0]
+    kf_equal = 0
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+    from util import sort_rows
     for k, sc in enumerate(scans):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -71,10 +74,13 @@ if __name__ == "__main__":
             dr = float(2 * np.arccos(min(1.0, abs(qa @ qb))))
             worst = (max(worst[0], dt), max(worst[1], dr))
             assert (st.n_planar, st.n_update, st.n_query) == (counts[1], counts[2], counts[3]), (k, st.n_planar, st.n_update, st.n_query, counts)
+            ka, kb = od.getKeyFrameCloudWithNormals(), oc.keyframe_pn()   # the key frame as a multiset of (point, normal) bit patterns
+            kf_equal += int(len(ka) == len(kb) and np.array_equal(sort_rows(ka), sort_rows(kb)))
         print(k, f"{ms[-1]:.3f} ms", st.n_planar, st.n_update, st.n_query, st.outer_iterations, st.keyframe_voxels, file=sys.stderr)
     print(json.dumps({"workload": "config 3: 128 x 2048 returns per scan, voxels 0.1 / 0.05 / 0.05", "scans": n, "points_per_scan": len(scans[0]),
                       "update_order": {"counting_sort_exact": orders[0], "replayed": orders[1], "approximate": orders[2]},
                       "ms_per_scan_after_first": float(np.mean(ms[1:])), "scans_per_s": 1e3 / float(np.mean(ms[1:])),
                       "cpu_oracle_scans_per_s": (n / t_cpu) if oc is not None else None,
-                      "max_pose_err_m": worst[0], "max_pose_err_rad": worst[1], "kernel_launches": int(ctx.kernel_launches),
+                      "max_pose_err_m": worst[0], "max_pose_err_rad": worst[1],
+                      "scans_with_keyframe_identical_to_the_oracle": kf_equal if oc is not None else None, "kernel_launches": int(ctx.kernel_launches),
                       "ms_per_scan": [float(v) for v in ms], "keyframe": od.keyframeInfo().as_dict()}))
