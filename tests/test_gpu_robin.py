@@ -283,3 +283,43 @@ def test_per_scan_kernel_replay_forced():
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, LO_B200_REPLAY_ALWAYS="1"), cwd=root, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert "replayed 8" in r.stdout
+
+
+def test_large_scan_update_order_replayed_on_the_grid():
+    """A 64-beam scan (131 072 rays, update voxels of 0.05 m: update sets of several 10^4 points, beyond one block's shared
+    memory) through scan_kernel_large with the replay forced on every scan: the grid-wide replay (csrc/lo_robin_grid.cuh)
+    must leave the key frame exactly as the pipeline over the real container does."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, ctypes, numpy as np\n"
+        "sys.path.insert(0, 'tests')\n"
+        "import lidar_odometry_demo_b200 as lo, oracle\n"
+        "from lidar_odometry_demo_b200 import synthetic as S\n"
+        "from util import sort_rows\n"
+        "orc = oracle.load('reference' if oracle.available('reference') else 'port')\n"
+        "lidar = S.LidarModel(64, 2048, -25.0, 15.0)\n"
+        "pos, q, _ = S.trajectory(4, 99)\n"
+        "scene = S.Scene(4321, length=400.0, scale=2.0)\n"
+        "scans = [S.generate_scan(scene, lidar, pos[k], q[k], pos[k + 1], q[k + 1], 4321 + k, t_offset=0.1 * k) for k in range(3)]\n"
+        "p = lo.Params(); lo.load_library().lo_params_default(ctypes.byref(p))\n"
+        "p.keyframe_voxel_size, p.keyframe_update_voxel_size, p.keyframe_matching_voxel_size = 0.1, 0.05, 0.05\n"
+        "op = orc.default_params()\n"
+        "op.keyframe_voxel_size, op.keyframe_update_voxel_size, op.keyframe_matching_voxel_size = 0.1, 0.05, 0.05\n"
+        "ctx = lo.Context(0)\n"
+        "od, oc = lo.LidarOdometry(ctx, p, keyframe_voxels=1 << 20, scan_points=1 << 17), orc.odometry(op)\n"
+        "for k, s in enumerate(scans):\n"
+        "    od.processCloud(s); oc.process(s)\n"
+        "    st = od.stats()\n"
+        "    assert st.n_update > 16384, st.n_update\n"
+        "    assert st.update_order == lo.LO_ORDER_REPLAYED, (k, st.update_order)\n"
+        "    a, b = od.getKeyFrameCloudWithNormals(), oc.keyframe_pn()\n"
+        "    assert len(a) == len(b) and np.array_equal(sort_rows(a), sort_rows(b)), k\n"
+        "    d = np.abs(od.getCurrentPose().astype(np.float64) - oc.pose().astype(np.float64)).max()\n"
+        "    assert d < 1e-5, (k, d)\n"
+        "print('replayed', len(scans))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, LO_B200_REPLAY_ALWAYS="1"), cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "replayed 3" in r.stdout
