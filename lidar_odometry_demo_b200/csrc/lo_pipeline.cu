@@ -898,7 +898,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) scan_replay_kernel(ScanArgs p
     if (threadIdx.x == 0) pose_s = s->current;
     // up to 2^14 update points: block 0 alone, in shared memory; more (a 128-beam scan): the later epochs on the whole grid
     const RobinGridBufs rg = robin_grid_carve(p.b.robin_grid, max(p.n, 1u));
-    const bool exact = robin_order_any(grid, p.b.uhash, p.b.uarr, nu, dyn_smem, rg, p.b.usorted, false);   // refused: usorted is untouched
+    const bool exact = robin_order_any(grid, p.b.uhash, p.b.uarr, nu, dyn_smem, rg, p.b.usorted, kRobinHandover);   // refused: usorted is untouched
     __syncthreads();
     const Pose* insert_pose = deferred == 2u ? nullptr : &pose_s;
     uint32_t gather_shift = 0;

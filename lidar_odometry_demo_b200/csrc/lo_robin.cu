@@ -224,11 +224,11 @@ __global__ void __launch_bounds__(512, 1) robin_order_block_kernel(const uint32_
 // the same for any n up to kRobinGridMax: block replay of the first 2^14 elements, the later epochs on the whole cooperative grid
 __global__ void __launch_bounds__(512, 1) robin_order_grid_kernel(const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n,
                                                                   uint32_t* scratch, uint32_t* __restrict__ out, uint32_t* __restrict__ refused,
-                                                                  int force_grid) {
+                                                                  uint32_t handover) {
     extern __shared__ __align__(16) unsigned char robin_smem[];
     cg::grid_group grid = cg::this_grid();
     const RobinGridBufs B = robin_grid_carve(scratch, n);
-    const bool ok = robin_order_any(grid, uh, ids, n, robin_smem, B, out, force_grid != 0);
+    const bool ok = robin_order_any(grid, uh, ids, n, robin_smem, B, out, handover);
     if (blockIdx.x == 0 && threadIdx.x == 0) *refused = ok ? 0u : 1u;
 }
 
@@ -260,8 +260,11 @@ extern "C" int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, siz
     LO_CUDA(cudaFuncSetAttribute(robin_order_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
     uint32_t* d_refused = ctx->small.as<uint32_t>() + 96;
     const char* force = getenv("LO_ROBIN_GRID");   // developer switch: 1 = every epoch on the grid, whatever n
+    const char* hand = getenv("LO_ROBIN_HANDOVER");   // developer switch: the block replays the first 2^k elements (k <= 14), the grid the rest
     const int force_grid = force && force[0] == '1' ? 1 : 0;
-    if (n > kRobinBlockMax || force_grid) {
+    uint32_t handover = force_grid ? 0u : kRobinHandover;
+    if (hand && !force_grid) handover = static_cast<uint32_t>(std::max(1, std::min(14, atoi(hand))));
+    if (n > (1u << handover) || force_grid) {
         uint32_t nn = static_cast<uint32_t>(n);
         LO_TRY(ctx->tmp_d.ensure(robin_grid_words(nn) * sizeof(uint32_t)));
         LO_CUDA(cudaFuncSetAttribute(robin_order_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kRobinBlockSmemBytes)));
@@ -276,8 +279,7 @@ extern "C" int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, siz
         const uint32_t* d_ids = ctx->tmp_b.as<uint32_t>();
         uint32_t* d_scratch = ctx->tmp_d.as<uint32_t>();
         uint32_t* d_out = ctx->tmp_c.as<uint32_t>();
-        int fg = force_grid;
-        void* kargs[] = {&d_uh, &d_ids, &nn, &d_scratch, &d_out, &d_refused, &fg};
+        void* kargs[] = {&d_uh, &d_ids, &nn, &d_scratch, &d_out, &d_refused, &handover};
         LO_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(robin_order_grid_kernel), dim3(blocks), dim3(512), kargs, kRobinBlockSmemBytes,
                                             ctx->stream));
         ctx->launches++;

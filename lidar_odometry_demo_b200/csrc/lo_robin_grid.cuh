@@ -1,8 +1,9 @@
 // The epoch replay of lo_robin_block.cuh for key sets that do not fit one block's shared memory (update sets of more than
 // 16 384 points: a 128-beam scan has ~180 k): the same phases, run by the whole cooperative grid on 32-bit arrays in global
 // memory (L2 resident), with grid-wide barriers where the block version has block barriers. It continues where the block
-// version stops: block 0 replays the first 2^14 elements in shared memory (epochs 0..14, where a grid-wide barrier per
-// phase would cost more than the work), the grid takes the epochs from there — four of them for 180 k keys.
+// version stops: block 0 replays the first 2^12 elements in shared memory (epochs 0..12, where a grid-wide barrier per
+// phase would cost more than the work), the grid takes the epochs from there — two for a VLP16 update set, six for the
+// 180 k keys of a 128-beam scan.
 // See lo_robin_block.cuh for the algorithm; the phase names are the same.
 #pragma once
 
@@ -300,13 +301,17 @@ __device__ inline bool robin_order_grid(cg::grid_group& grid, const uint32_t* __
     return true;
 }
 
-// The order for any n: block 0 replays the first min(n, 2^14) elements in its shared memory (`smem`: kRobinBlockSmemBytes,
-// needed in block 0 only), the grid takes the epochs after that. force_grid: every epoch on the grid (tests).
-// Every thread of the cooperative grid calls; returns false (uniformly) if the key set was refused.
+// The order for any n: block 0 replays the first 2^handover elements in its shared memory (`smem`: kRobinBlockSmemBytes, needed in
+// block 0 only; epochs 0 .. handover, where a grid-wide barrier per phase would cost more than the work), the grid takes the
+// epochs after that. handover <= 14; 0: every epoch on the grid (tests). Every thread of the cooperative grid calls; returns
+// false (uniformly) if the key set was refused.
 constexpr uint32_t kRobinGridMax = 1u << 19;   // keys: what the per-scan kernels take as a scan
+constexpr uint32_t kRobinHandover = 12;   // measured: 13 000 keys take 0.27 ms with 2^12 against 0.33 ms with 2^14 (all in the block) and 0.31 ms with 2^10
 __device__ inline bool robin_order_any(cg::grid_group& grid, const uint32_t* __restrict__ uh, const uint32_t* __restrict__ ids, uint32_t n,
-                                       unsigned char* smem, const RobinGridBufs& B, uint32_t* __restrict__ out, bool force_grid) {
-    if (n <= kRobinBlockMax && !force_grid) {
+                                       unsigned char* smem, const RobinGridBufs& B, uint32_t* __restrict__ out, uint32_t handover) {
+    const uint32_t first = 1u << handover;
+    if (handover == 0) return robin_order_grid(grid, uh, ids, n, B, out, 0u, 0u);
+    if (n <= first) {
         if (blockIdx.x == 0) {
             const bool ok = robin_order_block(uh, ids, n, smem, out);
             if (threadIdx.x == 0) B.flags[1] = ok ? 0u : 1u;
@@ -314,14 +319,13 @@ __device__ inline bool robin_order_any(cg::grid_group& grid, const uint32_t* __r
         grid.sync();
         return __ldcg(B.flags + 1) == 0u;
     }
-    if (force_grid) return robin_order_grid(grid, uh, ids, n, B, out, 0u, 0u);
-    if (blockIdx.x == 0) {   // epochs 0 .. 14: the iteration order of the first 2^14 elements, as element indices
-        const bool ok = robin_order_block(uh, nullptr, kRobinBlockMax, smem, B.prev[0]);
+    if (blockIdx.x == 0) {   // epochs 0 .. handover: the iteration order of the first 2^handover elements, as element indices
+        const bool ok = robin_order_block(uh, nullptr, first, smem, B.prev[0]);
         if (threadIdx.x == 0) B.flags[1] = ok ? 0u : 1u;
     }
     grid.sync();
     if (__ldcg(B.flags + 1)) return false;
-    return robin_order_grid(grid, uh, ids, n, B, out, 15u, kRobinBlockMax);
+    return robin_order_grid(grid, uh, ids, n, B, out, handover + 1u, first);
 }
 
 }  // namespace lo
