@@ -84,8 +84,8 @@ int lo_grid_get_cloud(lo_grid* g, int mode, int order, void* out, size_t cap, si
  * fills it): order_out[d] = index of the key at iteration position d after n DISTINCT keys with the 22-bit hashes hash22[0..n)
  * (IndicesHash, src/voxel_grid.h:31-38) were inserted in index order into an empty map. This is the block-local replay
  * (csrc/lo_robin_block.cuh) the per-scan pipeline runs for keyframe_downsampler.getCloud() (src/lidar_odometry.cpp:38,69) when
- * the order inside a group of equal ideal bucket matters; n <= 524 288 (LO_E_CAPACITY; beyond 16 384 the later epochs run on
- * the whole grid, csrc/lo_robin_grid.cuh); LO_E_RANGE for a key set with a run of
+ * the order inside a group of equal ideal bucket matters; n <= 524 288 (LO_E_CAPACITY; one block replays the first
+ * 4 096 keys in shared memory, the later epochs run on the whole grid, csrc/lo_robin_grid.cuh); LO_E_RANGE for a key set with a run of
  * more than 2 048 occupied buckets (degenerate hashes: lo_grid_get_cloud with order 1 replays any key set, sequentially). */
 int lo_robin_iteration_order(lo_ctx* ctx, const uint32_t* hash22, size_t n, uint32_t* order_out);
 /* radiusCleanup (:236-246): erase voxels whose FIRST stored point is farther than radius from center */
